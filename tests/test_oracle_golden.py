@@ -1,0 +1,69 @@
+"""CPU: the oracle restatement must reproduce the live reference's golden outputs (fp32, tol 2e-5)."""
+import numpy as np
+import torch
+
+from conftest import load_case, noise_bank, rel_l2
+from oracle.unet_oracle import DenoiserOracle, cylindrical_conv, sample_ddim, sample_edm
+
+TOL = 2e-5  # fp32 CPU vs fp32 CPU, different op order only
+
+
+def test_cylconv_known_answer():
+    """reference calodiffusion/tests/test_cyl_conv.py:7-25: rows [9,18,15] on every phi row."""
+    import os
+    from conftest import GOLDEN
+    kat = np.load(os.path.join(GOLDEN, "cylconv_kat.npz"))
+    x = torch.from_numpy(kat["x"])
+    w = torch.ones(1, 1, 1, 3, 3)
+    y = cylindrical_conv(x, w, None, padding=(0, 1, 1)).numpy()
+    assert np.array_equal(y, kat["y"])
+    assert y.reshape(4, 3).tolist() == [[9.0, 18.0, 15.0]] * 4
+
+
+def test_denoise_matches_reference(case):
+    name, c = case
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    for tag in ("a", "b"):
+        sig = torch.from_numpy(c["gold"][f"denoise_{tag}_sigma"])
+        scale = (1 + sig.view(-1, 1, 1, 1, 1) ** 2).sqrt()
+        with torch.no_grad():
+            y = m.denoise(c["x"] * scale, c["E"], sig, c["layers"]).numpy()
+        assert rel_l2(y, c["gold"][f"denoise_{tag}"]) < TOL, (name, tag)
+
+
+def test_ddpm_ddim_match_reference():
+    c = load_case("ds2")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    for name, steps, eta in (("DDPM", 4, 1.0), ("DDim", 3, 0.0)):
+        bank = noise_bank(c["shape"], c["B"], steps)
+        with torch.no_grad():
+            x, xs, x0s = sample_ddim(m, c["x"], c["E"], c["layers"], steps, eta, bank)
+        assert rel_l2(torch.stack(x0s).numpy(), c["gold"][f"{name}_x0s"]) < TOL
+        assert rel_l2(torch.stack(xs).numpy(), c["gold"][f"{name}_xs"]) < TOL
+        assert rel_l2(x.numpy(), c["gold"][f"{name}_x"]) < TOL
+
+
+def test_edm_euler_heun_match_reference():
+    c = load_case("ds3")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    for name, order in (("Euler", 1), ("Heun", 2)):
+        bank = noise_bank(c["shape"], c["B"], 3)
+        with torch.no_grad():
+            x, xs, x0s = sample_edm(m, c["x"], c["E"], None, 3, order, bank)
+        assert rel_l2(torch.stack(x0s).numpy(), c["gold"][f"{name}_x0s"]) < 5e-5
+        assert rel_l2(torch.stack(xs).numpy(), c["gold"][f"{name}_xs"]) < 5e-5
+        if name == "Euler":
+            assert rel_l2(x.numpy(), c["gold"]["Euler_x"]) < 5e-5
+        else:  # reference defect: Heun's last step divides by t_next = 0
+            assert not np.isfinite(c["gold"]["Heun_x"]).any()
+            assert not np.isfinite(x.numpy()).any()
+
+
+def test_hgcal_ddim_matches_reference():
+    c = load_case("hgcal")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    bank = noise_bank(c["shape"], c["B"], 2)
+    with torch.no_grad():
+        x, xs, x0s = sample_ddim(m, c["x"], c["E"], c["layers"], 2, 0.0, bank)
+    assert rel_l2(torch.stack(x0s).numpy(), c["gold"]["DDim_x0s"]) < TOL
+    assert rel_l2(x.numpy(), c["gold"]["DDim_x"]) < TOL
