@@ -1,0 +1,114 @@
+// Shared device/host definitions for the CaloDiffusion B200 denoiser library.
+//
+// Activation layout ("padded-linear, chunk-planar", PLCP), one tensor = C/8 chunk planes:
+//   plane k holds, for every row g of the padded-linear voxel space, channels 8k..8k+7 as 8 halves
+//   (16 bytes).  Rows enumerate (sample b, z in [0,Z], pp in [0,P+2), rr in [0,R+1)):
+//       g = ((b*(Z+1) + z)*(P+2) + pp)*(R+1) + rr
+//   pp = p+1 (pp=0 and pp=P+1 are circular phi copies of p=P-1 and p=0), rr = r (rr=R is a zero
+//   column shared by r=R of this phi row and r=-1 of the next), z=Z is a zero plane shared by z=Z of
+//   this sample and z=-1 of the next.  Every 3x3x3 neighbour of an interior voxel is then at the
+//   constant row offset dz*(P+2)*(R+1) + dp*(R+1) + dr, which is what lets the tcgen05 implicit-GEMM
+//   kernel fetch its A operand with plain 1-D bulk copies and address taps as shifted smem windows
+//   (reference semantics: circular phi + zero Z/R padding, models/models.py:90-96).
+//   `guard` zero rows precede row 0 and follow the last row of every chunk plane.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cd {
+
+struct Geom {       // one U-Net resolution level
+    int Z, P, R;    // interior extents
+    int Rp, Pp;     // R+1, P+2
+    int plane;      // Pp*Rp rows per z-plane
+    int rows_per_sample;  // (Z+1)*plane
+    int guard;      // zero rows before/after the payload in each chunk plane
+    long long chunk_stride;  // rows per chunk plane incl. guards (fixed by max batch)
+};
+
+struct TensorRef {  // a PLCP tensor
+    __half* base;   // start of chunk plane 0 (guard included)
+    int C;          // channels (multiple of 8)
+};
+
+__host__ __device__ inline long long plcp_offset(const Geom& g, int chunk, long long row) {
+    // element offset (in halves) of channel 8*chunk of padded-linear row `row`
+    return ((long long)chunk * g.chunk_stride + g.guard + row) * 8;
+}
+
+// Decode a padded-linear row. Returns kind: 0 interior, 1 phi-halo (src row returned), 2 zero row.
+struct RowInfo {
+    int b, z, pp, rr;
+    int kind;
+    long long src;  // for kind 1: the interior row this halo row mirrors; else the row itself
+};
+
+__device__ __forceinline__ RowInfo decode_row(const Geom& g, long long row) {
+    RowInfo ri;
+    int b = (int)(row / g.rows_per_sample);
+    int rem = (int)(row - (long long)b * g.rows_per_sample);
+    int z = rem / g.plane;
+    int rem2 = rem - z * g.plane;
+    int pp = rem2 / g.Rp;
+    int rr = rem2 - pp * g.Rp;
+    ri.b = b; ri.z = z; ri.pp = pp; ri.rr = rr;
+    ri.src = row;
+    if (z == g.Z || rr == g.R) {
+        ri.kind = 2;
+    } else if (pp == 0) {
+        ri.kind = 1; ri.src = row + (long long)g.P * g.Rp;
+    } else if (pp == g.P + 1) {
+        ri.kind = 1; ri.src = row - (long long)g.P * g.Rp;
+    } else {
+        ri.kind = 0;
+    }
+    return ri;
+}
+
+__host__ __device__ inline long long interior_row(const Geom& g, int b, int z, int p, int r) {
+    return (((long long)b * (g.Z + 1) + z) * g.Pp + (p + 1)) * g.Rp + r;
+}
+
+// ---- conv descriptors -------------------------------------------------------------------------
+struct ConvSrc {
+    const __half* base;
+    int C;
+};
+
+struct ConvParams {
+    Geom gin, gout;
+    ConvSrc src[2];
+    int nsrc;
+    int Cin_total;
+    __half* dst;        // PLCP output (C_out channels)
+    int Cout;
+    const float* w;     // packed [tap][ci][co] fp32
+    const float* bias;  // [co] or nullptr
+    int kz, kp, kr;
+    int sz, sp, sr;     // strides
+    int pz, cp, pr;     // zero pad Z, circular pad phi, zero pad R   (transposed: padding 1, 3(kp-1), 1)
+    int transposed;
+    int write_halo;     // 1: produce all rows incl. halos (gather form); 0: interior rows only
+    double* stats;      // [B][Cout][2] (sum, sumsq) or nullptr
+    int B;
+};
+
+// ---- small helpers ----------------------------------------------------------------------------
+__device__ __forceinline__ float silu_f(float v) { return v / (1.0f + __expf(-v)); }
+__device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f)); }
+
+struct alignas(16) Half8 { __half2 h[4]; };
+
+__device__ __forceinline__ void unpack8(const Half8& v, float* f) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 t = __half22float2(v.h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ Half8 pack8(const float* f) {
+    Half8 v;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v.h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+    return v;
+}
+
+}  // namespace cd

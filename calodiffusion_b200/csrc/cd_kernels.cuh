@@ -1,0 +1,51 @@
+// Launcher declarations for the hand-written kernels.
+#pragma once
+#include "cd_common.cuh"
+
+namespace cd {
+
+struct EmbedParams {
+    const float* tw[3]; const float* tb[3];   // time MLP  Linear(1,h/2) GELU Linear(h/2,h) GELU Linear(h,h)
+    const float* cw[3]; const float* cb[3];   // cond MLP  Linear(cs,hid) GELU Linear(hid,h) GELU Linear(h,h)
+    int cond_size, cond_hidden, cond_dim, time_mode;  // time_mode 0: sigma/sqrt(1+sigma^2), 1: 0.5*log(sigma)
+    int n_proj;
+    const float* pw[16]; const float* pb[16]; int pC[16]; int poff[16];
+    int addvec_stride;
+};
+
+struct FinalParams {
+    Geom g;
+    const __half* h; int C;
+    const float* w; float bias;         // final conv weights (C) + bias
+    const float* x;                     // denoiser input (B, voxels) fp32
+    const float* sigma; int sigma_stride; float sigma_data;
+    float* pred_out;                    // optional raw network output
+    float* x0_out;                      // optional denoised output
+    float* x_out;                       // optional sampler-updated state
+    const float* coef;                  // k0..k4 (device)
+    const float* a1; const float* a2; const float* a3;
+    int rng_enabled; unsigned long long seed; int shower_offset; int step;
+};
+
+void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,
+                       const float* r_vals, int rz_input, int phi_input, __half* dst, int B, cudaStream_t st);
+void launch_conv_generic(const ConvParams& p, cudaStream_t st);
+void launch_gn_finalize(const double* stats, const float* gamma, const float* beta, float2* affine, int B, int C,
+                        int groups, double count_per_channel, cudaStream_t st);
+void launch_gn_apply(const Geom& g, const __half* src, const float2* affine, const float* addvec, int addvec_stride,
+                     const __half* residual, __half* dst, int C, int act, int B, cudaStream_t st);
+void launch_row_stats(const Geom& g, const __half* src, double* stats, int C, int B, cudaStream_t st);
+void launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, __half* dst, int B, cudaStream_t st);
+void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, const float* cond, float* addvec, int B,
+                  cudaStream_t st);
+void launch_final(const FinalParams& p, int B, cudaStream_t st);
+void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps,
+                  unsigned long long seed, int shower_offset, int step, int rng_enabled, cudaStream_t st);
+void launch_fill_normal(float* out, long long n, int vps, unsigned long long seed, int shower_offset, int step,
+                        cudaStream_t st);
+
+// tcgen05 implicit-GEMM convolution (cd_conv_mma.cu); returns 0 if the shape is supported and was launched
+struct MmaConvWeights;  // packed fp16 weights, see cd_conv_mma.cu
+int launch_conv_mma(const ConvParams& p, const __half* packed_w, cudaStream_t st);
+
+}  // namespace cd
