@@ -1,0 +1,841 @@
+// Engine: builds the CondUnet evaluation plan from a cd_unet_desc + reference-named weights, owns the
+// PLCP activation workspaces, and exposes the C ABI of include/calodiffusion_b200.h.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/calodiffusion_b200.h"
+#include "cd_kernels.cuh"
+
+namespace cd {
+
+static thread_local char g_err[1024] = "";
+static int fail(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+#define CD_CUDA(call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct HostTensor {
+    std::vector<float> data;
+    std::vector<int64_t> shape;
+};
+
+struct ConvW {
+    float* w = nullptr;      // [tap][ci][co] fp32 (generic kernel)
+    float* bias = nullptr;   // [co]
+    __half* wmma = nullptr;  // [tap][ci/8][co][8] fp16 (tcgen05 kernel), only for stride-1 non-transposed convs
+    int Cin = 0, Cout = 0, kz = 1, kp = 1, kr = 1;
+    int transposed = 0;
+};
+
+struct Run {  // per-call state
+    int B;
+    cudaStream_t st;
+    const float* x;        // (B, voxels) fp32 denoiser input
+    const float* sigma;    // per-sample (stride 1) or broadcast (stride 0)
+    int sigma_stride;
+    const float* cond;     // (B, cond_size)
+    int scale_input;       // 1: multiply x by c_in (denoise); 0: raw forward
+    FinalParams fin;       // output routing of the final kernel
+};
+
+struct Buf { int level, C; __half* ptr; bool busy; };
+
+}  // namespace cd
+
+using namespace cd;
+
+struct cd_unet {
+    cd_unet_desc d;
+    int n_levels = 0;
+    Geom geom[CD_MAX_LEVELS];
+    std::map<std::string, HostTensor> weights;
+    std::vector<void*> dev_allocs;
+    std::vector<Buf> bufs;
+    std::vector<std::function<void(Run&)>> ops;
+    bool finalized = false;
+    int conv_backend = 0;
+    int64_t workspace_bytes = 0;
+    int64_t launches = 0;
+    int launches_per_forward = 0;
+    // scratch (zeroed per forward): per-sample byte size and base
+    unsigned char* scratch = nullptr;
+    size_t scratch_per_sample = 0;
+    // persistent small buffers
+    float* r_vals = nullptr;
+    float* addvec = nullptr;  // [maxB][addvec_stride]
+    int addvec_stride = 0;
+    float* final_w = nullptr;
+    float final_b = 0.f;
+    int final_C = 0;
+    const __half* final_h = nullptr;
+    EmbedParams embed;
+    // sampling state
+    float* state[CD_NUM_STATE_BUFS] = {nullptr, nullptr, nullptr, nullptr};
+    float* coef_tab = nullptr;  // [max_evals][8]
+    int coef_cap = 0;
+    float* unit_sigma = nullptr;
+    // graph cache
+    cudaGraphExec_t graph_exec = nullptr;
+    std::vector<unsigned char> graph_key;
+    int64_t graph_nodes = 0;
+
+    template <typename T>
+    T* dalloc(size_t n, bool zero = true) {
+        void* p = nullptr;
+        if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+        if (zero) cudaMemset(p, 0, n * sizeof(T));
+        dev_allocs.push_back(p);
+        workspace_bytes += (int64_t)(n * sizeof(T));
+        return (T*)p;
+    }
+    float* upload(const std::vector<float>& v) {
+        float* p = dalloc<float>(v.size(), false);
+        if (p) cudaMemcpy(p, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice);
+        return p;
+    }
+};
+
+namespace cd {
+
+static Geom make_geom(int Z, int P, int R, int max_batch) {
+    Geom g;
+    g.Z = Z; g.P = P; g.R = R;
+    g.Rp = R + 1; g.Pp = P + 2;
+    g.plane = g.Pp * g.Rp;
+    g.rows_per_sample = (Z + 1) * g.plane;
+    g.guard = ((g.plane + g.Rp + 1 + 7) / 8) * 8 + 1024;
+    long long rows = (long long)max_batch * g.rows_per_sample + 2LL * g.guard;
+    g.chunk_stride = (rows + 7) / 8 * 8;
+    return g;
+}
+
+static int acquire(cd_unet* h, int level, int C) {
+    for (size_t i = 0; i < h->bufs.size(); ++i)
+        if (!h->bufs[i].busy && h->bufs[i].level == level && h->bufs[i].C == C) { h->bufs[i].busy = true; return (int)i; }
+    Buf b;
+    b.level = level; b.C = C; b.busy = true;
+    size_t n = (size_t)(C / 8) * (size_t)h->geom[level].chunk_stride * 8;
+    b.ptr = h->dalloc<__half>(n, true);
+    h->bufs.push_back(b);
+    return (int)h->bufs.size() - 1;
+}
+static void release(cd_unet* h, int idx) { h->bufs[idx].busy = false; }
+
+static const HostTensor* find_w(cd_unet* h, const std::string& name) {
+    auto it = h->weights.find(name);
+    return it == h->weights.end() ? nullptr : &it->second;
+}
+
+// pack a conv weight; returns false (with error set) if missing / wrong shape
+static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& bname, int Cin_real, int Cin_pad, int Cout,
+                      int kz, int kp, int kr, int transposed, bool want_mma, ConvW* out) {
+    const HostTensor* w = find_w(h, wname);
+    if (!w) { fail("missing weight %s", wname.c_str()); return false; }
+    int64_t e0 = transposed ? Cin_real : Cout, e1 = transposed ? Cout : Cin_real;
+    if (w->shape.size() != 5 || w->shape[0] != e0 || w->shape[1] != e1 || w->shape[2] != kz || w->shape[3] != kp ||
+        w->shape[4] != kr) {
+        fail("weight %s has unexpected shape", wname.c_str());
+        return false;
+    }
+    int taps = kz * kp * kr;
+    std::vector<float> pk((size_t)taps * Cin_pad * Cout, 0.f);
+    for (int co = 0; co < Cout; ++co)
+        for (int ci = 0; ci < Cin_real; ++ci)
+            for (int t = 0; t < taps; ++t) {
+                size_t src = transposed ? (((size_t)ci * Cout + co) * taps + t) : (((size_t)co * Cin_real + ci) * taps + t);
+                pk[((size_t)t * Cin_pad + ci) * Cout + co] = w->data[src];
+            }
+    out->w = h->upload(pk);
+    out->Cin = Cin_pad; out->Cout = Cout; out->kz = kz; out->kp = kp; out->kr = kr; out->transposed = transposed;
+    if (!bname.empty()) {
+        const HostTensor* b = find_w(h, bname);
+        if (!b) { fail("missing weight %s", bname.c_str()); return false; }
+        if ((int)b->data.size() != Cout) { fail("bias %s has unexpected size", bname.c_str()); return false; }
+        out->bias = h->upload(b->data);
+    }
+    if (want_mma && !transposed && (Cin_pad % 16 == 0) && (Cout % 16 == 0)) {
+        std::vector<__half> hp((size_t)taps * Cin_pad * Cout);
+        int kc_n = Cin_pad / 8;
+        for (int t = 0; t < taps; ++t)
+            for (int kc = 0; kc < kc_n; ++kc)
+                for (int n = 0; n < Cout; ++n)
+                    for (int j = 0; j < 8; ++j)
+                        hp[(((size_t)t * kc_n + kc) * Cout + n) * 8 + j] =
+                            __float2half_rn(pk[((size_t)t * Cin_pad + kc * 8 + j) * Cout + n]);
+        out->wmma = h->dalloc<__half>(hp.size(), false);
+        if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
+    }
+    return true;
+}
+
+static float* upload_vec(cd_unet* h, const std::string& name, int n) {
+    const HostTensor* t = find_w(h, name);
+    if (!t) { fail("missing weight %s", name.c_str()); return nullptr; }
+    if ((int)t->data.size() != n) { fail("weight %s has unexpected size %zu (want %d)", name.c_str(), t->data.size(), n); return nullptr; }
+    return h->upload(t->data);
+}
+
+}  // namespace cd
+
+// -------------------------------------------------------------------------------------------------
+// plan construction
+// -------------------------------------------------------------------------------------------------
+namespace cd {
+
+struct Builder {
+    cd_unet* h;
+    bool ok = true;
+    size_t scratch_prefix = 0;  // bytes per sample
+
+    size_t slot(size_t bytes_per_sample) {
+        size_t off = scratch_prefix;
+        scratch_prefix += (bytes_per_sample + 15) / 16 * 16;
+        return off;
+    }
+
+    // conv: srcs are buffer indices at level_in; dst buffer at level_out
+    void conv(const ConvW& cw, int level_in, int level_out, std::vector<int> srcs, int dst, int stride, int pz, int cp, int pr,
+              int write_halo, long long stats_off /* -1: none */) {
+        cd_unet* hh = h;
+        ConvW w = cw;
+        hh->ops.push_back([=](Run& r) {
+            ConvParams p;
+            p.gin = hh->geom[level_in];
+            p.gout = hh->geom[level_out];
+            p.nsrc = (int)srcs.size();
+            p.Cin_total = w.Cin;
+            for (int i = 0; i < p.nsrc; ++i) { p.src[i].base = hh->bufs[srcs[i]].ptr; p.src[i].C = hh->bufs[srcs[i]].C; }
+            if (p.nsrc == 1) { p.src[1].base = nullptr; p.src[1].C = 0; }
+            p.dst = hh->bufs[dst].ptr;
+            p.Cout = w.Cout;
+            p.w = w.w; p.bias = w.bias;
+            p.kz = w.kz; p.kp = w.kp; p.kr = w.kr;
+            p.sz = p.sp = p.sr = stride;
+            p.pz = pz; p.cp = cp; p.pr = pr;
+            p.transposed = w.transposed;
+            p.write_halo = write_halo;
+            p.stats = stats_off >= 0 ? (double*)(hh->scratch + (size_t)stats_off * r.B) : nullptr;
+            p.B = r.B;
+            hh->launches += 1;
+            if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed && !write_halo) {
+                if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
+            }
+            launch_conv_generic(p, r.st);
+        });
+    }
+
+    // GroupNorm finalize + apply:  dst = act(GN(src)) + addvec + residual   (all rows incl. halos)
+    void gn(const std::string& gname, const std::string& bname, int level, int src, int dst, int C, int groups, long long stats_off,
+            int act, int addvec_off /* -1 none */, int residual /* -1 none */) {
+        cd_unet* hh = h;
+        float* gamma = upload_vec(hh, gname, C);
+        float* beta = upload_vec(hh, bname, C);
+        if (!gamma || !beta) { ok = false; return; }
+        float2* affine = hh->dalloc<float2>((size_t)hh->d.max_batch * C, false);
+        hh->ops.push_back([=](Run& r) {
+            const Geom& g = hh->geom[level];
+            double cnt = (double)g.Z * g.P * g.R;
+            launch_gn_finalize((const double*)(hh->scratch + (size_t)stats_off * r.B), gamma, beta, affine, r.B, C, groups, cnt, r.st);
+            launch_gn_apply(g, hh->bufs[src].ptr, affine, addvec_off >= 0 ? hh->addvec + addvec_off : nullptr, hh->addvec_stride,
+                            residual >= 0 ? hh->bufs[residual].ptr : nullptr, hh->bufs[dst].ptr, C, act, r.B, r.st);
+            hh->launches += 2;
+        });
+    }
+
+    // ResnetBlock (models.py:172-200).  srcs at `level`; returns output buffer (caller releases inputs)
+    int resblock(const std::string& pre, int level, std::vector<int> srcs, int Cin, int Cout, bool has_cond) {
+        int groups = h->d.groups;
+        ConvW c1, c2, cres;
+        if (!pack_conv(h, pre + "block1.proj.conv.weight", pre + "block1.proj.conv.bias", Cin, Cin, Cout, 3, 3, 3, 0, true, &c1) ||
+            !pack_conv(h, pre + "block2.proj.conv.weight", pre + "block2.proj.conv.bias", Cout, Cout, Cout, 3, 3, 3, 0, true, &c2)) {
+            ok = false; return -1;
+        }
+        bool has_res = find_w(h, pre + "res_conv.conv.weight") != nullptr;
+        if (!has_res && (Cin != Cout || srcs.size() != 1)) { fail("missing weight %sres_conv.conv.weight", pre.c_str()); ok = false; return -1; }
+        if (has_res && !pack_conv(h, pre + "res_conv.conv.weight", pre + "res_conv.conv.bias", Cin, Cin, Cout, 1, 1, 1, 0, true, &cres)) {
+            ok = false; return -1;
+        }
+        int addvec_off = -1;
+        if (has_cond) {
+            int k = h->embed.n_proj;
+            if (k >= 16) { fail("too many conditioned blocks"); ok = false; return -1; }
+            h->embed.pw[k] = upload_vec(h, pre + "mlp.1.weight", Cout * h->d.cond_dim);
+            h->embed.pb[k] = upload_vec(h, pre + "mlp.1.bias", Cout);
+            if (!h->embed.pw[k] || !h->embed.pb[k]) { ok = false; return -1; }
+            h->embed.pC[k] = Cout;
+            h->embed.poff[k] = h->addvec_stride;
+            addvec_off = h->addvec_stride;
+            h->addvec_stride += Cout;
+            h->embed.n_proj = k + 1;
+        }
+        size_t s1 = slot((size_t)Cout * 16), s2 = slot((size_t)Cout * 16);
+        int t1 = acquire(h, level, Cout);
+        conv(c1, level, level, srcs, t1, 1, 1, 1, 1, 0, (long long)s1);
+        int hbuf = acquire(h, level, Cout);
+        gn(pre + "block1.norm.weight", pre + "block1.norm.bias", level, t1, hbuf, Cout, groups, (long long)s1, 1, addvec_off, -1);
+        conv(c2, level, level, {hbuf}, t1, 1, 1, 1, 1, 0, (long long)s2);
+        int res = srcs[0];
+        int rbuf = -1;
+        if (has_res) {
+            rbuf = acquire(h, level, Cout);
+            conv(cres, level, level, srcs, rbuf, 1, 0, 0, 0, 0, -1);
+            res = rbuf;
+        }
+        // hbuf is free again as the destination: gn_apply reads t1 + residual only
+        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res);
+        release(h, t1);
+        if (rbuf >= 0) release(h, rbuf);
+        return hbuf;
+    }
+
+    // Residual(PreNorm(LinearAttention)) (models.py:111-117, 281-329); returns output buffer
+    int attention(const std::string& pre, int level, int x, int C) {
+        cd_unet* hh = h;
+        ConvW cq, co;
+        if (!pack_conv(h, pre + "fn.fn.to_qkv.conv.weight", "", C, C, 96, 1, 1, 1, 0, true, &cq) ||
+            !pack_conv(h, pre + "fn.fn.to_out.0.conv.weight", pre + "fn.fn.to_out.0.conv.bias", 32, 32, C, 1, 1, 1, 0, true, &co)) {
+            ok = false; return -1;
+        }
+        size_t s0 = slot((size_t)C * 16), s1 = slot((size_t)C * 16);
+        size_t skm = slot(32 * 4), sctx = slot(33 * 32 * 4);
+        hh->ops.push_back([=](Run& r) {
+            launch_row_stats(hh->geom[level], hh->bufs[x].ptr, (double*)(hh->scratch + s0 * r.B), C, r.B, r.st);
+            hh->launches += 1;
+        });
+        int xn = acquire(h, level, C);
+        gn(pre + "fn.norm.weight", pre + "fn.norm.bias", level, x, xn, C, 1, (long long)s0, 0, -1, -1);
+        int qkv = acquire(h, level, 96);
+        conv(cq, level, level, {xn}, qkv, 1, 0, 0, 0, 0, -1);
+        int ao = acquire(h, level, 32);
+        hh->ops.push_back([=](Run& r) {
+            launch_attention(hh->geom[level], hh->bufs[qkv].ptr, (unsigned*)(hh->scratch + skm * r.B),
+                             (float*)(hh->scratch + sctx * r.B), hh->bufs[ao].ptr, r.B, r.st);
+            hh->launches += 3;
+        });
+        // to_out conv -> xn reused as raw output, then GN(1) + residual x
+        conv(co, level, level, {ao}, xn, 1, 0, 0, 0, 0, (long long)s1);
+        int out = acquire(h, level, C);
+        gn(pre + "fn.fn.to_out.1.weight", pre + "fn.fn.to_out.1.bias", level, xn, out, C, 1, (long long)s1, 0, -1, x);
+        release(h, xn); release(h, qkv); release(h, ao);
+        return out;
+    }
+};
+
+static int build_plan(cd_unet* h) {
+    const cd_unet_desc& d = h->d;
+    Builder b;
+    b.h = h;
+    const std::string M = "model.";
+    int nl = h->n_levels;
+    const int* ls = d.layer_sizes;
+
+    // embedding MLPs
+    EmbedParams& e = h->embed;
+    memset(&e, 0, sizeof(e));
+    int half = d.cond_dim / 2;
+    int hid = d.cond_size > half / 2 ? d.cond_size : half / 2;
+    e.cond_size = d.cond_size; e.cond_hidden = hid; e.cond_dim = d.cond_dim; e.time_mode = d.time_embed;
+    if (d.cond_dim > 256 || hid > 256 || d.cond_size > 256) return fail("conditioning sizes above 256 are not supported");
+    const int tidx[3] = {1, 3, 5}, cidx[3] = {0, 2, 4};
+    const int tin[3] = {1, half / 2, half}, tout[3] = {half / 2, half, half};
+    const int cin[3] = {d.cond_size, hid, half}, cout[3] = {hid, half, half};
+    for (int i = 0; i < 3; ++i) {
+        e.tw[i] = upload_vec(h, M + "time_mlp." + std::to_string(tidx[i]) + ".weight", tin[i] * tout[i]);
+        e.tb[i] = upload_vec(h, M + "time_mlp." + std::to_string(tidx[i]) + ".bias", tout[i]);
+        e.cw[i] = upload_vec(h, M + "cond_mlp." + std::to_string(cidx[i]) + ".weight", cin[i] * cout[i]);
+        e.cb[i] = upload_vec(h, M + "cond_mlp." + std::to_string(cidx[i]) + ".bias", cout[i]);
+        if (!e.tw[i] || !e.tb[i] || !e.cw[i] || !e.cb[i]) return 1;
+    }
+    h->addvec_stride = 0;
+    h->ops.push_back([h](Run& r) {
+        launch_embed(h->embed, r.sigma, r.sigma_stride, r.cond, h->addvec, r.B, r.st);
+        h->launches += 1;
+    });
+
+    // input + init conv (geometry channels are generated in-kernel; Cin padded to 8)
+    int tin_buf = acquire(h, 0, 8);
+    h->ops.push_back([h, tin_buf](Run& r) {
+        launch_prep_input(h->geom[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f, h->r_vals,
+                          h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, r.B, r.st);
+        h->launches += 1;
+    });
+    ConvW cinit;
+    if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 8, ls[0], 3, 3, 3, 0, false, &cinit)) return 1;
+    int x = acquire(h, 0, ls[0]);
+    b.conv(cinit, 0, 0, {tin_buf}, x, 1, 1, 1, 1, 1, -1);
+    release(h, tin_buf);
+
+    std::vector<int> skips;
+    for (int i = 0; i < nl; ++i) {
+        std::string p = M + "downs." + std::to_string(i) + ".";
+        int cin_ = ls[i], cout_ = ls[i + 1];
+        int y = b.resblock(p + "0.", i, {x}, cin_, cout_, true);
+        if (!b.ok) return 1;
+        release(h, x);
+        int y2 = b.resblock(p + "1.", i, {y}, cout_, cout_, true);
+        if (!b.ok) return 1;
+        release(h, y);
+        int a = b.attention(M + "downs_attn." + std::to_string(i) + ".", i, y2, cout_);
+        if (!b.ok) return 1;
+        release(h, y2);
+        skips.push_back(a);
+        if (i < nl - 1) {
+            ConvW cd_;
+            if (!pack_conv(h, p + "2.conv.weight", p + "2.conv.bias", cout_, cout_, cout_, 3, 4, 4, 0, false, &cd_)) return 1;
+            x = acquire(h, i + 1, cout_);
+            b.conv(cd_, i, i + 1, {a}, x, 2, 1, 1, 1, 1, -1);
+        } else {
+            x = a;
+        }
+    }
+    int mid = ls[nl];
+    int lv = nl - 1;
+    {
+        int y = b.resblock(M + "mid_block1.", lv, {x}, mid, mid, true);
+        if (!b.ok) return 1;
+        // x is the last skip: keep it
+        int a = b.attention(M + "mid_attn.", lv, y, mid);
+        if (!b.ok) return 1;
+        release(h, y);
+        int y2 = b.resblock(M + "mid_block2.", lv, {a}, mid, mid, true);
+        if (!b.ok) return 1;
+        release(h, a);
+        x = y2;
+    }
+    for (int i = 0; i < nl; ++i) {
+        int lev = nl - 1 - i;
+        int dim_in = ls[lev], dim_out = ls[lev + 1];
+        std::string p = M + "ups." + std::to_string(i) + ".";
+        int skip = skips.back();
+        skips.pop_back();
+        int y = b.resblock(p + "0.", lev, {x, skip}, dim_out * 2, dim_in, true);
+        if (!b.ok) return 1;
+        release(h, x); release(h, skip);
+        int y2 = b.resblock(p + "1.", lev, {y}, dim_in, dim_in, true);
+        if (!b.ok) return 1;
+        release(h, y);
+        int a = b.attention(M + "ups_attn." + std::to_string(i) + ".", lev, y2, dim_in);
+        if (!b.ok) return 1;
+        release(h, y2);
+        if (i < nl - 1) {
+            const HostTensor* wt = find_w(h, p + "2.convTrans.weight");
+            if (!wt || wt->shape.size() != 5) return fail("missing weight %s2.convTrans.weight", p.c_str());
+            ConvW cu;
+            if (!pack_conv(h, p + "2.convTrans.weight", p + "2.convTrans.bias", dim_in, dim_in, dim_in, (int)wt->shape[2], 4, 4, 1, false, &cu)) return 1;
+            x = acquire(h, lev - 1, dim_in);
+            b.conv(cu, lev, lev - 1, {a}, x, 2, 1, 1, 1, 1, -1);
+            release(h, a);
+        } else {
+            x = a;
+        }
+    }
+    {
+        int y = b.resblock(M + "final_conv.0.", 0, {x}, ls[1], ls[0], false);
+        if (!b.ok) return 1;
+        release(h, x);
+        x = y;
+    }
+    h->final_w = upload_vec(h, M + "final_conv.1.conv.weight", ls[0]);
+    const HostTensor* fb = find_w(h, M + "final_conv.1.conv.bias");
+    if (!h->final_w || !fb) return fail("missing final conv weights");
+    h->final_b = fb->data[0];
+    h->final_C = ls[0];
+    h->final_h = h->bufs[x].ptr;
+    h->ops.push_back([h](Run& r) {
+        FinalParams f = r.fin;
+        f.g = h->geom[0];
+        f.h = h->final_h; f.C = h->final_C; f.w = h->final_w; f.bias = h->final_b;
+        f.x = r.x; f.sigma = r.sigma; f.sigma_stride = r.sigma_stride;
+        f.sigma_data = r.scale_input ? h->d.sigma_data : -1.f;
+        launch_final(f, r.B, r.st);
+        h->launches += 1;
+    });
+
+    h->scratch_per_sample = b.scratch_prefix;
+    h->scratch = h->dalloc<unsigned char>(h->scratch_per_sample * (size_t)d.max_batch, true);
+    h->addvec = h->dalloc<float>((size_t)d.max_batch * (h->addvec_stride > 0 ? h->addvec_stride : 1), true);
+    h->embed.addvec_stride = h->addvec_stride;
+    if (!h->scratch || !h->addvec) return fail("out of device memory for scratch");
+    return 0;
+}
+
+static int run_forward(cd_unet* h, Run& r) {
+    if (h->scratch_per_sample)
+        cudaMemsetAsync(h->scratch, 0, h->scratch_per_sample * (size_t)r.B, r.st);
+    for (auto& op : h->ops) op(r);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+}  // namespace cd
+
+// -------------------------------------------------------------------------------------------------
+// dense <-> PLCP converters (test hooks only)
+// -------------------------------------------------------------------------------------------------
+namespace cd {
+__global__ void dense_to_plcp_kernel(Geom g, const float* __restrict__ x, __half* __restrict__ dst, int C, long long nrows) {
+    long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    RowInfo ri = decode_row(g, row);
+    int p = ri.pp - 1;
+    if (p < 0) p += g.P;
+    if (p >= g.P) p -= g.P;
+    long long sp = (long long)g.Z * g.P * g.R;
+    for (int k = 0; k < C / 8; ++k) {
+        float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (ri.kind != 2)
+            for (int j = 0; j < 8; ++j)
+                f[j] = x[((long long)ri.b * C + k * 8 + j) * sp + ((long long)ri.z * g.P + p) * g.R + ri.rr];
+        *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = pack8(f);
+    }
+}
+__global__ void plcp_to_dense_kernel(Geom g, const __half* __restrict__ src, float* __restrict__ y, int C, long long nvox) {
+    long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nvox) return;
+    long long sp = (long long)g.Z * g.P * g.R;
+    int b = (int)(v / sp);
+    int rem = (int)(v - b * sp);
+    int z = rem / (g.P * g.R);
+    int rem2 = rem - z * g.P * g.R;
+    int p = rem2 / g.R, r = rem2 - p * g.R;
+    long long row = interior_row(g, b, z, p, r);
+    for (int k = 0; k < C / 8; ++k) {
+        Half8 hv = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k, row));
+        float f[8];
+        unpack8(hv, f);
+        for (int j = 0; j < 8; ++j) y[((long long)b * C + k * 8 + j) * sp + rem] = f[j];
+    }
+}
+}  // namespace cd
+
+// -------------------------------------------------------------------------------------------------
+// C ABI
+// -------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* cd_last_error(void) { return cd::g_err; }
+int cd_version(void) { return 1; }
+
+int cd_device_check(void) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail("no CUDA device: %s", cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, dev);
+    if (e != cudaSuccess) return fail("cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10) return fail("device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
+    return 0;
+}
+
+cd_unet* cd_unet_create(const cd_unet_desc* desc) {
+    if (!desc) { fail("null desc"); return nullptr; }
+    if (cd_device_check()) return nullptr;
+    if (desc->n_sizes < 2 || desc->n_sizes > CD_MAX_LEVELS + 1) { fail("unsupported LAYER_SIZE_UNET length %d", desc->n_sizes); return nullptr; }
+    for (int i = 0; i < desc->n_sizes; ++i)
+        if (desc->layer_sizes[i] % 8 != 0 || desc->layer_sizes[i] % desc->groups != 0) {
+            fail("LAYER_SIZE_UNET[%d]=%d must be a multiple of 8 and of BLOCK_GROUPS", i, desc->layer_sizes[i]);
+            return nullptr;
+        }
+    if (desc->layer_sizes[0] != desc->layer_sizes[1]) { fail("final ResnetBlock needs LAYER_SIZE_UNET[0]==[1] (models.py:697-699)"); return nullptr; }
+    if (desc->in_channels > 8 || desc->R > 64 || desc->max_batch < 1) { fail("unsupported desc"); return nullptr; }
+    cd_unet* h = new cd_unet();
+    h->d = *desc;
+    h->n_levels = desc->n_sizes - 1;
+    int Z = desc->Z, P = desc->P, R = desc->R;
+    for (int l = 0; l < h->n_levels; ++l) {
+        if (Z < 1 || P < 1 || R < 1) { fail("level %d has an empty extent", l); delete h; return nullptr; }
+        h->geom[l] = make_geom(Z, P, R, desc->max_batch);
+        Z = (Z + 1) / 2; P = P / 2; R = R / 2;  // models.py:629-634
+    }
+    return h;
+}
+
+void cd_unet_destroy(cd_unet* h) {
+    if (!h) return;
+    if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    for (void* p : h->dev_allocs) cudaFree(p);
+    delete h;
+}
+
+int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, const int64_t* shape, int ndim) {
+    if (!h || !name || !host_data) return fail("null argument");
+    if (h->finalized) return fail("weights are frozen after cd_unet_finalize; create a new handle");
+    HostTensor t;
+    int64_t n = 1;
+    for (int i = 0; i < ndim; ++i) { t.shape.push_back(shape[i]); n *= shape[i]; }
+    t.data.assign(host_data, host_data + n);
+    h->weights[name] = std::move(t);
+    return 0;
+}
+
+int cd_unet_set_option(cd_unet* h, const char* key, int value) {
+    if (!h || !key) return fail("null argument");
+    if (!strcmp(key, "conv_backend")) {
+        h->conv_backend = value;
+        if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
+        return 0;
+    }
+    return fail("unknown option %s", key);
+}
+
+int cd_unet_finalize(cd_unet* h) {
+    if (!h) return fail("null handle");
+    if (h->finalized) return 0;
+    std::vector<float> rv(h->d.r_centres, h->d.r_centres + h->d.R);
+    h->r_vals = h->upload(rv);
+    if (build_plan(h)) return 1;
+    size_t nv = (size_t)h->d.max_batch * h->d.Z * h->d.P * h->d.R;
+    for (int i = 0; i < CD_NUM_STATE_BUFS; ++i) {
+        h->state[i] = h->dalloc<float>(nv, true);
+        if (!h->state[i]) return fail("out of device memory for sampler state");
+    }
+    h->coef_cap = 4096;
+    h->coef_tab = h->dalloc<float>((size_t)h->coef_cap * 8, true);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return fail("finalize: %s", cudaGetErrorString(e));
+    for (auto& b : h->bufs) if (!b.ptr) return fail("out of device memory for activations");
+    h->weights.clear();
+    h->finalized = true;
+    return 0;
+}
+
+int64_t cd_unet_workspace_bytes(const cd_unet* h) { return h ? h->workspace_bytes : 0; }
+int64_t cd_unet_launch_count(const cd_unet* h) { return h ? h->launches : 0; }
+
+int cd_level_shape(const cd_unet* h, int level, int* zpr) {
+    if (!h || level < 0 || level >= h->n_levels) return fail("bad level");
+    zpr[0] = h->geom[level].Z; zpr[1] = h->geom[level].P; zpr[2] = h->geom[level].R;
+    return 0;
+}
+
+static int check_call(cd_unet* h, int B) {
+    if (!h) return fail("null handle");
+    if (!h->finalized) return fail("cd_unet_finalize has not been called");
+    if (B < 1 || B > h->d.max_batch) return fail("batch %d outside [1, max_batch=%d]", B, h->d.max_batch);
+    return 0;
+}
+
+int cd_unet_forward(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev, float* pred_dev, int B,
+                    void* stream) {
+    if (check_call(h, B)) return 1;
+    Run r;
+    memset(&r.fin, 0, sizeof(r.fin));
+    r.B = B; r.st = (cudaStream_t)stream; r.x = x_dev; r.sigma = sigma_dev; r.sigma_stride = 1; r.cond = cond_dev;
+    r.scale_input = 0;
+    r.fin.pred_out = pred_dev;
+    return run_forward(h, r);
+}
+
+int cd_denoise(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev, float* x0_dev, int B, void* stream) {
+    if (check_call(h, B)) return 1;
+    Run r;
+    memset(&r.fin, 0, sizeof(r.fin));
+    r.B = B; r.st = (cudaStream_t)stream; r.x = x_dev; r.sigma = sigma_dev; r.sigma_stride = 1; r.cond = cond_dev;
+    r.scale_input = 1;
+    r.fin.x0_out = x0_dev;
+    return run_forward(h, r);
+}
+
+int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t seed, int shower_offset, int slot, void* stream) {
+    if (cd_device_check()) return 1;
+    launch_fill_normal(out_dev, n_showers * voxels, (int)voxels, seed, shower_offset, slot, (cudaStream_t)stream);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("fill_normal: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+}  // extern "C"
+
+// -------------------------------------------------------------------------------------------------
+// sampling loop
+// -------------------------------------------------------------------------------------------------
+namespace cd {
+
+struct SampleArgs {
+    const float* start; float start_scale; const float* cond; const cd_eval* evals; int n_evals;
+    const float* bank; uint64_t seed; int shower_offset; int final_buf; float* x_final; float* xs; float* x0s; int B;
+};
+
+static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
+    const int V = h->d.Z * h->d.P * h->d.R;
+    const long long n = (long long)a.B * V;
+    const size_t bytes = (size_t)n * sizeof(float);
+    float* tab = h->coef_tab;
+    // buf[0] = start * start_scale  (row n_evals of the table holds [start_scale, 0])
+    launch_axpby(a.start, nullptr, h->state[0], tab + (size_t)a.n_evals * 8, n, V, a.seed, a.shower_offset, 0, 0, st);
+    h->launches += 1;
+    for (int i = 0; i < a.n_evals; ++i) {
+        const cd_eval& e = a.evals[i];
+        float* row = tab + (size_t)i * 8;
+        if (e.pre_b != 0.f) {
+            const float* nz = a.bank ? a.bank + (size_t)e.pre_noise_index * n : nullptr;
+            launch_axpby(h->state[e.x_in], nz, h->state[e.x_in], row + 6, n, V, a.seed, a.shower_offset, e.pre_noise_index, 1, st);
+            h->launches += 1;
+        }
+        Run r;
+        memset(&r.fin, 0, sizeof(r.fin));
+        r.B = a.B; r.st = st; r.x = h->state[e.x_in]; r.sigma = row; r.sigma_stride = 0; r.cond = a.cond; r.scale_input = 1;
+        float* x0_dst = nullptr;
+        if (e.x0_buf >= 0) x0_dst = h->state[e.x0_buf];
+        else if (e.rec_x0 >= 0 && a.x0s) x0_dst = a.x0s + (size_t)e.rec_x0 * n;
+        r.fin.x0_out = x0_dst;
+        if (e.x_out >= 0) {
+            r.fin.x_out = h->state[e.x_out];
+            r.fin.coef = row + 1;
+            if (e.a1 >= 0) r.fin.a1 = h->state[e.a1];
+            else if (e.a1 == -2) {
+                if (a.bank) r.fin.a1 = a.bank + (size_t)e.noise_index * n;
+                else { r.fin.rng_enabled = 1; r.fin.seed = a.seed; r.fin.shower_offset = a.shower_offset; r.fin.step = e.noise_index; }
+            }
+            if (e.a2 >= 0) r.fin.a2 = h->state[e.a2];
+            if (e.a3 >= 0) r.fin.a3 = h->state[e.a3];
+        }
+        if (run_forward(h, r)) return 1;
+        if (e.x0_buf >= 0 && e.rec_x0 >= 0 && a.x0s)
+            cudaMemcpyAsync(a.x0s + (size_t)e.rec_x0 * n, h->state[e.x0_buf], bytes, cudaMemcpyDeviceToDevice, st);
+        if (e.rec_x >= 0 && a.xs)
+            cudaMemcpyAsync(a.xs + (size_t)e.rec_x * n, h->state[e.rec_x_buf], bytes, cudaMemcpyDeviceToDevice, st);
+    }
+    cudaMemcpyAsync(a.x_final, h->state[a.final_buf], bytes, cudaMemcpyDeviceToDevice, st);
+    cudaError_t err = cudaPeekAtLastError();
+    if (err != cudaSuccess) return fail("sample enqueue: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+}  // namespace cd
+
+extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_scale, const float* cond_dev, const cd_eval* evals,
+                             int n_evals, const float* noise_bank_dev, uint64_t seed, int shower_offset, int final_buf,
+                             float* x_final_dev, float* xs_dev, float* x0s_dev, int B, void* stream, int use_graph) {
+    if (check_call(h, B)) return 1;
+    if (n_evals < 1 || n_evals + 1 > h->coef_cap) return fail("n_evals %d outside [1, %d]", n_evals, h->coef_cap - 1);
+    if (final_buf < 0 || final_buf >= CD_NUM_STATE_BUFS) return fail("bad final_buf");
+    for (int i = 0; i < n_evals; ++i) {
+        const cd_eval& e = evals[i];
+        auto okb = [](int b, int lo) { return b >= lo && b < CD_NUM_STATE_BUFS; };
+        if (!okb(e.x_in, 0) || !okb(e.x_out, -1) || !okb(e.x0_buf, -1) || !okb(e.a1, -2) || !okb(e.a2, -1) || !okb(e.a3, -1) ||
+            (e.rec_x >= 0 && !okb(e.rec_x_buf, 0)))
+            return fail("eval %d references a state buffer outside [0,%d)", i, CD_NUM_STATE_BUFS);
+        if (!(e.sigma > 0.f)) return fail("eval %d: sigma must be > 0 (got %g)", i, (double)e.sigma);  // sample.py:166-167
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<float> tab((size_t)(n_evals + 1) * 8, 0.f);
+    for (int i = 0; i < n_evals; ++i) {
+        float* row = &tab[(size_t)i * 8];
+        row[0] = evals[i].sigma;
+        for (int j = 0; j < 5; ++j) row[1 + j] = evals[i].k[j];
+        row[6] = evals[i].pre_a; row[7] = evals[i].pre_b;
+    }
+    tab[(size_t)n_evals * 8] = start_scale;
+    CD_CUDA(cudaMemcpyAsync(h->coef_tab, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+    SampleArgs a{start_dev, start_scale, cond_dev, evals, n_evals, noise_bank_dev, seed, shower_offset, final_buf,
+                 x_final_dev, xs_dev, x0s_dev, B};
+    if (!use_graph) return enqueue_sample(h, a, st);
+
+    // key: everything baked into the graph (structure + pointers); numeric schedule values live in coef_tab
+    std::vector<unsigned char> key;
+    auto put = [&key](const void* p, size_t n) { const unsigned char* c = (const unsigned char*)p; key.insert(key.end(), c, c + n); };
+    put(&start_dev, sizeof(void*)); put(&cond_dev, sizeof(void*)); put(&noise_bank_dev, sizeof(void*));
+    put(&x_final_dev, sizeof(void*)); put(&xs_dev, sizeof(void*)); put(&x0s_dev, sizeof(void*));
+    put(&seed, sizeof(seed)); put(&shower_offset, sizeof(int)); put(&final_buf, sizeof(int)); put(&B, sizeof(int));
+    put(&h->conv_backend, sizeof(int));
+    for (int i = 0; i < n_evals; ++i) {
+        const cd_eval& e = evals[i];
+        int s[12] = {e.x_in, e.x_out, e.x0_buf, e.a1, e.a2, e.a3, e.noise_index, e.pre_b != 0.f, e.pre_noise_index, e.rec_x0, e.rec_x, e.rec_x_buf};
+        put(s, sizeof(s));
+    }
+    if (!h->graph_exec || key != h->graph_key) {
+        if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; }
+        h->graph_key.clear();
+        int64_t before = h->launches;
+        CD_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_sample(h, a, st);
+        cudaGraph_t graph = nullptr;
+        cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        h->graph_nodes = h->launches - before;
+        h->launches = before;
+        if (rc) { if (graph) cudaGraphDestroy(graph); return 1; }
+        if (ce != cudaSuccess) return fail("graph capture failed: %s", cudaGetErrorString(ce));
+        ce = cudaGraphInstantiate(&h->graph_exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) { h->graph_exec = nullptr; return fail("graph instantiate failed: %s", cudaGetErrorString(ce)); }
+        h->graph_key = key;
+    }
+    CD_CUDA(cudaGraphLaunch(h->graph_exec, st));
+    h->launches += h->graph_nodes;
+    return 0;
+}
+
+// -------------------------------------------------------------------------------------------------
+// test hook: one convolution in isolation, dense fp32 in/out
+// -------------------------------------------------------------------------------------------------
+extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize, const int* stride,
+                            int transposed, const float* w_host, const float* bias_host, const float* x_dev, float* y_dev,
+                            int B, int backend, void* stream) {
+    if (check_call(h, B)) return 1;
+    if (level_in < 0 || level_in >= h->n_levels || level_out < 0 || level_out >= h->n_levels) return fail("bad level");
+    if (Cin % 8 || Cout % 8) return fail("channels must be multiples of 8");
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geom& gi = h->geom[level_in];
+    const Geom& go = h->geom[level_out];
+    HostTensor wt;
+    int taps = ksize[0] * ksize[1] * ksize[2];
+    wt.shape = {transposed ? Cin : Cout, transposed ? Cout : Cin, ksize[0], ksize[1], ksize[2]};
+    wt.data.assign(w_host, w_host + (size_t)Cin * Cout * taps);
+    h->weights["__test.w"] = wt;
+    if (bias_host) {
+        HostTensor bt;
+        bt.shape = {Cout};
+        bt.data.assign(bias_host, bias_host + Cout);
+        h->weights["__test.b"] = bt;
+    }
+    ConvW cw;
+    bool okp = pack_conv(h, "__test.w", bias_host ? "__test.b" : "", Cin, Cin, Cout, ksize[0], ksize[1], ksize[2], transposed, true, &cw);
+    h->weights.clear();
+    if (!okp) return 1;
+    __half *xin = nullptr, *yout = nullptr;
+    size_t nin = (size_t)(Cin / 8) * gi.chunk_stride * 8, nout = (size_t)(Cout / 8) * go.chunk_stride * 8;
+    CD_CUDA(cudaMalloc(&xin, nin * sizeof(__half)));
+    CD_CUDA(cudaMalloc(&yout, nout * sizeof(__half)));
+    cudaMemsetAsync(xin, 0, nin * sizeof(__half), st);
+    cudaMemsetAsync(yout, 0, nout * sizeof(__half), st);
+    long long nrows = (long long)B * gi.rows_per_sample;
+    dense_to_plcp_kernel<<<(unsigned)((nrows + 127) / 128), 128, 0, st>>>(gi, x_dev, xin, Cin, nrows);
+    ConvParams p;
+    p.gin = gi; p.gout = go; p.nsrc = 1; p.Cin_total = Cin;
+    p.src[0].base = xin; p.src[0].C = Cin; p.src[1].base = nullptr; p.src[1].C = 0;
+    p.dst = yout; p.Cout = Cout; p.w = cw.w; p.bias = cw.bias;
+    p.kz = ksize[0]; p.kp = ksize[1]; p.kr = ksize[2];
+    p.sz = stride[0]; p.sp = stride[1]; p.sr = stride[2];
+    bool is1 = taps == 1;
+    p.pz = is1 ? 0 : 1; p.cp = is1 ? 0 : 1; p.pr = is1 ? 0 : 1;
+    p.transposed = transposed; p.write_halo = 0; p.stats = nullptr; p.B = B;
+    int rc = 0;
+    if (backend == 0) {
+        if (!cw.wmma || launch_conv_mma(p, cw.wmma, st) != 0) rc = fail("tcgen05 conv does not support this shape");
+    } else {
+        launch_conv_generic(p, st);
+    }
+    long long nvox = (long long)B * go.Z * go.P * go.R;
+    if (!rc) plcp_to_dense_kernel<<<(unsigned)((nvox + 127) / 128), 128, 0, st>>>(go, yout, y_dev, Cout, nvox);
+    cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(xin); cudaFree(yout);
+    if (e != cudaSuccess) return fail("test conv: %s", cudaGetErrorString(e));
+    return rc;
+}

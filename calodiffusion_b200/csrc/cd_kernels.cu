@@ -20,7 +20,7 @@ __global__ void prep_input_kernel(Geom g, const float* __restrict__ x, const flo
         if (p < 0) p += g.P;
         if (p >= g.P) p -= g.P;
         float s = sigma[(long long)ri.b * sigma_stride];
-        float c_in = rsqrtf(s * s + sigma_data * sigma_data);
+        float c_in = sigma_data > 0.f ? rsqrtf(s * s + sigma_data * sigma_data) : 1.f;
         long long vox = (((long long)ri.b * g.Z + ri.z) * g.P + p) * g.R + ri.rr;
         f[0] = x[vox] * c_in;
         int c = 1;
@@ -589,7 +589,7 @@ __global__ void final_kernel(FinalParams p, long long nvox) {
     float sd = p.sigma_data;
     float den = s * s + sd * sd;
     float xin = p.x[v];
-    float x0 = (sd * sd / den) * xin + (s * sd * rsqrtf(den)) * pred;
+    float x0 = sd > 0.f ? (sd * sd / den) * xin + (s * sd * rsqrtf(den)) * pred : pred;
     if (p.pred_out) p.pred_out[v] = pred;
     if (p.x0_out) p.x0_out[v] = x0;
     if (p.x_out) {

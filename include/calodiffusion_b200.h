@@ -1,0 +1,118 @@
+/* calodiffusion_b200 — C ABI of the B200-native CaloDiffusion denoiser / sampling-loop library.
+ *
+ * Drop-in boundary for the one hot path of OzAmram/CaloDiffusion: the U-Net denoiser evaluated at
+ * every step of the reverse-diffusion sampling loop.  Plain pointers and sizes only; device pointers
+ * are CUDA device addresses on the current device, `stream` is a cudaStream_t passed as void*.
+ * All int-returning functions return 0 on success, non-zero on failure; cd_last_error() describes
+ * the failure.  There is no CPU fallback: every compute entry point fails if no sm_100 device exists.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo, calodiffusion/):
+ *   cd_unet_create / cd_unet_set_weight / cd_unet_finalize
+ *        -> CaloDiffusion.init_model (models/calodiffusion.py:39-81) + CondUnet.__init__
+ *           (models/models.py:523-699) + load_state_dict (models/calodiffusion.py:31-37)
+ *   cd_unet_forward  -> CaloDiffusion.forward (models/calodiffusion.py:86-98) = add_RZPhi + CondUnet.forward
+ *           (models/models.py:701-748)
+ *   cd_denoise       -> CaloDiffusion.denoise / __call__ (models/calodiffusion.py:154-173) with
+ *           Loss.get_scaling (models/loss.py:29-41) and do_time_embed (models/calodiffusion.py:144-152)
+ *   cd_sample_run    -> the per-step loops of DDim/DDPM.__call__ (models/sample.py:41-109) and
+ *           EDMAbstract.for_loop + Euler/Heun.in_loop_sampler (models/sample.py:631-662, 784-821),
+ *           expressed as a table of evaluations (see cd_eval) built by the host-side sampler classes
+ *   cd_fill_normal   -> Diffusion.noise_generation (models/diffusion.py:58-61)
+ */
+#ifndef CALODIFFUSION_B200_H
+#define CALODIFFUSION_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CD_MAX_LEVELS 4
+
+typedef struct cd_unet cd_unet; /* opaque handle: one model on one device */
+
+typedef struct cd_unet_desc {
+    int Z, P, R;                 /* SHAPE_FINAL[2:5] */
+    int n_sizes;                 /* len(LAYER_SIZE_UNET) (= levels + 1), <= CD_MAX_LEVELS + 1 */
+    int layer_sizes[CD_MAX_LEVELS + 1];
+    int in_channels;             /* 1 + 2*R_Z_INPUT + PHI_INPUT */
+    int rz_input, phi_input;
+    int cond_size;               /* width of the conditioning vector E||layers */
+    int cond_dim;                /* COND_SIZE_UNET */
+    int groups;                  /* BLOCK_GROUPS (default 8) */
+    int dataset_num;             /* DATASET_NUM: selects the R bin centres */
+    int time_embed;              /* 0 = 'sigma', 1 = 'log' (TIME_EMBED) */
+    float sigma_data;            /* 1.0 if 'log' in NOISE_SCHED else 0.5 (models/loss.py:16-25) */
+    int max_batch;               /* largest batch a single call will carry */
+    float r_centres[64];         /* scaled R bin centres (R values), utils/utils.py:134-150 */
+} cd_unet_desc;
+
+/* One denoiser evaluation inside a sampling loop plus the fused state update that follows it:
+ *   [optional]  buf[x_in] = pre_a*buf[x_in] + pre_b*noise(pre_noise_index)
+ *   x0 = denoise(buf[x_in], sigma)
+ *   [optional]  buf[x0_buf] = x0
+ *   [optional]  buf[x_out] = k0*x0 + k1*buf[x_in] + k2*A1 + k3*buf[a2] + k4*buf[a3]
+ * A1 is buf[a1] if a1 >= 0, noise slot `noise_index` if a1 == -2, absent if a1 == -1.
+ * Noise comes from the caller's bank (noise_bank != NULL: slot i = bank + i*B*voxels) or from the
+ * in-kernel Philox generator keyed by (seed, shower index, slot, voxel). */
+typedef struct cd_eval {
+    float sigma;
+    int x_in, x_out, x0_buf;
+    float k[5];
+    int a1, a2, a3;
+    int noise_index;
+    float pre_a, pre_b;
+    int pre_noise_index;
+    int rec_x0;    /* >= 0: also copy x0 to x0s[rec_x0] */
+    int rec_x;     /* >= 0: copy a state buffer to xs[rec_x] ... */
+    int rec_x_buf; /* ... this buffer, after the update */
+} cd_eval;
+
+#define CD_NUM_STATE_BUFS 4
+
+const char* cd_last_error(void);
+int cd_version(void);
+/* 0 if a usable sm_100 device is current, else non-zero (and cd_last_error says why) */
+int cd_device_check(void);
+
+cd_unet* cd_unet_create(const cd_unet_desc* desc);
+void cd_unet_destroy(cd_unet* h);
+/* fp32 host tensor under its reference state-dict name (e.g. "model.downs.0.0.block1.proj.conv.weight") */
+int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, const int64_t* shape, int ndim);
+/* validates that every tensor of the topology was supplied, packs weights, allocates workspaces */
+int cd_unet_finalize(cd_unet* h);
+/* options: "conv_backend" 0 = tcgen05 implicit GEMM where supported (default), 1 = generic SIMT everywhere */
+int cd_unet_set_option(cd_unet* h, const char* key, int value);
+int64_t cd_unet_workspace_bytes(const cd_unet* h);
+/* number of kernel launches issued by this handle since creation (graph replays count their nodes) */
+int64_t cd_unet_launch_count(const cd_unet* h);
+
+/* pred = CondUnet(add_RZPhi(x), cond, time=f(sigma)); x is used as given (no c_in scaling) */
+int cd_unet_forward(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev,
+                    float* pred_dev, int B, void* stream);
+/* x0 = c_skip*x + c_out*CondUnet(c_in*x, ...); sigma_dev holds B values */
+int cd_denoise(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev,
+               float* x0_dev, int B, void* stream);
+/* buf[0] = start*start_scale, then the evaluations in order; x_final = buf[final_buf].
+ * xs / x0s (optional, device) receive the per-step records.  use_graph: 0 eager launches,
+ * 1 the whole loop captured and replayed as one CUDA graph (cached while the arguments repeat). */
+int cd_sample_run(cd_unet* h, const float* start_dev, float start_scale, const float* cond_dev,
+                  const cd_eval* evals, int n_evals, const float* noise_bank_dev, uint64_t seed,
+                  int shower_offset, int final_buf, float* x_final_dev, float* xs_dev, float* x0s_dev,
+                  int B, void* stream, int use_graph);
+/* out[b][v] = N(0,1) from the library's Philox stream (slot = `slot`) */
+int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t seed, int shower_offset,
+                   int slot, void* stream);
+
+/* test hooks: one layer in isolation on PLCP tensors held by the handle (used by tests/ only) */
+int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,
+                 const int* stride, int transposed, const float* w_host, const float* bias_host,
+                 const float* x_dev /* (B,Cin,Z,P,R) fp32 */, float* y_dev /* (B,Cout,Zo,Po,Ro) fp32 */,
+                 int B, int backend, void* stream);
+int cd_level_shape(const cd_unet* h, int level, int* zpr /* [3] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
