@@ -8,5 +8,5 @@ nvcc $FLAGS -c cd_kernels.cu -o cd_kernels.o &
 nvcc $FLAGS -c cd_conv_mma.cu -o cd_conv_mma.o &
 nvcc $FLAGS -c cd_engine.cu -o cd_engine.o &
 wait
-nvcc -shared -gencode arch=compute_100a,code=sm_100a -o $OUT cd_kernels.o cd_conv_mma.o cd_engine.o -lcudart
+nvcc -shared -gencode arch=compute_100a,code=sm_100a -Xlinker --no-undefined -o $OUT cd_kernels.o cd_conv_mma.o cd_engine.o -lcudart
 echo built $OUT

@@ -50,6 +50,7 @@ struct Run {  // per-call state
     int sigma_stride;
     const float* cond;     // (B, cond_size)
     int scale_input;       // 1: multiply x by c_in (denoise); 0: raw forward
+    int time_is_raw;       // 1: `sigma` already holds the embedded time value (CaloDiffusion.forward's `time`)
     FinalParams fin;       // output routing of the final kernel
 };
 
@@ -363,7 +364,9 @@ static int build_plan(cd_unet* h) {
     }
     h->addvec_stride = 0;
     h->ops.push_back([h](Run& r) {
-        launch_embed(h->embed, r.sigma, r.sigma_stride, r.cond, h->addvec, r.B, r.st);
+        EmbedParams ep = h->embed;
+        if (r.time_is_raw) ep.time_mode = 2;
+        launch_embed(ep, r.sigma, r.sigma_stride, r.cond, h->addvec, r.B, r.st);
         h->launches += 1;
     });
 
@@ -631,13 +634,13 @@ static int check_call(cd_unet* h, int B) {
     return 0;
 }
 
-int cd_unet_forward(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev, float* pred_dev, int B,
+int cd_unet_forward(cd_unet* h, const float* x_dev, const float* time_dev, const float* cond_dev, float* pred_dev, int B,
                     void* stream) {
     if (check_call(h, B)) return 1;
     Run r;
     memset(&r.fin, 0, sizeof(r.fin));
-    r.B = B; r.st = (cudaStream_t)stream; r.x = x_dev; r.sigma = sigma_dev; r.sigma_stride = 1; r.cond = cond_dev;
-    r.scale_input = 0;
+    r.B = B; r.st = (cudaStream_t)stream; r.x = x_dev; r.sigma = time_dev; r.sigma_stride = 1; r.cond = cond_dev;
+    r.scale_input = 0; r.time_is_raw = 1;
     r.fin.pred_out = pred_dev;
     return run_forward(h, r);
 }
@@ -647,7 +650,7 @@ int cd_denoise(cd_unet* h, const float* x_dev, const float* sigma_dev, const flo
     Run r;
     memset(&r.fin, 0, sizeof(r.fin));
     r.B = B; r.st = (cudaStream_t)stream; r.x = x_dev; r.sigma = sigma_dev; r.sigma_stride = 1; r.cond = cond_dev;
-    r.scale_input = 1;
+    r.scale_input = 1; r.time_is_raw = 0;
     r.fin.x0_out = x0_dev;
     return run_forward(h, r);
 }
@@ -690,7 +693,7 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
         }
         Run r;
         memset(&r.fin, 0, sizeof(r.fin));
-        r.B = a.B; r.st = st; r.x = h->state[e.x_in]; r.sigma = row; r.sigma_stride = 0; r.cond = a.cond; r.scale_input = 1;
+        r.B = a.B; r.st = st; r.x = h->state[e.x_in]; r.sigma = row; r.sigma_stride = 0; r.cond = a.cond; r.scale_input = 1; r.time_is_raw = 0;
         float* x0_dst = nullptr;
         if (e.x0_buf >= 0) x0_dst = h->state[e.x0_buf];
         else if (e.rec_x0 >= 0 && a.x0s) x0_dst = a.x0s + (size_t)e.rec_x0 * n;

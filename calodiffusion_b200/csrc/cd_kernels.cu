@@ -501,7 +501,7 @@ __global__ void __launch_bounds__(128) embed_kernel(EmbedParams p, const float* 
     int half_dim = p.cond_dim / 2;
     if (threadIdx.x == 0) {
         float s = sigma[(long long)b * sigma_stride];
-        buf0[0] = (p.time_mode == 0) ? s / sqrtf(1.f + s * s) : 0.5f * logf(s);
+        buf0[0] = (p.time_mode == 0) ? s / sqrtf(1.f + s * s) : (p.time_mode == 1 ? 0.5f * logf(s) : s);
     }
     __syncthreads();
     dense_layer(p.tw[0], p.tb[0], buf0, buf1, 1, half_dim / 2, 1);
@@ -627,7 +627,7 @@ __global__ void axpby_kernel(const float* __restrict__ x, const float* __restric
     out[v] = o;
 }
 
-void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps, uint64_t seed,
+void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps, unsigned long long seed,
                   int shower_offset, int step, int rng_enabled, cudaStream_t st) {
     axpby_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, noise, out, coef, n, vps, seed, shower_offset, step,
                                                               rng_enabled);
@@ -639,7 +639,7 @@ __global__ void fill_normal_kernel(float* out, long long n, int vps, uint64_t se
     int b = (int)(v / vps);
     out[v] = philox_normal(seed, (uint32_t)(shower_offset + b), (uint32_t)step, (uint32_t)(v - (long long)b * vps));
 }
-void launch_fill_normal(float* out, long long n, int vps, uint64_t seed, int shower_offset, int step, cudaStream_t st) {
+void launch_fill_normal(float* out, long long n, int vps, unsigned long long seed, int shower_offset, int step, cudaStream_t st) {
     fill_normal_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n, vps, seed, shower_offset, step);
 }
 

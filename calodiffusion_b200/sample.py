@@ -1,0 +1,175 @@
+"""Sampler registry mirror (models/sample.py).  Same class names, constructor `(config)`, `SAMPLER_OPTIONS`
+keys and `__call__(model, start, energy, layers, num_steps, sample_offset, debug) -> (x, xs, x0s)`.
+
+Each sampler turns its schedule into a table of `cd_eval` records (include/calodiffusion_b200.h) — one per
+denoiser evaluation, carrying the coefficients of the state update that the CUDA library fuses into the
+final-conv epilogue — and hands the whole N-step loop to `model.run_program`, which replays it as one
+CUDA graph.  Schedules are computed with the same fp32 torch expressions as the reference.
+
+Noise: the reference draws `torch.randn` every step.  Here the per-step noise comes from the in-kernel
+Philox generator (seeded from torch's global RNG, keyed by global shower index so results do not depend
+on the batch sharding) or, when `sampler.noise_bank` is set (parity tests), from that tensor
+(slot i = the reference's i-th draw).
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+from .loss import cosine_beta_schedule
+
+
+def _eval(**kw):
+    e = _lib.Eval()
+    e.x_out = e.x0_buf = e.a1 = e.a2 = e.a3 = -1
+    e.rec_x0 = e.rec_x = -1
+    e.pre_a = 1.0
+    for k, v in kw.items():
+        if k == "k":
+            for i, c in enumerate(v):
+                e.k[i] = float(c)
+        else:
+            setattr(e, k, v)
+    return e
+
+
+class Sample:
+    def __init__(self, config):
+        self.config = config
+        self.sample_config = self.config.get("SAMPLER_OPTIONS", {})
+        self.noise_bank = None      # optional (n_draws, B, ...) tensor replacing the RNG (parity tests)
+        self.shower_offset = 0      # global index of the first shower of this batch (multi-GPU sharding)
+
+    def _seed(self):
+        return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        raise NotImplementedError
+
+
+class DDim(Sample):
+    """models/sample.py:29-109 (eta = 0)."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        self.ddim_eta = 0.0
+
+    @torch.no_grad()
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        betas = cosine_beta_schedule(num_steps)
+        alphas_cumprod = torch.cumprod(1.0 - betas, dim=0)
+        alphas_cumprod_prev = torch.nn.functional.pad(alphas_cumprod[:-1], (1, 0), value=1.0)
+        sqrt_ac = torch.sqrt(alphas_cumprod)
+        sqrt_1m = torch.sqrt(1.0 - alphas_cumprod)
+        time_steps = torch.flip(torch.arange(num_steps), [0])
+        if sample_offset > 0:
+            time_steps = time_steps[sample_offset:]
+        sigma_start = float(sqrt_1m[time_steps[0]] / sqrt_ac[time_steps[0]])
+        evals = []
+        for i, t in enumerate(time_steps.tolist()):
+            alpha, alpha_prev = alphas_cumprod[t], alphas_cumprod_prev[t]
+            denom = sqrt_ac[max(t - 1, 0)]
+            sigma = sqrt_1m[t] / sqrt_ac[t]
+            ddim_sigma = self.ddim_eta * (((1 - alpha_prev) / (1 - alpha)) * (1 - alpha / alpha_prev)) ** 0.5
+            sigma_prev = (1.0 - alpha_prev - ddim_sigma ** 2).sqrt() / denom
+            a = float(sigma_prev / sigma) if t > 0 else 0.0          # mask * sigma_prev / sigma
+            ns = float(ddim_sigma / denom)
+            # x = x0 + a*(x - x0) + ns*noise
+            evals.append(_eval(sigma=float(sigma), x_in=0, x_out=0, k=(1.0 - a, a, ns, 0, 0), a1=-2, noise_index=i,
+                               rec_x0=i if debug else -1, rec_x=i if debug else -1, rec_x_buf=0))
+        n = len(evals)
+        x, xs, x0s = model.run_program(start, energy, layers, evals, sigma_start, 0, noise_bank=self.noise_bank,
+                                       seed=self._seed(), shower_offset=self.shower_offset,
+                                       n_rec_x=n if debug else 0, n_rec_x0=n if debug else 0)
+        return x, (xs if debug else []), (x0s if debug else [])
+
+
+class DDPM(DDim):
+    """models/sample.py:112-121 (eta = 1)."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        self.ddim_eta = 1.0
+
+
+class EDMAbstract(Sample):
+    """models/sample.py:577-726: Karras schedule + churn loop; subclasses pick the in-loop update."""
+    order = 1
+
+    def __init__(self, config):
+        super().__init__(config)
+        noisy = self.config.get("NOISY_SAMPLE", False)
+        self.S_churn = 40 if noisy else 0
+        self.S_min = self.sample_config.get("S_MIN", 0.01)
+        self.S_max = 50 if noisy else 1
+        self.S_noise = self.sample_config.get("S_NOISE", 1.003)
+        self.sigma_min = self.sample_config.get("SIGMA_MIN", 0.002)
+        self.sigma_max = self.sample_config.get("SIGMA_MAX", 80.0)
+        self.orig_schedule = self.sample_config.get("ORG_SCHEDULE", False)
+        self.rho = self.sample_config.get("RHO", 7)
+        self.last_step_euler = False   # True: guarded final step (utils/sampling.py:232) instead of the reference's 1/0
+
+    def setup(self, num_steps, sample_offset):
+        if self.orig_schedule:
+            raise ValueError("ORG_SCHEDULE is not supported by the B200 backend")
+        step_indices = torch.arange(num_steps, dtype=torch.float32)
+        t_steps = (self.sigma_max ** (1 / self.rho) + step_indices / (num_steps - 1)
+                   * (self.sigma_min ** (1 / self.rho) - self.sigma_max ** (1 / self.rho))) ** self.rho
+        t_steps = torch.cat([t_steps, torch.zeros_like(t_steps[:1])])
+        return t_steps[sample_offset:]
+
+    @torch.no_grad()
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        t_steps = self.setup(num_steps, sample_offset)
+        evals = []
+        cur, other = 0, 1     # state buffers: x_cur lives in `cur`
+        n_steps = len(t_steps) - 1
+        for i in range(n_steps):
+            t_cur, t_next = t_steps[i], t_steps[i + 1]
+            gamma = min(self.S_churn / num_steps, np.sqrt(2) - 1) if self.S_min <= t_cur <= self.S_max else 0
+            t_hat = torch.as_tensor(t_cur + gamma * t_cur)
+            pre_b = float((t_hat ** 2 - t_cur ** 2).sqrt() * self.S_noise)
+            h = t_next - t_hat
+            ht = float(h / t_hat)
+            if pre_b != 0.0 and self.order == 2:
+                raise ValueError("Heun with NOISY_SAMPLE churn is not supported by the B200 backend yet")
+            common = dict(sigma=float(t_hat), x_in=cur, pre_a=1.0, pre_b=pre_b, pre_noise_index=i,
+                          rec_x0=i if debug else -1)
+            # NOTE: with churn the reference records the un-noised x_cur; records are taken only when pre_b == 0
+            if self.order == 1 or (self.last_step_euler and float(t_next) == 0.0):
+                # x_next = x_hat + h*(x_hat - D)/t_hat
+                evals.append(_eval(**common, x_out=other, k=(-ht, 1.0 + ht, 0, 0, 0),
+                                   rec_x=i if debug else -1, rec_x_buf=cur))
+                cur, other = other, cur
+            else:
+                # first evaluation: D -> buf2, x' -> buf3
+                evals.append(_eval(**common, x_out=3, x0_buf=2, k=(-ht, 1.0 + ht, 0, 0, 0)))
+                # second: D' at t' = t_hat + h ; x_next = x_hat + h*(0.5*(x_hat-D)/t_hat + 0.5*(x_cur-D')/t_next)
+                t_prime = t_hat + h
+                with np.errstate(divide="ignore"):
+                    hn = float(np.float32(0.5) * np.float32(h) / np.float32(t_next))  # inf at the last step (reference)
+                k = (-hn, 0.0, 1.0 + 0.5 * ht + hn, -0.5 * ht, 0)
+                sig2 = float(t_prime)
+                if not sig2 > 0.0:
+                    # reference evaluates the network at sigma = 0 here (log 0 / division by zero): results are
+                    # non-finite there as well; evaluate at a tiny sigma and let the inf coefficients propagate
+                    sig2 = 1e-30
+                evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=k, a1=cur, a2=2,
+                                   rec_x=i if debug else -1, rec_x_buf=cur))
+                cur, other = other, cur
+        n = n_steps
+        x, xs, x0s = model.run_program(start, energy, layers, evals, float(t_steps[0]), cur, noise_bank=self.noise_bank,
+                                       seed=self._seed(), shower_offset=self.shower_offset,
+                                       n_rec_x=n if debug else 0, n_rec_x0=n if debug else 0)
+        return x, (xs if debug else []), (x0s if debug else [])
+
+
+class Euler(EDMAbstract):
+    """models/sample.py:772-789."""
+    order = 1
+
+
+class Heun(EDMAbstract):
+    """models/sample.py:792-821 — including its use of x_cur in d' (:820) and the unguarded last step."""
+    order = 2

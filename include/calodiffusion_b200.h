@@ -88,8 +88,8 @@ int64_t cd_unet_workspace_bytes(const cd_unet* h);
 /* number of kernel launches issued by this handle since creation (graph replays count their nodes) */
 int64_t cd_unet_launch_count(const cd_unet* h);
 
-/* pred = CondUnet(add_RZPhi(x), cond, time=f(sigma)); x is used as given (no c_in scaling) */
-int cd_unet_forward(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev,
+/* pred = CondUnet(add_RZPhi(x), cond, time); x and time (B values, already embedded) are used as given */
+int cd_unet_forward(cd_unet* h, const float* x_dev, const float* time_dev, const float* cond_dev,
                     float* pred_dev, int B, void* stream);
 /* x0 = c_skip*x + c_out*CondUnet(c_in*x, ...); sigma_dev holds B values */
 int cd_denoise(cd_unet* h, const float* x_dev, const float* sigma_dev, const float* cond_dev,
