@@ -242,7 +242,7 @@ struct Builder {
 
     // GroupNorm finalize + apply:  dst = act(GN(src)) + addvec + residual   (all rows incl. halos)
     void gn(const std::string& gname, const std::string& bname, int level, int src, int dst, int C, int groups, long long stats_off,
-            int act, int addvec_off /* -1 none */, int residual /* -1 none */) {
+            int act, int addvec_off /* -1 none */, int residual /* -1 none */, int residual2 = -1) {
         cd_unet* hh = h;
         float* gamma = upload_vec(hh, gname, C);
         float* beta = upload_vec(hh, bname, C);
@@ -253,7 +253,8 @@ struct Builder {
             double cnt = (double)g.Z * g.P * g.R;
             launch_gn_finalize((const double*)(hh->scratch + (size_t)stats_off * r.B), gamma, beta, affine, r.B, C, groups, cnt, r.st);
             launch_gn_apply(g, hh->bufs[src].ptr, affine, addvec_off >= 0 ? hh->addvec + addvec_off : nullptr, hh->addvec_stride,
-                            residual >= 0 ? hh->bufs[residual].ptr : nullptr, hh->bufs[dst].ptr, C, act, r.B, r.st);
+                            residual >= 0 ? hh->bufs[residual].ptr : nullptr, residual2 >= 0 ? hh->bufs[residual2].ptr : nullptr,
+                            residual >= 0 ? hh->bufs[residual].C / 8 : 0, hh->bufs[dst].ptr, C, act, r.B, r.st);
             hh->launches += 2;
         });
     }
@@ -267,7 +268,7 @@ struct Builder {
             ok = false; return -1;
         }
         bool has_res = find_w(h, pre + "res_conv.conv.weight") != nullptr;
-        if (!has_res && (Cin != Cout || srcs.size() != 1)) { fail("missing weight %sres_conv.conv.weight", pre.c_str()); ok = false; return -1; }
+        if (!has_res && Cin != Cout) { fail("missing weight %sres_conv.conv.weight", pre.c_str()); ok = false; return -1; }
         if (has_res && !pack_conv(h, pre + "res_conv.conv.weight", pre + "res_conv.conv.bias", Cin, Cin, Cout, 1, 1, 1, 0, true, &cres)) {
             ok = false; return -1;
         }
@@ -298,7 +299,8 @@ struct Builder {
             res = rbuf;
         }
         // hbuf is free again as the destination: gn_apply reads t1 + residual only
-        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res);
+        int res2 = (!has_res && srcs.size() == 2) ? srcs[1] : -1;  // identity residual over a concatenated input
+        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res, res2);
         release(h, t1);
         if (rbuf >= 0) release(h, rbuf);
         return hbuf;

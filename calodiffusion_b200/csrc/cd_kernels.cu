@@ -215,6 +215,7 @@ void launch_gn_finalize(const double* stats, const float* gamma, const float* be
 // residual (:200), PreNorm (:327-329) and Residual(to_out GN) (:117,:293).
 __global__ void gn_apply_kernel(Geom g, const __half* __restrict__ src, const float2* __restrict__ affine,
                                 const float* __restrict__ addvec, int addvec_stride, const __half* __restrict__ residual,
+                                const __half* __restrict__ residual2, int res_split,
                                 __half* __restrict__ dst, int C, int act, long long nrows) {
     long long row = (long long)blockIdx.x * 32 + threadIdx.x;
     int k = threadIdx.y + blockIdx.y * blockDim.y;
@@ -238,7 +239,9 @@ __global__ void gn_apply_kernel(Geom g, const __half* __restrict__ src, const fl
             for (int j = 0; j < 8; ++j) f[j] += av[j];
         }
         if (residual) {
-            Half8 rv = *reinterpret_cast<const Half8*>(residual + plcp_offset(g, k, ri.src));
+            // the residual may be the channel concatenation of two tensors (torch.cat skip, models.py:741)
+            const __half* rb = (k < res_split) ? residual + plcp_offset(g, k, ri.src) : residual2 + plcp_offset(g, k - res_split, ri.src);
+            Half8 rv = *reinterpret_cast<const Half8*>(rb);
             float r[8];
             unpack8(rv, r);
 #pragma unroll
@@ -249,13 +252,15 @@ __global__ void gn_apply_kernel(Geom g, const __half* __restrict__ src, const fl
 }
 
 void launch_gn_apply(const Geom& g, const __half* src, const float2* affine, const float* addvec, int addvec_stride,
-                     const __half* residual, __half* dst, int C, int act, int B, cudaStream_t st) {
+                     const __half* residual, const __half* residual2, int res_split, __half* dst, int C, int act, int B,
+                     cudaStream_t st) {
     long long nrows = (long long)B * g.rows_per_sample;
     int chunks = C >> 3;
     int by = chunks < 8 ? chunks : 8;
     dim3 block(32, by);
     dim3 grid((unsigned)((nrows + 31) / 32), (chunks + by - 1) / by);
-    gn_apply_kernel<<<grid, block, 0, st>>>(g, src, affine, addvec, addvec_stride, residual, dst, C, act, nrows);
+    gn_apply_kernel<<<grid, block, 0, st>>>(g, src, affine, addvec, addvec_stride, residual, residual2,
+                                            residual2 ? res_split : (C >> 3), dst, C, act, nrows);
 }
 
 // per-(sample, channel) sum / sumsq over interior rows of an existing tensor (GroupNorm(1,C) PreNorm input)

@@ -33,7 +33,8 @@ void launch_conv_generic(const ConvParams& p, cudaStream_t st);
 void launch_gn_finalize(const double* stats, const float* gamma, const float* beta, float2* affine, int B, int C,
                         int groups, double count_per_channel, cudaStream_t st);
 void launch_gn_apply(const Geom& g, const __half* src, const float2* affine, const float* addvec, int addvec_stride,
-                     const __half* residual, __half* dst, int C, int act, int B, cudaStream_t st);
+                     const __half* residual, const __half* residual2, int res_split, __half* dst, int C, int act, int B,
+                     cudaStream_t st);
 void launch_row_stats(const Geom& g, const __half* src, double* stats, int C, int B, cudaStream_t st);
 void launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, __half* dst, int B, cudaStream_t st);
 void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, const float* cond, float* addvec, int B,

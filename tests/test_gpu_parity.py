@@ -88,6 +88,40 @@ def test_generic_conv_variants(models, case):
     assert max(errs.values()) < TOL_LAYER, errs
 
 
+@pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
+def test_tcgen05_conv_variants(models, case):
+    """The tcgen05/TMEM implicit-GEMM kernel (backend 0) vs torch fp32 on fp16-rounded operands."""
+    m, c = models(case)
+    lib = m._lib
+    errs = {}
+    errs["k3_l0_32_32"] = _conv_case(m, lib, 0, 0, 32, 32, (3, 3, 3), (1, 1, 1), False, 0)
+    errs["k3_l1_64_64"] = _conv_case(m, lib, 1, 1, 64, 64, (3, 3, 3), (1, 1, 1), False, 0)
+    errs["k3_l1_128_32"] = _conv_case(m, lib, 1, 1, 128, 32, (3, 3, 3), (1, 1, 1), False, 0)
+    errs["k3_l2_64_32"] = _conv_case(m, lib, 2, 2, 64, 32, (3, 3, 3), (1, 1, 1), False, 0)
+    errs["k3_l2_192_64"] = _conv_case(m, lib, 2, 2, 192, 64, (3, 3, 3), (1, 1, 1), False, 0)
+    errs["k1_l0_32_96"] = _conv_case(m, lib, 0, 0, 32, 96, (1, 1, 1), (1, 1, 1), False, 0)
+    errs["k1_l1_64_32"] = _conv_case(m, lib, 1, 1, 64, 32, (1, 1, 1), (1, 1, 1), False, 0)
+    print(case, {k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
+@pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
+def test_denoise_generic_backend(models, case):
+    """Same golden check with the SIMT convolution everywhere (conv_backend=1)."""
+    m, c = models(case)
+    m.set_conv_backend(1)
+    try:
+        sig = torch.from_numpy(c["gold"]["denoise_a_sigma"])
+        scale = (1 + sig.view(-1, 1, 1, 1, 1) ** 2).sqrt()
+        y = m.denoise((c["x"] * scale).cuda(), E=c["E"].cuda(), sigma=sig.cuda(),
+                      layers=None if c["layers"] is None else c["layers"].cuda())
+        e = rel_l2(y.cpu().numpy(), c["gold"]["denoise_a"])
+    finally:
+        m.set_conv_backend(0)
+    print(case, "generic-backend denoise rel-L2:", f"{e:.2e}")
+    assert e < TOL
+
+
 def _level_z(m, lev):
     z = (C.c_int * 3)()
     m._lib.cd_level_shape(m._engine(2), lev, z)
