@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""Benchmark of the CaloDiffusion sampling hot path on B200 (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload ds2|ds3] [--impl reference]
+
+A "step" is one pass of the hot path over one batch: the whole reverse-diffusion loop (BASELINE config 2:
+Dataset-2, DDPM, 400 denoiser evaluations; config 3: Dataset-3, Heun) for B showers per GPU, replayed as one
+CUDA graph.  `value` = showers/s with inputs resident in HBM; `e2e` = showers/s through the public API
+(`CaloDiffusion.sample`: pinned-host conditioning -> device, showers -> host numpy) inside the timed region.
+Synthetic conditioning/noise, random-init weights (no datasets or checkpoints offline).
+Under torchrun (N > 1) every rank samples its own B showers (weak scaling, no data-path collective) and one
+NCCL all_gather collects the showers at the end of each step, as SURVEY 8(e) prescribes.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# hot-path keys of the reference's shipped configs (configs/config_dataset{2,3}.json)
+_COMMON = dict(COND_SIZE_UNET=128, BLOCK_ATTN=True, MID_ATTN=True, COMPRESS_Z=True, CYLINDRICAL=True, R_Z_INPUT=True,
+               TRAINING_OBJ="hybrid_weight", LOSS_TYPE="l2", COND_EMBED="id", SHOWER_EMBED="", NSTEPS=400)
+WORKLOADS = {
+    "ds2": dict(
+        cfg=dict(_COMMON, DATASET_NUM=2, SHAPE_ORIG=[-1, 6480], SHAPE_PAD=[-1, 1, 45, 16, 9],
+                 SHAPE_FINAL=[-1, 1, 45, 16, 9], LAYER_SIZE_UNET=[32, 32, 64, 32], SHOWERMAP="layer-logit-norm",
+                 NOISE_SCHED="log", TIME_EMBED="log", SAMPLER="DDPM", BATCH=128),
+        name="CaloChallenge Dataset-2 (45x16x9), cylindrical U-Net, DDPM 400 steps", sampler="DDPM", steps=400,
+        evals_per_shower=400, batch=1000, n_layers=46, gflop_per_eval=5.4439),
+    "ds3": dict(
+        cfg=dict(_COMMON, DATASET_NUM=3, SHAPE_ORIG=[-1, 40500], SHAPE_PAD=[-1, 1, 45, 50, 18],
+                 SHAPE_FINAL=[-1, 1, 45, 50, 18], LAYER_SIZE_UNET=[32, 32, 32, 32], SHOWERMAP="logit-norm",
+                 NOISE_SCHED="cosine", TIME_EMBED="sigma", SAMPLER="Heun", BATCH=64),
+        name="CaloChallenge Dataset-3 (45x50x18), cylindrical U-Net, EDM Heun 50 steps", sampler="Heun", steps=50,
+        evals_per_shower=100, batch=256, n_layers=0, gflop_per_eval=30.351),
+}
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=float(p["hbm_gbs"]), tf=float(p["bf16_tflops"]), tf_sus=float(p["bf16_tflops_sustained"]),
+                    src="MEASURED_PEAKS.json")
+    except Exception:
+        return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [c.strip() for c in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def finish(self):
+        self._stop.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(int(float(r[0])) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(float(self.rows[0][1])), "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_reference_leg(wl, budget_s=12.0, batch=16):
+    """The reference's CPU algorithm for the path (oracle port: plain torch CPU fp32 ops, all host threads) on a
+    bounded sample of the same workload.  Returns (showers_per_s, cores, sample description, seconds)."""
+    import torch
+    from oracle.unet_oracle import DenoiserOracle, sample_ddim, sample_edm, synth_state_dict
+    from calodiffusion_b200.calodiffusion import unet_param_shapes
+    cfg = wl["cfg"]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    zpr = cfg["SHAPE_FINAL"][2:]
+    cond_size = 1 + wl["n_layers"]
+    shapes = {"model." + k: v for k, v in unet_param_shapes(cfg["LAYER_SIZE_UNET"], 3, cond_size, cfg["COND_SIZE_UNET"], zpr).items()}
+    sd = synth_state_dict(shapes, seed=0)
+    o = DenoiserOracle(cfg, sd)
+    g = torch.Generator().manual_seed(1)
+    E = torch.rand(batch, 1, generator=g)
+    layers = torch.randn(batch, wl["n_layers"], generator=g) if wl["n_layers"] else None
+    start = torch.randn([batch] + cfg["SHAPE_PAD"][1:], generator=torch.Generator().manual_seed(2))
+    evals_done, t_total, n = 0, 0.0, 1
+    with torch.no_grad():
+        o.denoise(start, E, torch.ones(batch), layers)   # warm-up (thread pool, allocator)
+        while t_total < budget_s and evals_done < 4096:
+            t0 = time.perf_counter()
+            if wl["sampler"] in ("DDPM", "DDim"):
+                sample_ddim(o, start, E, layers, wl["steps"], 1.0 if wl["sampler"] == "DDPM" else 0.0, None,
+                            sample_offset=wl["steps"] - n)
+                evals = n
+            else:
+                sample_edm(o, start, E, layers, max(n, 2), 2 if wl["sampler"] == "Heun" else 1, None, last_step_euler=False)
+                evals = 2 * max(n, 2) if wl["sampler"] == "Heun" else max(n, 2)
+            t_total += time.perf_counter() - t0
+            evals_done += evals
+            n = min(n * 2, 8)
+    showers_per_s = batch * evals_done / t_total / wl["evals_per_shower"]
+    sample = (f"{evals_done} denoiser evaluations of the {wl['sampler']} loop at batch {batch} "
+              f"({t_total:.1f} s), scaled to {wl['evals_per_shower']} evaluations per shower")
+    return showers_per_s, cores, sample, t_total
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals, sample, cores = [], "", 1
+    for _ in range(max(args.warmup, 0)):
+        cpu_reference_leg(wl, budget_s=2.0)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        v, cores, sample, _ = cpu_reference_leg(wl, budget_s=10.0)
+        vals.append(v)
+    dt = time.perf_counter() - t0
+    v = sum(vals) / len(vals)
+    line = {
+        "impl": "reference", "metric": "showers/sec sampled", "value": v, "unit": "showers/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "batch_per_gpu": wl["batch"], "sampler": wl["sampler"],
+                   "sampling_steps": wl["steps"], "note": "each step = a bounded sample of the workload on the host CPU"},
+        "cpu_baseline": {"value": v, "unit": "showers/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "showers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def _op_profile(model, x, E, layers, sigma, reps=3):
+    """Per-op CUDA-event timing of single denoiser evaluations at the bench batch (eager diagnostic mode)."""
+    import torch
+    model.denoise(x, E=E, sigma=sigma, layers=layers)
+    torch.cuda.synchronize()
+    model.set_profile(2)
+    for _ in range(reps):
+        model.denoise(x, E=E, sigma=sigma, layers=layers)
+    torch.cuda.synchronize()
+    rep = model.profile_report()
+    model.set_profile(0)
+    return rep
+
+
+def _roofline(rep, peaks, B):
+    """Roofline entry of the dominant op class (largest share of the evaluation time)."""
+    total_ms = sum(v["ms"] for v in rep.values())
+    # group the per-shape op names into kernel classes
+    classes = {}
+    for name, v in rep.items():
+        if name.startswith("conv_") and name.endswith("_mma"):
+            cls = "conv_mma_kernel"
+        elif name.startswith("conv_"):
+            cls = "conv_generic_kernel"
+        elif name.startswith("gn_apply"):
+            cls = "gn_finalize+gn_apply"
+        else:
+            cls = name.split("_L")[0]
+        c = classes.setdefault(cls, dict(ms=0.0, flops=0.0, bytes=0.0, count=0))
+        for k in ("ms", "flops", "bytes", "count"):
+            c[k] += v[k]
+    top = max(classes, key=lambda k: classes[k]["ms"])
+    c = classes[top]
+    if c["flops"] > 0 and top.startswith("conv"):
+        achieved = c["flops"] / (c["ms"] * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf_sus"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["tf_sus"], "traffic": None}
+    else:
+        achieved = c["bytes"] / (c["ms"] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm"], "traffic": None}
+    roof.update(kernel=top, launches=c["count"], avg_launch_ms=c["ms"] / max(c["count"], 1),
+                share_of_eval=c["ms"] / total_ms, peak_source=peaks["src"] + (" (sustained bf16/fp16 dense)" if roof["bound"] == "tensor" else ""))
+    table = {k: {kk: v[kk] for kk in ("ms", "flops", "bytes", "count")}
+             for k, v in sorted(classes.items(), key=lambda kv: -kv[1]["ms"])}
+    return roof, table, total_ms
+
+
+def run_gpu_arm(args, wl):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from calodiffusion_b200.calodiffusion import CaloDiffusion
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg, B, steps = dict(wl["cfg"]), int(args.batch or wl["batch"]), int(args.sampling_steps or wl["steps"])
+    torch.manual_seed(0)                                   # identical random-init weights on every rank
+    model = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=B)
+    sampler = model.sampler_algorithm
+    sampler.shower_offset = rank * B                       # global shower index keys the Philox stream
+    if wl["sampler"] == "Heun":
+        sampler.last_step_euler = True                     # finite showers; 2 evals on all other steps
+    vox = int(np.prod(cfg["SHAPE_PAD"][1:]))
+    g = torch.Generator().manual_seed(1 + rank)
+    E_host = torch.rand(B, 1, generator=g).pin_memory()
+    L_host = torch.randn(B, wl["n_layers"], generator=g).pin_memory() if wl["n_layers"] else None
+    E_dev = E_host.to(dev)
+    L_dev = L_host.to(dev) if L_host is not None else None
+    start_dev = torch.randn([B] + cfg["SHAPE_PAD"][1:], device=dev, generator=torch.Generator(device=dev).manual_seed(2 + rank))
+    gathered = torch.empty(world * B, vox, device=dev) if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        x, _, _ = sampler(model, start_dev, E_dev, L_dev, steps, 0, False)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, x.reshape(B, vox))
+        return x
+
+    def api_step():
+        out = model.sample(E_host, L_host, num_steps=steps)     # numpy on host (models/diffusion.py:77-104)
+        return out
+
+    for _ in range(args.warmup):
+        x = device_step()
+    barrier()
+    assert bool(torch.isfinite(x).all()), "non-finite showers"
+    launches0 = model.launch_count()
+    clk = ClockSampler(local_rank)
+    if rank == 0:
+        clk.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        device_step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = clk.finish() if rank == 0 else None
+    launches = model.launch_count() - launches0
+
+    # end to end through the public API, host buffers in, host numpy out
+    api_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = api_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    assert out.shape[0] == B and np.isfinite(out).all()
+
+    t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    total_showers = world * B * args.steps
+    value = total_showers / (ms * 1e-3)
+    e2e = total_showers / (e2e_ms * 1e-3)
+    h2d = 4 * B * (1 + wl["n_layers"])
+    d2h = 4 * B * vox
+
+    if rank == 0:
+        peaks = _peaks()
+        sig = torch.full((B,), 1.5, device=dev)
+        rep = _op_profile(model, start_dev, E_dev, L_dev, sig)
+        roof, table, eval_ms = _roofline(rep, peaks, B)
+        reps = 3
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, sample, _ = cpu_reference_leg(wl, budget_s=12.0)
+            cpu = {"value": v, "unit": "showers/s", "cores": cores, "kind": "port", "sample": sample}
+        evals = wl["evals_per_shower"] * steps / wl["steps"]
+        line = {
+            "metric": "showers/sec sampled", "value": value, "unit": "showers/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 operands, f32 accumulate", "data": "synthetic",
+            "config": {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
+                       "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
+                       "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
+                       "weights": "random init (seed 0)"},
+            "e2e": {"value": e2e, "unit": "showers/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+            "shower_evals_per_s": value * evals,
+            "model_tflops": value * evals * wl["gflop_per_eval"] / 1e3,
+            "eval_ms_profiled": eval_ms / reps,
+        }
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"op_profile_{args.workload}_n{world}.json"), "w") as f:
+            json.dump({"batch": B, "reps": reps, "classes": table, "ops": rep}, f, indent=1)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="ds2", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="override showers per GPU (diagnostics only)")
+    ap.add_argument("--sampling-steps", type=int, default=0, help="override sampler steps (diagnostics only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_gpu_arm(args, wl)
+
+
+if __name__ == "__main__":
+    main()

@@ -11,7 +11,7 @@ CD_NUM_STATE_BUFS = 4
 EXPORTS = [
     "cd_last_error", "cd_version", "cd_device_check", "cd_unet_create", "cd_unet_destroy", "cd_unet_set_weight",
     "cd_unet_finalize", "cd_unet_set_option", "cd_unet_workspace_bytes", "cd_unet_launch_count", "cd_unet_forward",
-    "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_test_conv", "cd_level_shape",
+    "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
 ]
 
 
@@ -76,6 +76,7 @@ def load():
     lib.cd_fill_normal.argtypes = [vp, i64, i64, u64, i32, i32, vp]
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
+    lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]
     _lib = lib
     return lib
 

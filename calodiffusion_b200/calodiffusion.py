@@ -250,6 +250,22 @@ class CaloDiffusion(Diffusion):
     def launch_count(self):
         return int(self._lib.cd_unet_launch_count(self._handle)) if self._handle else 0
 
+    def set_profile(self, mode):
+        """1: time every op with CUDA events (eager, diagnostic); 2: same and reset the accumulators; 0: off."""
+        if self._handle is None:
+            raise RuntimeError("no engine yet: run one evaluation first")
+        _lib.check(self._lib.cd_unet_set_option(self._handle, b"profile", int(mode)), "set_option")
+
+    def profile_report(self):
+        """{op name: dict(count, ms, flops, bytes)} accumulated while profiling was on."""
+        buf = C.create_string_buffer(1 << 16)
+        _lib.check(self._lib.cd_unet_profile_report(self._handle, buf, len(buf)), "profile_report")
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, cnt, ms, fl, by = line.split()
+            out[name] = dict(count=int(cnt), ms=float(ms), flops=float(fl), bytes=float(by))
+        return out
+
     def workspace_bytes(self):
         return int(self._lib.cd_unet_workspace_bytes(self._handle)) if self._handle else 0
 

@@ -56,6 +56,9 @@ struct Run {  // per-call state
 
 struct Buf { int level, C; __half* ptr; bool busy; };
 
+struct OpInfo { std::string name; double flops, bytes; };          // per shower
+struct ProfAcc { long long count = 0; double ms = 0, flops = 0, bytes = 0; };
+
 }  // namespace cd
 
 using namespace cd;
@@ -68,6 +71,10 @@ struct cd_unet {
     std::vector<void*> dev_allocs;
     std::vector<Buf> bufs;
     std::vector<std::function<void(Run&)>> ops;
+    std::vector<cd::OpInfo> op_info;      // parallel to ops: name + algorithmic flops/bytes per shower
+    std::map<std::string, cd::ProfAcc> prof;
+    int profile = 0;
+    std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
     int conv_backend = 0;
     int64_t workspace_bytes = 0;
@@ -214,6 +221,17 @@ struct Builder {
               int write_halo, long long stats_off /* -1: none */) {
         cd_unet* hh = h;
         ConvW w = cw;
+        {
+            const Geom& go = hh->geom[level_out];
+            const Geom& gi = hh->geom[level_in];
+            double mo = (double)go.Z * go.P * go.R, mi = (double)gi.Z * gi.P * gi.R;
+            int taps = w.kz * w.kp * w.kr;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : ""), w.Cin, w.Cout,
+                     level_out, (w.wmma && stride == 1 && !w.transposed && !write_halo) ? "_mma" : "_simt");
+            // FLOP = 2*MAC over output voxels as the reference executes them; bytes = fp16 in + out
+            hh->op_info.push_back({nm, 2.0 * mo * w.Cin * w.Cout * taps, 2.0 * (mi * w.Cin + mo * w.Cout)});
+        }
         hh->ops.push_back([=](Run& r) {
             ConvParams p;
             p.gin = hh->geom[level_in];
@@ -248,6 +266,13 @@ struct Builder {
         float* beta = upload_vec(hh, bname, C);
         if (!gamma || !beta) { ok = false; return; }
         float2* affine = hh->dalloc<float2>((size_t)hh->d.max_batch * C, false);
+        {
+            const Geom& g = hh->geom[level];
+            double m = (double)g.Z * g.P * g.R;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "gn_apply_c%d_L%d%s", C, level, residual >= 0 ? "_res" : "");
+            hh->op_info.push_back({nm, 0.0, 2.0 * m * C * (residual >= 0 ? 3 : 2)});
+        }
         hh->ops.push_back([=](Run& r) {
             const Geom& g = hh->geom[level];
             double cnt = (double)g.Z * g.P * g.R;
@@ -316,6 +341,13 @@ struct Builder {
         }
         size_t s0 = slot((size_t)C * 16), s1 = slot((size_t)C * 16);
         size_t skm = slot(32 * 4), sctx = slot(33 * 32 * 4);
+        {
+            const Geom& g = hh->geom[level];
+            double m = (double)g.Z * g.P * g.R;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "row_stats_c%d_L%d", C, level);
+            hh->op_info.push_back({nm, 0.0, 2.0 * m * C});
+        }
         hh->ops.push_back([=](Run& r) {
             launch_row_stats(hh->geom[level], hh->bufs[x].ptr, (double*)(hh->scratch + s0 * r.B), C, r.B, r.st);
             hh->launches += 1;
@@ -325,6 +357,14 @@ struct Builder {
         int qkv = acquire(h, level, 96);
         conv(cq, level, level, {xn}, qkv, 1, 0, 0, 0, 0, -1);
         int ao = acquire(h, level, 32);
+        {
+            const Geom& g = hh->geom[level];
+            double m = (double)g.Z * g.P * g.R;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "attention_L%d", level);
+            // two 32x32xn einsums; bytes: k read twice, v, q read once, out written
+            hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m, 2.0 * m * 32 * 5});
+        }
         hh->ops.push_back([=](Run& r) {
             launch_attention(hh->geom[level], hh->bufs[qkv].ptr, (unsigned*)(hh->scratch + skm * r.B),
                              (float*)(hh->scratch + sctx * r.B), hh->bufs[ao].ptr, r.B, r.st);
@@ -365,6 +405,7 @@ static int build_plan(cd_unet* h) {
         if (!e.tw[i] || !e.tb[i] || !e.cw[i] || !e.cb[i]) return 1;
     }
     h->addvec_stride = 0;
+    h->op_info.push_back({"embed_mlp", 0.0, 0.0});
     h->ops.push_back([h](Run& r) {
         EmbedParams ep = h->embed;
         if (r.time_is_raw) ep.time_mode = 2;
@@ -374,6 +415,10 @@ static int build_plan(cd_unet* h) {
 
     // input + init conv (geometry channels are generated in-kernel; Cin padded to 8)
     int tin_buf = acquire(h, 0, 8);
+    {
+        double m = (double)d.Z * d.P * d.R;
+        h->op_info.push_back({"prep_input", 0.0, m * 4 + m * 16});
+    }
     h->ops.push_back([h, tin_buf](Run& r) {
         launch_prep_input(h->geom[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f, h->r_vals,
                           h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, r.B, r.st);
@@ -461,6 +506,10 @@ static int build_plan(cd_unet* h) {
     h->final_b = fb->data[0];
     h->final_C = ls[0];
     h->final_h = h->bufs[x].ptr;
+    {
+        double m = (double)d.Z * d.P * d.R;
+        h->op_info.push_back({"final_conv_update", 2.0 * m * ls[0], m * (2.0 * ls[0] + 16)});
+    }
     h->ops.push_back([h](Run& r) {
         FinalParams f = r.fin;
         f.g = h->geom[0];
@@ -482,7 +531,24 @@ static int build_plan(cd_unet* h) {
 static int run_forward(cd_unet* h, Run& r) {
     if (h->scratch_per_sample)
         cudaMemsetAsync(h->scratch, 0, h->scratch_per_sample * (size_t)r.B, r.st);
-    for (auto& op : h->ops) op(r);
+    if (h->profile) {
+        // eager per-op timing with CUDA events on the launch stream (diagnostic mode; not capturable):
+        // events are recorded between the ops without host synchronisation, read back after the last op
+        const size_t n = h->ops.size();
+        while (h->prof_evs.size() < n + 1) { cudaEvent_t ev; cudaEventCreate(&ev); h->prof_evs.push_back(ev); }
+        cudaEventRecord(h->prof_evs[0], r.st);
+        for (size_t i = 0; i < n; ++i) { h->ops[i](r); cudaEventRecord(h->prof_evs[i + 1], r.st); }
+        cudaEventSynchronize(h->prof_evs[n]);
+        for (size_t i = 0; i < n; ++i) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, h->prof_evs[i], h->prof_evs[i + 1]);
+            ProfAcc& a = h->prof[h->op_info[i].name];
+            a.count += 1; a.ms += ms;
+            a.flops += h->op_info[i].flops * r.B; a.bytes += h->op_info[i].bytes * r.B;
+        }
+    } else {
+        for (auto& op : h->ops) op(r);
+    }
     cudaError_t e = cudaPeekAtLastError();
     if (e != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(e));
     return 0;
@@ -574,6 +640,7 @@ cd_unet* cd_unet_create(const cd_unet_desc* desc) {
 void cd_unet_destroy(cd_unet* h) {
     if (!h) return;
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    for (cudaEvent_t ev : h->prof_evs) cudaEventDestroy(ev);
     for (void* p : h->dev_allocs) cudaFree(p);
     delete h;
 }
@@ -594,6 +661,11 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
     if (!strcmp(key, "conv_backend")) {
         h->conv_backend = value;
         if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
+        return 0;
+    }
+    if (!strcmp(key, "profile")) {
+        h->profile = value;
+        if (value == 2) { h->prof.clear(); h->profile = 1; }   // 2 = enable and reset
         return 0;
     }
     return fail("unknown option %s", key);
@@ -622,6 +694,19 @@ int cd_unet_finalize(cd_unet* h) {
 
 int64_t cd_unet_workspace_bytes(const cd_unet* h) { return h ? h->workspace_bytes : 0; }
 int64_t cd_unet_launch_count(const cd_unet* h) { return h ? h->launches : 0; }
+
+int cd_unet_profile_report(const cd_unet* h, char* buf, int cap) {
+    if (!h || !buf || cap < 1) return fail("bad argument");
+    int n = 0;
+    buf[0] = 0;
+    for (auto& kv : h->prof) {
+        int w = snprintf(buf + n, (size_t)(cap - n), "%s %lld %.6f %.6e %.6e\n", kv.first.c_str(), kv.second.count, kv.second.ms,
+                         kv.second.flops, kv.second.bytes);
+        if (w < 0 || w >= cap - n) return fail("profile report buffer too small");
+        n += w;
+    }
+    return 0;
+}
 
 int cd_level_shape(const cd_unet* h, int level, int* zpr) {
     if (!h || level < 0 || level >= h->n_levels) return fail("bad level");
@@ -751,7 +836,7 @@ extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_sca
     CD_CUDA(cudaMemcpyAsync(h->coef_tab, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, st));
     SampleArgs a{start_dev, start_scale, cond_dev, evals, n_evals, noise_bank_dev, seed, shower_offset, final_buf,
                  x_final_dev, xs_dev, x0s_dev, B};
-    if (!use_graph) return enqueue_sample(h, a, st);
+    if (!use_graph || h->profile) return enqueue_sample(h, a, st);
 
     // key: everything baked into the graph (structure + pointers); numeric schedule values live in coef_tab
     std::vector<unsigned char> key;

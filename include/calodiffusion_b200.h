@@ -82,11 +82,15 @@ void cd_unet_destroy(cd_unet* h);
 int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, const int64_t* shape, int ndim);
 /* validates that every tensor of the topology was supplied, packs weights, allocates workspaces */
 int cd_unet_finalize(cd_unet* h);
-/* options: "conv_backend" 0 = tcgen05 implicit GEMM where supported (default), 1 = generic SIMT everywhere */
+/* options: "conv_backend" 0 = tcgen05 implicit GEMM where supported (default), 1 = generic SIMT everywhere;
+ *          "profile" 1 = time every op of each forward with CUDA events (eager, diagnostic), 2 = same + reset, 0 = off */
 int cd_unet_set_option(cd_unet* h, const char* key, int value);
 int64_t cd_unet_workspace_bytes(const cd_unet* h);
 /* number of kernel launches issued by this handle since creation (graph replays count their nodes) */
 int64_t cd_unet_launch_count(const cd_unet* h);
+
+/* per-op timing gathered while "profile" is on: lines "name count total_ms flops bytes" (flops/bytes = algorithmic totals) */
+int cd_unet_profile_report(const cd_unet* h, char* buf, int cap);
 
 /* pred = CondUnet(add_RZPhi(x), cond, time); x and time (B values, already embedded) are used as given */
 int cd_unet_forward(cd_unet* h, const float* x_dev, const float* time_dev, const float* cond_dev,
