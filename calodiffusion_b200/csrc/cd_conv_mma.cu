@@ -1,19 +1,28 @@
 // tcgen05 / TMEM implicit-GEMM convolution for stride-1 CylindricalConv (3x3x3 and 1x1x1), sm_100a.
 //
-// GEMM view: D[M = padded-linear rows, N = C_out] += A_tap[M, C_in] * W_tap[C_in, C_out]
-// summed over the 27 (or 1) taps.  Thanks to the PLCP layout (cd_common.cuh) the A operand of tap
-// (dz,dp,dr) is the SAME activation rows shifted by dz*plane + dp*Rp + dr, so a CTA
-//   * bulk-copies (cp.async.bulk, the 1-D form of TMA; chunk planes are contiguous) three z-windows of
-//     (128*MT + 2*(Rp+1)) rows per 8-channel chunk into shared memory ONCE per tile,
-//   * addresses every tap as a shifted window of that smem through the UMMA shared-memory descriptor
-//     (no-swizzle K-major canonical layout: 8 rows x 16 B core matrices, SBO = 128 B, LBO = chunk stride),
-//   * streams W_tap ([kchunk][n][8] fp16, N x K K-major) through an mbarrier ring,
-//   * accumulates in TMEM (MT accumulators of 128 lanes x C_out fp32 columns) with tcgen05.mma issued by
-//     one thread, and
-//   * drains TMEM with tcgen05.ld in four epilogue warps that add the bias, round to fp16, store the
-//     interior rows and reduce the GroupNorm statistics (sum / sum of squares per sample and channel).
-// Circular phi padding and zero Z/R padding therefore cost no instructions here: they are the halo rows
-// of the PLCP tensor (models/models.py:90-96 semantics).
+// GEMM view for the 3x3x3 case ("R-stacked"): for every padded-linear row m of the PLCP tensor (cd_common.cuh)
+//     D[m, g*CB + co] = sum over (dz,dp) in {-1,0,1}^2, ci:  X[m + dz*plane + dp*Rp, ci] * W[dz,dp,dr=g-1][ci, co]
+//     out[m, co]      = D[m-1, 0*CB+co] + D[m, 1*CB+co] + D[m+1, 2*CB+co] + bias[co]
+// i.e. the three R-taps are stacked in the GEMM N dimension (N = 3*CB, CB = block of output channels) and
+// recombined in the epilogue with two warp shuffles.  Why: with C_out = 32 a plain K-concatenated implicit GEMM
+// issues M128xN32xK16 MMAs whose A operand (4 KB) must be re-read from shared memory for each of the 27 taps;
+// measured on B200 (scripts/mma_microbench.cu) such an MMA takes 44 clk instead of its 16 clk tensor floor
+// (128 B/clk shared-memory read limit).  Stacking R gives M128xN96xK16 MMAs: 56 clk for 3x the work (85 % of
+// the tensor floor), and N=192 for C_out = 64 runs at the floor.
+//
+//   * A operand: cp.async.bulk (1-D TMA) copies contiguous row windows of each 8-channel chunk plane into shared
+//     memory once per tile; every (dz,dp) shift is the same window at a row offset, addressed through the UMMA
+//     shared-memory descriptor (no-swizzle K-major: 8 rows x 16 B core matrices, SBO 128 B, LBO = chunk stride).
+//     Circular phi padding and zero Z/R padding are the halo rows of the PLCP tensor (models/models.py:90-96).
+//   * B operand: packed weights [shift][kchunk][n][8] fp16, resident in shared memory for the whole persistent
+//     CTA when they fit (the dominant 32->32 shape: 55 KB), else streamed through an mbarrier ring.
+//   * D: TMEM accumulator slots of 128 lanes x N fp32 columns, ring-buffered so the epilogue of one 128-row
+//     sub-tile overlaps the MMAs of the next.  Sub-tiles advance by 126 rows (rows 0 and 127 of a sub-tile lack
+//     their m-1 / m+1 neighbour).
+//   * Epilogue (2 groups of 4 warps): tcgen05.ld, R-recombination by shuffles (+ a 2x32-float shared-memory
+//     exchange at the warp-quarter boundaries), bias, fp16 rounding, coalesced PLCP stores of the interior rows,
+//     and the GroupNorm statistics (per sample and channel sum / sum of squares) by a butterfly transpose-reduce
+//     kept in registers across the CTA's consecutive tiles and flushed with double atomics on sample change.
 #include <cuda.h>
 #include <cstdio>
 
@@ -23,29 +32,43 @@ namespace cd {
 
 namespace {
 
-constexpr int kThreads = 192;  // warp 0: loads, warp 1: MMA issue + TMEM alloc, warps 2-5: epilogue
-constexpr int kMaxStages = 4;
+constexpr int kEpiWarps = 8;                    // 2 groups x 4 lane quarters
+constexpr int kThreads = 64 + 32 * kEpiWarps;   // warp 0: loads, warp 1: MMA issue + TMEM alloc, warps 2..9: epilogue
+constexpr int kMaxWStages = 4;
+constexpr int kAStages = 2;
+constexpr int kMaxAcc = 8;
 
 struct MmaParams {
     Geom g;
     const __half* src[2];
     int src_chunks[2];      // 8-channel chunks per source
-    int nchunks;            // total
-    const __half* w;        // [tap][kc][n][8]
+    int nchunks;            // Cin / 8
+    const __half* w;        // this launch's packed weights: [cb][shift][kc][n][8]
     const float* bias;
     __half* dst;
     double* stats;
-    int Cout;
-    int ntaps;              // 27 or 1
-    int MT;                 // 128-row sub-tiles per CTA tile
-    int wrows;              // rows per smem window
-    int nwin;               // 3 (3x3x3) or 1
-    int halo;               // Rp+1 or 0
-    int nstages;
-    int stage_bytes;        // one tap of weights
+    int Cout, CB, ncb;      // output channels, channels per block, blocks
+    int N;                  // GEMM N = 3*CB (3x3x3) or CB (1x1x1)
+    int nshift;             // 9 or 1
+    int sub_stride;         // 126 or 128
+    int MT;                 // sub-tiles per tile
+    int tile_rows;          // output rows per tile = sub_stride * MT
+    int d_lead;             // D row of sub-tile 0 relative to the tile's first output row: -1 or 0
+    int wrows, nwin;        // rows per shared-memory window, windows per chunk (1 = union, 3 = one per dz)
+    int row0;               // first window row relative to the tile's first D row (<= 0)
+    int win_dz;             // window offset per dz in rows (3-window mode: plane; union mode: 0)
+    int off_dz, off_dp;     // row offset inside a window per dz / dp step
+    int nacc;               // TMEM accumulator slots
+    int resident;           // 1: weights resident in smem, 0: streamed ring
+    int w_bytes_cb;         // bytes of one channel block's weights
+    int wstage_bytes;       // ring stage = one shift x one K group
+    int kgroup_chunks;      // chunks per ring stage
+    int nwstages;
+    int a_stage_bytes;
+    int astages;            // activation window stages (2, or 1 when shared memory is short)
     long long nrows;        // B * rows_per_sample
     int ntiles;
-    int tmem_cols;
+    int tiles_per_cta;
     uint32_t idesc;
 };
 
@@ -95,48 +118,67 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 struct SmemCtl {
-    uint64_t a_full, a_empty, tmem_full, tmem_empty;
-    uint64_t w_full[kMaxStages], w_empty[kMaxStages];
+    uint64_t a_full[kAStages], a_empty[kAStages];
+    uint64_t t_full[kMaxAcc], t_empty[kMaxAcc];
+    uint64_t w_full[kMaxWStages], w_empty[kMaxWStages];
+    uint64_t w_res;
     uint32_t tmem_base;
-    int bmin, bmax;
-    int pad;
+    uint32_t pad;
 };
+constexpr int kCtlBytes = 512;
+constexpr int kXchBytes = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64 * 4;   // 8 KB
+static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
-__global__ void __launch_bounds__(kThreads) conv_mma_kernel(const MmaParams p) {
+// sum over the 32 lanes of v[c] for every c in [0,32): lane l returns the total of channel l (31 shuffles)
+__device__ __forceinline__ float butterfly32(float* v, int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool hi = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = hi ? v[i] : v[i + off];
+            const float keep = hi ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
+template <int CB, bool K3>
+__global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem);
-    // layout: [ctl 256 B][stats scratch][weight ring][A windows]
-    float* red = reinterpret_cast<float*>(smem + 256);                 // [128][Cout+1] + [4][Cout][2]
-    const int red_bytes = ((128 * (p.Cout + 1) + 8 * p.Cout) * 4 + 127) / 128 * 128;
-    unsigned char* wring = smem + 256 + red_bytes;
-    unsigned char* abuf = wring + (size_t)p.nstages * p.stage_bytes;
-    const uint32_t wring_s = smem_u32(wring), abuf_s = smem_u32(abuf);
+    float* xch = reinterpret_cast<float*>(smem + kCtlBytes);
+    unsigned char* wbuf = smem + kCtlBytes + kXchBytes;
+    const int w_smem_bytes = p.resident ? p.w_bytes_cb : p.nwstages * p.wstage_bytes;
+    unsigned char* abuf = wbuf + ((w_smem_bytes + 127) / 128) * 128;
+    const uint32_t wbuf_s = smem_u32(wbuf), abuf_s = smem_u32(abuf);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Geom& g = p.g;
+    constexpr int N = K3 ? 3 * CB : CB;
 
     if (threadIdx.x == 0) {
-        mbar_init(smem_u32(&ctl->a_full), 1);
-        mbar_init(smem_u32(&ctl->a_empty), 1);
-        mbar_init(smem_u32(&ctl->tmem_full), 1);
-        mbar_init(smem_u32(&ctl->tmem_empty), 4);
-        for (int s = 0; s < p.nstages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), 1); }
+        for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), 1); }
+        for (int s = 0; s < kMaxAcc; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 4); }
+        for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), 1); }
+        mbar_init(smem_u32(&ctl->w_res), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&ctl->tmem_base)), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&ctl->tmem_base)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -144,164 +186,332 @@ __global__ void __launch_bounds__(kThreads) conv_mma_kernel(const MmaParams p) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = ctl->tmem_base;
 
-    const int tile_rows = 128 * p.MT;
+    const int cb = blockIdx.x % p.ncb;
+    const int cta = blockIdx.x / p.ncb;
+    const int tile_begin = cta * p.tiles_per_cta;
+    int tile_end = tile_begin + p.tiles_per_cta;
+    if (tile_end > p.ntiles) tile_end = p.ntiles;
+    const int my_tiles = tile_end > tile_begin ? tile_end - tile_begin : 0;
     const uint32_t win_bytes = (uint32_t)p.wrows * 16u;
     const uint32_t chunk_bytes = win_bytes * p.nwin;   // smem bytes per 8-channel chunk
+    const unsigned char* wsrc = reinterpret_cast<const unsigned char*>(p.w) + (size_t)cb * p.w_bytes_cb;
+    const int nkg = (p.nchunks + p.kgroup_chunks - 1) / p.kgroup_chunks;
 
     if (warp == 0) {
-        // ===================== producer: activation windows + weight ring =====================
+        // ===================== producer: resident weights / weight ring + activation windows =====================
         if (lane == 0) {
-            uint32_t it = 0, wcount = 0;
-            for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
-                const long long m0 = (long long)tile * tile_rows;
-                mbar_wait(smem_u32(&ctl->a_empty), (it & 1) ^ 1);
-                mbar_expect_tx(smem_u32(&ctl->a_full), chunk_bytes * p.nchunks);
+            if (p.resident) {
+                mbar_expect_tx(smem_u32(&ctl->w_res), p.w_bytes_cb);
+                for (int off = 0; off < p.w_bytes_cb; off += 32768) {
+                    int n = p.w_bytes_cb - off < 32768 ? p.w_bytes_cb - off : 32768;
+                    bulk_g2s(wbuf_s + off, wsrc + off, n, smem_u32(&ctl->w_res));
+                }
+            }
+            uint32_t wcount = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int tile = tile_begin + it;
+                const int stage = it % p.astages;
+                const uint32_t ph = (it / p.astages) & 1;
+                const long long d0 = (long long)tile * p.tile_rows + p.d_lead;
+                mbar_wait(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
+                mbar_expect_tx(smem_u32(&ctl->a_full[stage]), p.a_stage_bytes);
                 int ch = 0;
                 for (int s = 0; s < 2; ++s) {
                     for (int k = 0; k < p.src_chunks[s]; ++k, ++ch) {
                         const __half* plane0 = p.src[s] + plcp_offset(g, k, 0);
                         for (int w = 0; w < p.nwin; ++w) {
-                            long long r0 = m0 + (long long)(w - (p.nwin >> 1)) * g.plane - p.halo;
-                            bulk_g2s(abuf_s + ch * chunk_bytes + w * win_bytes, plane0 + r0 * 8, win_bytes, smem_u32(&ctl->a_full));
+                            const long long r0 = d0 + p.row0 + (long long)(w - (p.nwin >> 1)) * p.win_dz;
+                            bulk_g2s(abuf_s + stage * p.a_stage_bytes + ch * chunk_bytes + w * win_bytes, plane0 + r0 * 8, win_bytes,
+                                     smem_u32(&ctl->a_full[stage]));
                         }
                     }
                 }
-                for (int t = 0; t < p.ntaps; ++t, ++wcount) {
-                    const uint32_t s = wcount % p.nstages, ph = (wcount / p.nstages) & 1;
-                    mbar_wait(smem_u32(&ctl->w_empty[s]), ph ^ 1);
-                    mbar_expect_tx(smem_u32(&ctl->w_full[s]), p.stage_bytes);
-                    bulk_g2s(wring_s + s * p.stage_bytes, reinterpret_cast<const unsigned char*>(p.w) + (size_t)t * p.stage_bytes,
-                             p.stage_bytes, smem_u32(&ctl->w_full[s]));
+                if (!p.resident) {
+                    for (int s = 0; s < p.nshift; ++s) {
+                        for (int kg = 0; kg < nkg; ++kg, ++wcount) {
+                            const uint32_t ws = wcount % p.nwstages, wph = (wcount / p.nwstages) & 1;
+                            const int kc0 = kg * p.kgroup_chunks;
+                            const int kcn = (p.nchunks - kc0) < p.kgroup_chunks ? (p.nchunks - kc0) : p.kgroup_chunks;
+                            const uint32_t bytes = (uint32_t)kcn * N * 16u;
+                            mbar_wait(smem_u32(&ctl->w_empty[ws]), wph ^ 1);
+                            mbar_expect_tx(smem_u32(&ctl->w_full[ws]), bytes);
+                            bulk_g2s(wbuf_s + ws * p.wstage_bytes, wsrc + ((size_t)s * p.nchunks + kc0) * N * 16u, bytes,
+                                     smem_u32(&ctl->w_full[ws]));
+                        }
+                    }
                 }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
         if (lane == 0) {
-            uint32_t it = 0, wcount = 0;
-            const int k16 = p.nchunks >> 1;
-            for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
-                mbar_wait(smem_u32(&ctl->tmem_empty), (it & 1) ^ 1);
-                mbar_wait(smem_u32(&ctl->a_full), it & 1);
+            uint32_t cnt = 0, wcount = 0;
+            if (p.resident) mbar_wait(smem_u32(&ctl->w_res), 0);
+            for (int it = 0; it < my_tiles; ++it) {
+                const int stage = it % p.astages;
+                const uint32_t ph = (it / p.astages) & 1;
+                const uint32_t a_base = abuf_s + stage * p.a_stage_bytes;
+                mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                for (int t = 0; t < p.ntaps; ++t, ++wcount) {
-                    const uint32_t s = wcount % p.nstages, ph = (wcount / p.nstages) & 1;
-                    mbar_wait(smem_u32(&ctl->w_full[s]), ph);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    int win = 0, shift = 0;
-                    if (p.ntaps == 27) {
-                        const int a = t / 9, b = (t / 3) % 3, c = t % 3;
-                        win = a;
-                        shift = (b - 1) * g.Rp + (c - 1);
+                if (p.resident) {
+                    for (int j = 0; j < p.MT; ++j, ++cnt) {
+                        const uint32_t slot = cnt % p.nacc, tph = (cnt / p.nacc) & 1;
+                        mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        uint32_t accum = 0;
+                        for (int s = 0; s < p.nshift; ++s) {
+                            const int a = K3 ? s / 3 : 1, b = K3 ? s % 3 : 1;
+                            const int win = p.nwin == 3 ? a : 0;
+                            const int rowoff = -p.row0 + (a - 1) * p.off_dz + (b - 1) * p.off_dp + j * p.sub_stride;
+                            const uint32_t a_row0 = a_base + win * win_bytes + (uint32_t)rowoff * 16u;
+                            const uint32_t b0 = wbuf_s + (uint32_t)(s * p.nchunks) * N * 16u;
+                            for (int q = 0; q < (p.nchunks >> 1); ++q) {
+                                const uint64_t ad = make_desc(a_row0 + (uint32_t)(2 * q) * chunk_bytes, chunk_bytes, 128u);
+                                const uint64_t bd = make_desc(b0 + (uint32_t)(2 * q) * N * 16u, (uint32_t)N * 16u, 128u);
+                                umma_f16(tmem_base + slot * N, ad, bd, p.idesc, accum);
+                                accum = 1;
+                            }
+                        }
+                        umma_commit(smem_u32(&ctl->t_full[slot]));
                     }
-                    const uint32_t a_row0 = abuf_s + win * win_bytes + (uint32_t)(p.halo + shift) * 16u;
-                    const uint32_t b0 = wring_s + s * p.stage_bytes;
+                } else {
                     for (int j = 0; j < p.MT; ++j) {
-                        for (int q = 0; q < k16; ++q) {
-                            const uint64_t ad = make_desc(a_row0 + (uint32_t)(2 * q) * chunk_bytes + (uint32_t)j * 2048u, chunk_bytes, 128u);
-                            const uint64_t bd = make_desc(b0 + (uint32_t)(2 * q) * p.Cout * 16u, (uint32_t)p.Cout * 16u, 128u);
-                            umma_f16(tmem_base + (uint32_t)(j * p.Cout), ad, bd, p.idesc, (t | q) != 0);
+                        const uint32_t n = cnt + j, slot = n % p.nacc, tph = (n / p.nacc) & 1;
+                        mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                    }
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    for (int s = 0; s < p.nshift; ++s) {
+                        const int a = K3 ? s / 3 : 1, b = K3 ? s % 3 : 1;
+                        const int win = p.nwin == 3 ? a : 0;
+                        for (int kg = 0; kg < nkg; ++kg, ++wcount) {
+                            const uint32_t ws = wcount % p.nwstages, wph = (wcount / p.nwstages) & 1;
+                            const int kc0 = kg * p.kgroup_chunks;
+                            const int kcn = (p.nchunks - kc0) < p.kgroup_chunks ? (p.nchunks - kc0) : p.kgroup_chunks;
+                            mbar_wait(smem_u32(&ctl->w_full[ws]), wph);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            const uint32_t b0 = wbuf_s + ws * p.wstage_bytes;
+                            for (int j = 0; j < p.MT; ++j) {
+                                const uint32_t slot = (cnt + j) % p.nacc;
+                                const int rowoff = -p.row0 + (a - 1) * p.off_dz + (b - 1) * p.off_dp + j * p.sub_stride;
+                                const uint32_t a_row0 = a_base + win * win_bytes + (uint32_t)rowoff * 16u;
+                                for (int q = 0; q < (kcn >> 1); ++q) {
+                                    const uint64_t ad = make_desc(a_row0 + (uint32_t)(kc0 + 2 * q) * chunk_bytes, chunk_bytes, 128u);
+                                    const uint64_t bd = make_desc(b0 + (uint32_t)(2 * q) * N * 16u, (uint32_t)N * 16u, 128u);
+                                    umma_f16(tmem_base + slot * N, ad, bd, p.idesc, (s | kg | q) != 0);
+                                }
+                            }
+                            umma_commit(smem_u32(&ctl->w_empty[ws]));
                         }
                     }
-                    umma_commit(smem_u32(&ctl->w_empty[s]));
+                    for (int j = 0; j < p.MT; ++j) umma_commit(smem_u32(&ctl->t_full[(cnt + j) % p.nacc]));
+                    cnt += p.MT;
                 }
-                umma_commit(smem_u32(&ctl->a_empty));
-                umma_commit(smem_u32(&ctl->tmem_full));
+                umma_commit(smem_u32(&ctl->a_empty[stage]));
             }
         }
     } else {
         // ===================== epilogue: TMEM -> registers -> global (+ GroupNorm statistics) =====================
-        const int ew = warp & 3;                 // TMEM lane quarter this warp may read
-        const int et = ew * 32 + lane;           // row within the 128-row sub-tile
-        const int epi_tid = threadIdx.x - 64;    // 0..127
-        const int pitch = p.Cout + 1;
-        float* part = red + 128 * pitch;         // [4][Cout][2]
-        uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
-            const long long m0 = (long long)tile * tile_rows;
-            mbar_wait(smem_u32(&ctl->tmem_full), it & 1);
+        const int q = warp & 3;                   // TMEM lane quarter this warp may read (warp id % 4)
+        const int group = (warp - 2) >> 2;        // 0 / 1: the two groups alternate sub-tiles
+        const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
+        constexpr int CBP = (CB + 31) / 32 * 32;  // channels padded to whole 32-blocks for the butterfly
+        constexpr int NB = CBP / 32;
+        float bias[CB];
+#pragma unroll
+        for (int c = 0; c < CB; ++c) bias[c] = p.bias ? __ldg(p.bias + cb * CB + c) : 0.f;
+        double run_s[NB], run_q[NB];              // lane l: running sums of channel blk*32+l for sample cur_b
+#pragma unroll
+        for (int b = 0; b < NB; ++b) { run_s[b] = 0.0; run_q[b] = 0.0; }
+        int cur_b = -1;
+        auto flush = [&]() {
+            if (cur_b >= 0) {
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    const int c = b * 32 + lane;
+                    if (c < CB) {
+                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + c) * 2;
+                        atomicAdd(d, run_s[b]);
+                        atomicAdd(d + 1, run_q[b]);
+                    }
+                    run_s[b] = 0.0; run_q[b] = 0.0;
+                }
+            }
+        };
+        const int total_sub = my_tiles * p.MT;
+        for (int n = group; n < total_sub; n += 2) {
+            const int tile = tile_begin + n / p.MT, j = n % p.MT;
+            const uint32_t slot = n % p.nacc, tph = (n / p.nacc) & 1;
+            const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
+            mbar_wait(smem_u32(&ctl->t_full[slot]), tph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int j = 0; j < p.MT; ++j) {
-                const long long row = m0 + (long long)j * 128 + et;
-                RowInfo ri;
-                ri.kind = 2; ri.b = 0;
-                if (row < p.nrows) ri = decode_row(g, row);
-                const bool valid = ri.kind == 0;
-                if (p.stats) {
-                    if (epi_tid == 0) { ctl->bmin = 0x7fffffff; ctl->bmax = -1; }
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    if (valid) { atomicMin(&ctl->bmin, ri.b); atomicMax(&ctl->bmax, ri.b); }
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * N;
+            float acc[CBP];
+#pragma unroll
+            for (int c = CB; c < CBP; ++c) acc[c] = 0.f;
+            if constexpr (K3) {
+                const int par = (n >> 1) & 1;
+                float* xup = xch + (size_t)(((group * 2 + par) * 2 + 0) * 4) * 64;
+                float* xdn = xch + (size_t)(((group * 2 + par) * 2 + 1) * 4) * 64;
+#pragma unroll
+                for (int c0 = 0; c0 < CB; c0 += 16) {
+                    float t[16];
+                    tmem_ld16(taddr + CB + c0, t);
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[c0 + k] = t[k] + bias[c0 + k];
                 }
-                for (int c0 = 0; c0 < p.Cout; c0 += 32) {
-                    uint32_t r[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(j * p.Cout + c0), r);
-                    float v[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + (p.bias ? __ldg(p.bias + c0 + i) : 0.f);
+                for (int c0 = 0; c0 < CB; c0 += 16) {        // D_0 of row m-1
+                    float t[16];
+                    tmem_ld16(taddr + c0, t);
+                    if (lane == 31) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        Half8 h = pack8(v + 8 * k);
-                        if (valid) *reinterpret_cast<Half8*>(p.dst + plcp_offset(g, (c0 >> 3) + k, row)) = h;
-                        if (p.stats) unpack8(h, v + 8 * k);   // statistics of the values as stored
+                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<float4*>(xup + q * 64 + c0 + k) = make_float4(t[k], t[k + 1], t[k + 2], t[k + 3]);
                     }
-                    if (p.stats) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) red[et * pitch + c0 + i] = valid ? v[i] : 0.f;
-                    }
+                    for (int k = 0; k < 16; ++k) { const float u = __shfl_up_sync(0xffffffffu, t[k], 1); if (lane > 0) acc[c0 + k] += u; }
                 }
-                if (p.stats) {
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    const int bmin = ctl->bmin, bmax = ctl->bmax;
-                    const bool uniform = bmax >= 0 && bmin == bmax;
-                    if (uniform) {
-                        // one sample in this sub-tile: column sums by 4 row-quarters
-                        for (int c = lane; c < p.Cout; c += 32) {
-                            float s = 0.f, q = 0.f;
-                            for (int rr = ew * 32; rr < ew * 32 + 32; ++rr) { float x = red[rr * pitch + c]; s += x; q += x * x; }
-                            part[(ew * p.Cout + c) * 2] = s;
-                            part[(ew * p.Cout + c) * 2 + 1] = q;
-                        }
+#pragma unroll
+                for (int c0 = 0; c0 < CB; c0 += 16) {        // D_2 of row m+1
+                    float t[16];
+                    tmem_ld16(taddr + 2 * CB + c0, t);
+                    if (lane == 0) {
+#pragma unroll
+                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<float4*>(xdn + q * 64 + c0 + k) = make_float4(t[k], t[k + 1], t[k + 2], t[k + 3]);
                     }
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) { const float u = __shfl_down_sync(0xffffffffu, t[k], 1); if (lane < 31) acc[c0 + k] += u; }
+                }
+                // the accumulator slot is free again
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+                // quarter-boundary rows: exchange through shared memory within the group
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
+                if (lane == 0 && q > 0) {
+#pragma unroll
+                    for (int c = 0; c < CB; c += 4) { const float4 u = *reinterpret_cast<const float4*>(xup + (q - 1) * 64 + c); acc[c] += u.x; acc[c + 1] += u.y; acc[c + 2] += u.z; acc[c + 3] += u.w; }
+                }
+                if (lane == 31 && q < 3) {
+#pragma unroll
+                    for (int c = 0; c < CB; c += 4) { const float4 u = *reinterpret_cast<const float4*>(xdn + (q + 1) * 64 + c); acc[c] += u.x; acc[c + 1] += u.y; acc[c + 2] += u.z; acc[c + 3] += u.w; }
+                }
+            } else {
+#pragma unroll
+                for (int c0 = 0; c0 < CB; c0 += 16) {
+                    float t[16];
+                    tmem_ld16(taddr + c0, t);
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[c0 + k] = t[k] + bias[c0 + k];
+                }
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+            }
+            // which output row is this?
+            bool valid = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
+            int sample = -1;
+            if (valid) {
+                const RowInfo ri = decode_row(g, row);
+                valid = ri.kind == 0;
+                sample = ri.b;
+            }
+#pragma unroll
+            for (int k = 0; k < CB / 8; ++k) {
+                const Half8 h = pack8(acc + 8 * k);
+                if (valid) *reinterpret_cast<Half8*>(p.dst + plcp_offset(g, cb * (CB / 8) + k, row)) = h;
+                unpack8(h, acc + 8 * k);      // statistics of the values as stored
+            }
+            if (p.stats) {
+                const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+                if (vmask) {
+                    const int b_first = __shfl_sync(0xffffffffu, sample, __ffs(vmask) - 1);
+                    const bool uniform = __all_sync(0xffffffffu, !valid || sample == b_first);
                     if (uniform) {
-                        // ... then one atomic pair per channel
-                        for (int c = epi_tid; c < p.Cout; c += 128) {
-                            float s = 0.f, q = 0.f;
-                            for (int w4 = 0; w4 < 4; ++w4) { s += part[(w4 * p.Cout + c) * 2]; q += part[(w4 * p.Cout + c) * 2 + 1]; }
-                            double* d = p.stats + ((long long)bmin * p.Cout + c) * 2;
-                            atomicAdd(d, (double)s);
-                            atomicAdd(d + 1, (double)q);
+                        if (b_first != cur_b) { flush(); cur_b = b_first; }
+#pragma unroll
+                        for (int b = 0; b < NB; ++b) {
+                            float v[32], w[32];
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) { const float x = valid ? acc[b * 32 + c] : 0.f; v[c] = x; w[c] = x * x; }
+                            run_s[b] += (double)butterfly32(v, lane);
+                            run_q[b] += (double)butterfly32(w, lane);
                         }
-                    } else if (bmax >= 0 && valid) {
-                        // sub-tile straddles two samples (rare): per-row atomics
-                        for (int c = 0; c < p.Cout; ++c) {
-                            float x = red[et * pitch + c];
-                            double* d = p.stats + ((long long)ri.b * p.Cout + c) * 2;
-                            atomicAdd(d, (double)x);
-                            atomicAdd(d + 1, (double)(x * x));
+                    } else {
+                        // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
+                        flush();
+                        cur_b = -1;
+                        if (valid) {
+#pragma unroll
+                            for (int c = 0; c < CB; ++c) {
+                                double* d = p.stats + ((long long)sample * p.Cout + cb * CB + c) * 2;
+                                atomicAdd(d, (double)acc[c]);
+                                atomicAdd(d + 1, (double)(acc[c] * acc[c]));
+                            }
                         }
                     }
                 }
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&ctl->tmem_empty));
         }
+        if (p.stats) flush();
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
 }
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------------------
+// host side: weight packing, tile planning, launch
+// ---------------------------------------------------------------------------------------------------------
+static int pick_cb(int Cout) {
+    const int cands[4] = {64, 48, 32, 16};
+    for (int c : cands) if (Cout % c == 0) return c;
+    return 0;
+}
+
+bool mma_conv_supported(int Cin, int Cout, int taps) {
+    return (taps == 27 || taps == 1) && Cin % 16 == 0 && Cin >= 16 && Cout % 16 == 0 && pick_cb(Cout) > 0;
+}
+
+size_t mma_packed_elems(int Cin, int Cout, int taps) { return (size_t)taps * Cin * Cout; }
+
+// w: fp32 [tap][ci][co] (tap = (a*3+b)*3+c for 3x3x3).  out: fp16 [cb][shift][kc][n][8], n = g*CB + co_local
+void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out) {
+    const int CB = pick_cb(Cout), ncb = Cout / CB, nkc = Cin / 8;
+    const int nshift = taps == 27 ? 9 : 1, ng = taps == 27 ? 3 : 1, N = ng * CB;
+    for (int cb = 0; cb < ncb; ++cb)
+        for (int s = 0; s < nshift; ++s)
+            for (int kc = 0; kc < nkc; ++kc)
+                for (int n = 0; n < N; ++n)
+                    for (int j = 0; j < 8; ++j) {
+                        const int gi = n / CB, co = cb * CB + n % CB;
+                        const int tap = s * ng + gi;
+                        out[((((size_t)cb * nshift + s) * nkc + kc) * N + n) * 8 + j] =
+                            __float2half_rn(w[((size_t)tap * Cin + kc * 8 + j) * Cout + co]);
+                    }
+}
+
+template <int CB, bool K3>
+static cudaError_t launch_inst(const MmaParams& p, int grid, size_t smem, int max_smem, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(conv_mma_kernel<CB, K3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    conv_mma_kernel<CB, K3><<<grid, kThreads, smem, st>>>(p);
+    return cudaSuccess;
+}
+
 int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t st) {
     const int taps = cp.kz * cp.kp * cp.kr;
     if (cp.transposed || cp.sz != 1 || cp.sp != 1 || cp.sr != 1) return 1;
-    if (!(taps == 27 && cp.kz == 3 && cp.kp == 3 && cp.kr == 3 && cp.pz == 1 && cp.cp == 1 && cp.pr == 1) && taps != 1) return 1;
-    if (cp.Cout % 32 != 0 || cp.Cout > 256 || cp.Cin_total % 16 != 0) return 1;
+    const bool k3 = taps == 27;
+    if (k3 && !(cp.kz == 3 && cp.kp == 3 && cp.kr == 3 && cp.pz == 1 && cp.cp == 1 && cp.pr == 1)) return 1;
+    if (!mma_conv_supported(cp.Cin_total, cp.Cout, taps)) return 1;
     if (cp.gin.Z != cp.gout.Z || cp.gin.P != cp.gout.P || cp.gin.R != cp.gout.R) return 1;
     for (int s = 0; s < cp.nsrc; ++s) if (cp.src[s].C % 8 != 0) return 1;
 
@@ -311,56 +521,75 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
         cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        cudaFuncSetAttribute(conv_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     }
+    const Geom& g = cp.gout;
     MmaParams p;
-    p.g = cp.gout;
+    p.g = g;
     p.src[0] = cp.src[0].base; p.src_chunks[0] = cp.src[0].C / 8;
     p.src[1] = cp.nsrc > 1 ? cp.src[1].base : nullptr; p.src_chunks[1] = cp.nsrc > 1 ? cp.src[1].C / 8 : 0;
     p.nchunks = cp.Cin_total / 8;
     if (p.src_chunks[0] + p.src_chunks[1] != p.nchunks) return 1;
     p.w = packed_w; p.bias = cp.bias; p.dst = cp.dst; p.stats = cp.stats;
-    p.Cout = cp.Cout; p.ntaps = taps;
-    p.nwin = taps == 27 ? 3 : 1;
-    p.halo = taps == 27 ? cp.gout.Rp + 1 : 0;
-    p.stage_bytes = cp.Cin_total * cp.Cout * 2;
-    p.nrows = (long long)cp.B * cp.gout.rows_per_sample;
-    const int red_bytes = ((128 * (cp.Cout + 1) + 8 * cp.Cout) * 4 + 127) / 128 * 128;
-    // pick MT (sub-tiles per CTA) and ring depth: prefer >= 2 CTAs per SM, then the largest tile
-    int best_mt = 0, best_stages = 0;
-    size_t best_smem = 0;
-    for (int pass = 0; pass < 2 && !best_mt; ++pass) {
-        const size_t budget = pass == 0 ? (size_t)(max_smem / 2 - 2048) : (size_t)max_smem;
-        for (int mt = 4; mt >= 1; mt >>= 1) {
-            if (mt * cp.Cout > 256) continue;
-            const size_t a_bytes = (size_t)p.nchunks * p.nwin * (128 * mt + 2 * p.halo) * 16;
-            const size_t fixed = 256 + red_bytes + a_bytes;
-            if (fixed + 2 * (size_t)p.stage_bytes > budget) continue;
-            int stages = (int)((budget - fixed) / p.stage_bytes);
-            if (stages > kMaxStages) stages = kMaxStages;
-            if (stages > taps) stages = taps;
-            if (stages < 1) continue;
-            best_mt = mt; best_stages = stages; best_smem = fixed + (size_t)stages * p.stage_bytes;
-            break;
+    p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout); p.ncb = cp.Cout / p.CB;
+    p.N = k3 ? 3 * p.CB : p.CB;
+    p.nshift = k3 ? 9 : 1;
+    p.sub_stride = k3 ? 126 : 128;
+    p.d_lead = k3 ? -1 : 0;
+    p.nacc = 512 / p.N; if (p.nacc > kMaxAcc) p.nacc = kMaxAcc;
+    p.w_bytes_cb = p.nshift * cp.Cin_total * p.N * 2;
+    p.kgroup_chunks = p.nchunks < 8 ? p.nchunks : 8;
+    p.wstage_bytes = p.kgroup_chunks * p.N * 16;
+    p.nwstages = 3;
+    p.nrows = (long long)cp.B * g.rows_per_sample;
+
+    const size_t fixed = kCtlBytes + kXchBytes + 256;
+    bool found = false;
+    size_t smem_total = 0;
+    for (int astages = kAStages; astages >= 1 && !found; --astages) {
+        for (int resident = 1; resident >= 0 && !found; --resident) {
+            const size_t wbytes = resident ? (size_t)p.w_bytes_cb : (size_t)p.nwstages * p.wstage_bytes;
+            for (int mt = 4; mt >= 1 && !found; --mt) {
+                if (resident ? (p.nacc < 2 && mt > 1) : (mt > p.nacc)) continue;
+                const int span = p.sub_stride * (mt - 1) + 128;
+                int nwin = 1, wrows = span, row0 = 0, win_dz = 0, off_dz = 0, off_dp = 0;
+                if (k3) {
+                    const int uni = span + 2 * g.plane + 2 * g.Rp, three = 3 * (span + 2 * g.Rp);
+                    if (uni <= three) { nwin = 1; wrows = uni; row0 = -(g.plane + g.Rp); win_dz = 0; off_dz = g.plane; off_dp = g.Rp; }
+                    else { nwin = 3; wrows = span + 2 * g.Rp; row0 = -g.Rp; win_dz = g.plane; off_dz = 0; off_dp = g.Rp; }
+                }
+                const size_t a_stage = (size_t)p.nchunks * nwin * wrows * 16;
+                const size_t total = fixed + (wbytes + 127) / 128 * 128 + astages * a_stage;
+                if (total > (size_t)max_smem) continue;
+                if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
+                p.resident = resident; p.MT = mt; p.nwin = nwin; p.wrows = wrows; p.row0 = row0; p.win_dz = win_dz;
+                p.off_dz = off_dz; p.off_dp = off_dp; p.a_stage_bytes = (int)a_stage; p.astages = astages;
+                smem_total = total;
+                found = true;
+            }
         }
     }
-    if (!best_mt) return 1;
-    p.MT = best_mt; p.nstages = best_stages;
-    p.wrows = 128 * p.MT + 2 * p.halo;
-    const long long tile_rows = 128LL * p.MT;
-    p.ntiles = (int)((p.nrows + tile_rows - 1) / tile_rows);
-    int cols = p.MT * cp.Cout, tc = 32;
-    while (tc < cols) tc <<= 1;
-    p.tmem_cols = tc;
-    p.idesc = (1u << 4) | ((uint32_t)(cp.Cout >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32, K-major A and B
-    int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_mma_kernel, kThreads, best_smem);
-    if (occ < 1) return 1;
-    if (occ * tc > 512) occ = 512 / tc;   // TMEM columns per SM
-    int grid = num_sms * occ;
-    if (grid > p.ntiles) grid = p.ntiles;
-    conv_mma_kernel<<<grid, kThreads, best_smem, st>>>(p);
-    return 0;
+    if (!found) return 1;
+    p.tile_rows = p.sub_stride * p.MT;
+    p.ntiles = (int)((p.nrows + p.tile_rows - 1) / p.tile_rows);
+    int ctas = num_sms;            // one persistent CTA per SM (the kernel owns all 512 TMEM columns)
+    if (ctas > p.ntiles) ctas = p.ntiles;
+    p.tiles_per_cta = (p.ntiles + ctas - 1) / ctas;
+    ctas = (p.ntiles + p.tiles_per_cta - 1) / p.tiles_per_cta;
+    p.idesc = (1u << 4) | ((uint32_t)(p.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32, K-major A and B
+    const int grid = ctas * p.ncb;
+    cudaError_t e = cudaSuccess;
+    switch (p.CB * 2 + (k3 ? 1 : 0)) {
+        case 16 * 2 + 1: e = launch_inst<16, true>(p, grid, smem_total, max_smem, st); break;
+        case 32 * 2 + 1: e = launch_inst<32, true>(p, grid, smem_total, max_smem, st); break;
+        case 48 * 2 + 1: e = launch_inst<48, true>(p, grid, smem_total, max_smem, st); break;
+        case 64 * 2 + 1: e = launch_inst<64, true>(p, grid, smem_total, max_smem, st); break;
+        case 16 * 2: e = launch_inst<16, false>(p, grid, smem_total, max_smem, st); break;
+        case 32 * 2: e = launch_inst<32, false>(p, grid, smem_total, max_smem, st); break;
+        case 48 * 2: e = launch_inst<48, false>(p, grid, smem_total, max_smem, st); break;
+        case 64 * 2: e = launch_inst<64, false>(p, grid, smem_total, max_smem, st); break;
+        default: return 1;
+    }
+    return e == cudaSuccess ? 0 : 1;
 }
 
 }  // namespace cd

@@ -99,6 +99,7 @@ struct cd_unet {
     float* unit_sigma = nullptr;
     // graph cache
     cudaGraphExec_t graph_exec = nullptr;
+    cudaStream_t capture_stream = nullptr;
     std::vector<unsigned char> graph_key;
     int64_t graph_nodes = 0;
 
@@ -176,15 +177,9 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         if ((int)b->data.size() != Cout) { fail("bias %s has unexpected size", bname.c_str()); return false; }
         out->bias = h->upload(b->data);
     }
-    if (want_mma && !transposed && (Cin_pad % 16 == 0) && (Cout % 16 == 0)) {
-        std::vector<__half> hp((size_t)taps * Cin_pad * Cout);
-        int kc_n = Cin_pad / 8;
-        for (int t = 0; t < taps; ++t)
-            for (int kc = 0; kc < kc_n; ++kc)
-                for (int n = 0; n < Cout; ++n)
-                    for (int j = 0; j < 8; ++j)
-                        hp[(((size_t)t * kc_n + kc) * Cout + n) * 8 + j] =
-                            __float2half_rn(pk[((size_t)t * Cin_pad + kc * 8 + j) * Cout + n]);
+    if (want_mma && !transposed && mma_conv_supported(Cin_pad, Cout, taps)) {
+        std::vector<__half> hp(mma_packed_elems(Cin_pad, Cout, taps));
+        mma_pack_weights(pk.data(), Cin_pad, Cout, taps, hp.data());
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
@@ -640,6 +635,7 @@ cd_unet* cd_unet_create(const cd_unet_desc* desc) {
 void cd_unet_destroy(cd_unet* h) {
     if (!h) return;
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    if (h->capture_stream) cudaStreamDestroy(h->capture_stream);
     for (cudaEvent_t ev : h->prof_evs) cudaEventDestroy(ev);
     for (void* p : h->dev_allocs) cudaFree(p);
     delete h;
@@ -854,10 +850,12 @@ extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_sca
         if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; }
         h->graph_key.clear();
         int64_t before = h->launches;
-        CD_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        int rc = enqueue_sample(h, a, st);
+        // capture on a private stream: the caller's stream may be the legacy default stream, which cannot capture
+        if (!h->capture_stream) CD_CUDA(cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
+        CD_CUDA(cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_sample(h, a, h->capture_stream);
         cudaGraph_t graph = nullptr;
-        cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        cudaError_t ce = cudaStreamEndCapture(h->capture_stream, &graph);
         h->graph_nodes = h->launches - before;
         h->launches = before;
         if (rc) { if (graph) cudaGraphDestroy(graph); return 1; }

@@ -46,7 +46,10 @@ void launch_fill_normal(float* out, long long n, int vps, unsigned long long see
                         cudaStream_t st);
 
 // tcgen05 implicit-GEMM convolution (cd_conv_mma.cu); returns 0 if the shape is supported and was launched
-struct MmaConvWeights;  // packed fp16 weights, see cd_conv_mma.cu
 int launch_conv_mma(const ConvParams& p, const __half* packed_w, cudaStream_t st);
+bool mma_conv_supported(int Cin, int Cout, int taps);
+size_t mma_packed_elems(int Cin, int Cout, int taps);
+// w: fp32 [tap][ci][co]; out: fp16 blocks in the layout the tcgen05 kernel streams (see cd_conv_mma.cu)
+void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out);
 
 }  // namespace cd
