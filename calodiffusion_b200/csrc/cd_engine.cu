@@ -37,7 +37,8 @@ struct HostTensor {
 struct ConvW {
     float* w = nullptr;      // [tap][ci][co] fp32 (generic kernel)
     float* bias = nullptr;   // [co]
-    __half* wmma = nullptr;  // [tap][ci/8][co][8] fp16 (tcgen05 kernel), only for stride-1 non-transposed convs
+    __half* wmma = nullptr;  // fp16 blocks for the R-stacked tcgen05 kernel (stride-1 3x3x3 / 1x1x1 convs)
+    __half* wgat = nullptr;  // fp16 [tap][kc][co][8] for the gather tcgen05 kernel (strided / transposed / thin-input convs)
     int Cin = 0, Cout = 0, kz = 1, kp = 1, kr = 1;
     int transposed = 0;
 };
@@ -152,7 +153,7 @@ static const HostTensor* find_w(cd_unet* h, const std::string& name) {
 
 // pack a conv weight; returns false (with error set) if missing / wrong shape
 static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& bname, int Cin_real, int Cin_pad, int Cout,
-                      int kz, int kp, int kr, int transposed, bool want_mma, ConvW* out) {
+                      int kz, int kp, int kr, int transposed, bool want_mma, ConvW* out, bool want_gather = false) {
     const HostTensor* w = find_w(h, wname);
     if (!w) { fail("missing weight %s", wname.c_str()); return false; }
     int64_t e0 = transposed ? Cin_real : Cout, e1 = transposed ? Cout : Cin_real;
@@ -182,6 +183,12 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         mma_pack_weights(pk.data(), Cin_pad, Cout, taps, hp.data());
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
+    }
+    if (want_gather && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {
+        std::vector<__half> hp(gather_packed_elems(Cin_pad, Cout, taps));
+        gather_pack_weights(pk.data(), Cin_pad, Cout, taps, hp.data());
+        out->wgat = h->dalloc<__half>(hp.size(), false);
+        if (out->wgat) cudaMemcpy(out->wgat, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
     return true;
 }
@@ -223,7 +230,7 @@ struct Builder {
             int taps = w.kz * w.kp * w.kr;
             char nm[96];
             snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : ""), w.Cin, w.Cout,
-                     level_out, (w.wmma && stride == 1 && !w.transposed && !write_halo) ? "_mma" : "_simt");
+                     level_out, (w.wmma && stride == 1 && !w.transposed && !write_halo) ? "_mma" : (w.wgat ? "_gather" : "_simt"));
             // FLOP = 2*MAC over output voxels as the reference executes them; bytes = fp16 in + out
             hh->op_info.push_back({nm, 2.0 * mo * w.Cin * w.Cout * taps, 2.0 * (mi * w.Cin + mo * w.Cout)});
         }
@@ -248,6 +255,9 @@ struct Builder {
             hh->launches += 1;
             if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed && !write_halo) {
                 if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
+            }
+            if (hh->conv_backend == 0 && w.wgat) {
+                if (launch_conv_gather(p, w.wgat, r.st) == 0) return;
             }
             launch_conv_generic(p, r.st);
         });
@@ -420,7 +430,7 @@ static int build_plan(cd_unet* h) {
         h->launches += 1;
     });
     ConvW cinit;
-    if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 8, ls[0], 3, 3, 3, 0, false, &cinit)) return 1;
+    if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 8, ls[0], 3, 3, 3, 0, false, &cinit, true)) return 1;
     int x = acquire(h, 0, ls[0]);
     b.conv(cinit, 0, 0, {tin_buf}, x, 1, 1, 1, 1, 1, -1);
     release(h, tin_buf);
@@ -441,7 +451,7 @@ static int build_plan(cd_unet* h) {
         skips.push_back(a);
         if (i < nl - 1) {
             ConvW cd_;
-            if (!pack_conv(h, p + "2.conv.weight", p + "2.conv.bias", cout_, cout_, cout_, 3, 4, 4, 0, false, &cd_)) return 1;
+            if (!pack_conv(h, p + "2.conv.weight", p + "2.conv.bias", cout_, cout_, cout_, 3, 4, 4, 0, false, &cd_, true)) return 1;
             x = acquire(h, i + 1, cout_);
             b.conv(cd_, i, i + 1, {a}, x, 2, 1, 1, 1, 1, -1);
         } else {
@@ -481,7 +491,7 @@ static int build_plan(cd_unet* h) {
             const HostTensor* wt = find_w(h, p + "2.convTrans.weight");
             if (!wt || wt->shape.size() != 5) return fail("missing weight %s2.convTrans.weight", p.c_str());
             ConvW cu;
-            if (!pack_conv(h, p + "2.convTrans.weight", p + "2.convTrans.bias", dim_in, dim_in, dim_in, (int)wt->shape[2], 4, 4, 1, false, &cu)) return 1;
+            if (!pack_conv(h, p + "2.convTrans.weight", p + "2.convTrans.bias", dim_in, dim_in, dim_in, (int)wt->shape[2], 4, 4, 1, false, &cu, true)) return 1;
             x = acquire(h, lev - 1, dim_in);
             b.conv(cu, lev, lev - 1, {a}, x, 2, 1, 1, 1, 1, -1);
             release(h, a);
@@ -894,7 +904,7 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
         h->weights["__test.b"] = bt;
     }
     ConvW cw;
-    bool okp = pack_conv(h, "__test.w", bias_host ? "__test.b" : "", Cin, Cin, Cout, ksize[0], ksize[1], ksize[2], transposed, true, &cw);
+    bool okp = pack_conv(h, "__test.w", bias_host ? "__test.b" : "", Cin, Cin, Cout, ksize[0], ksize[1], ksize[2], transposed, true, &cw, true);
     h->weights.clear();
     if (!okp) return 1;
     __half *xin = nullptr, *yout = nullptr;
@@ -917,6 +927,9 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     int rc = 0;
     if (backend == 0) {
         if (!cw.wmma || launch_conv_mma(p, cw.wmma, st) != 0) rc = fail("tcgen05 conv does not support this shape");
+    } else if (backend == 2) {
+        p.write_halo = 1;
+        if (!cw.wgat || launch_conv_gather(p, cw.wgat, st) != 0) rc = fail("gather tcgen05 conv does not support this shape");
     } else {
         launch_conv_generic(p, st);
     }

@@ -47,6 +47,11 @@ void launch_fill_normal(float* out, long long n, int vps, unsigned long long see
 
 // tcgen05 implicit-GEMM convolution (cd_conv_mma.cu); returns 0 if the shape is supported and was launched
 int launch_conv_mma(const ConvParams& p, const __half* packed_w, cudaStream_t st);
+// tcgen05 gather implicit GEMM for strided / transposed / thin-input convolutions (cd_conv_gather.cu)
+int launch_conv_gather(const ConvParams& p, const __half* packed_w, cudaStream_t st);
+bool gather_conv_supported(int Cin, int Cout);
+size_t gather_packed_elems(int Cin, int Cout, int taps);
+void gather_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out);
 bool mma_conv_supported(int Cin, int Cout, int taps);
 size_t mma_packed_elems(int Cin, int Cout, int taps);
 // w: fp32 [tap][ci][co]; out: fp16 blocks in the layout the tcgen05 kernel streams (see cd_conv_mma.cu)

@@ -113,7 +113,7 @@ int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t s
 int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,
                  const int* stride, int transposed, const float* w_host, const float* bias_host,
                  const float* x_dev /* (B,Cin,Z,P,R) fp32 */, float* y_dev /* (B,Cout,Zo,Po,Ro) fp32 */,
-                 int B, int backend, void* stream);
+                 int B, int backend /* 0 R-stacked tcgen05, 1 SIMT, 2 gather tcgen05 */, void* stream);
 int cd_level_shape(const cd_unet* h, int level, int* zpr /* [3] */);
 
 #ifdef __cplusplus

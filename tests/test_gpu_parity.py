@@ -89,6 +89,25 @@ def test_generic_conv_variants(models, case):
 
 
 @pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
+def test_gather_tcgen05_conv_variants(models, case):
+    """The gather tcgen05 kernel (backend 2): strided Downsample, transposed Upsample, thin-input stride-1 convs."""
+    m, c = models(case)
+    lib = m._lib
+    errs = {}
+    errs["k3_l0_8_32"] = _conv_case(m, lib, 0, 0, 8, 32, (3, 3, 3), (1, 1, 1), False, 2)
+    errs["k3_l1_32_64"] = _conv_case(m, lib, 1, 1, 32, 64, (3, 3, 3), (1, 1, 1), False, 2)
+    errs["k1_l2_64_32"] = _conv_case(m, lib, 2, 2, 64, 32, (1, 1, 1), (1, 1, 1), False, 2)
+    errs["down_l0"] = _conv_case(m, lib, 0, 1, 32, 32, (3, 4, 4), (2, 2, 2), False, 2)
+    errs["down_l1"] = _conv_case(m, lib, 1, 2, 64, 64, (3, 4, 4), (2, 2, 2), False, 2)
+    for lev in (2, 1):
+        zk = 4 if _level_z(m, lev - 1) % 2 == 0 else 3
+        errs[f"up_l{lev}_32"] = _conv_case(m, lib, lev, lev - 1, 32, 32, (zk, 4, 4), (2, 2, 2), True, 2)
+        errs[f"up_l{lev}_64"] = _conv_case(m, lib, lev, lev - 1, 64, 64, (zk, 4, 4), (2, 2, 2), True, 2)
+    print(case, {k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
+@pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
 def test_tcgen05_conv_variants(models, case):
     """The tcgen05/TMEM implicit-GEMM kernel (backend 0) vs torch fp32 on fp16-rounded operands."""
     m, c = models(case)
