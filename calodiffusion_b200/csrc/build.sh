@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")"
 OUT=../libcalodiffusion_b200.so
-FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
+FLAGS="$CD_EXTRA -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
 pids=()
 for f in cd_kernels cd_conv_mma cd_conv_gather cd_engine; do
   nvcc $FLAGS -c $f.cu -o $f.o &

@@ -191,10 +191,14 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
         // ===================== MMA issuer =====================
         if (lane == 0) {
             uint32_t n = 0, tcount = 0;
+            const uint64_t adesc_hi = g_make_desc(0, 2048u, 128u);
+            const uint64_t bdesc_hi = g_make_desc(0, (uint32_t)N * 16u, 128u);
+            const uint32_t bstep = (2u * N * 16u) >> 4;
             for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++tcount) {
                 const GClass& c = p.cls[find_class(p, tile)];
                 const int nst = (c.ntaps + G - 1) / G;
                 const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
+                const uint32_t dcol = tmem_base + acc * 256;
                 g_mbar_wait(g_smem_u32(&ctl->t_empty[acc]), aph ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 uint32_t accum = 0;
@@ -204,16 +208,10 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                     const int nt = c.ntaps - t0 < G ? c.ntaps - t0 : G;
                     g_mbar_wait(g_smem_u32(&ctl->full[slot]), ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    for (int gi = 0; gi < nt; ++gi) {
-                        const uint32_t a0 = abuf_s + slot * p.a_stage_bytes + (uint32_t)(gi * NCH) * 2048u;
-                        const uint32_t b0 = wbuf_s + slot * p.w_stage_bytes + gi * p.w_tap_bytes;
-#pragma unroll
-                        for (int q = 0; q < NCH / 2; ++q) {
-                            const uint64_t ad = g_make_desc(a0 + (uint32_t)(2 * q) * 2048u, 2048u, 128u);
-                            const uint64_t bd = g_make_desc(b0 + (uint32_t)(2 * q) * N * 16u, (uint32_t)N * 16u, 128u);
-                            g_umma_f16(tmem_base + acc * 256, ad, bd, p.idesc, accum);
-                            accum = 1;
-                        }
+                    uint32_t al = (abuf_s + slot * p.a_stage_bytes) >> 4, bl = (wbuf_s + slot * p.w_stage_bytes) >> 4;
+                    for (int e = 0; e < nt * (NCH / 2); ++e, al += 256u, bl += bstep) {   // stage layouts are contiguous in (tap, k16)
+                        g_umma_f16(dcol, adesc_hi | al, bdesc_hi | bl, p.idesc, accum);
+                        accum = 1;
                     }
                     g_umma_commit(g_smem_u32(&ctl->empty[slot]));
                 }

@@ -25,15 +25,31 @@
 //     kept in registers across the CTA's consecutive tiles and flushed with double atomics on sample change.
 #include <cuda.h>
 #include <cstdio>
+#include <cstdlib>
 
 #include "cd_kernels.cuh"
 
 namespace cd {
 
+#ifdef CD_MMA_DEBUG
+__device__ long long g_mma_dbg[16];
+#define DBG_T() clock64()
+#define DBG_ADD(i, v) dbg_local[i] += (v)
+#define DBG_DECL() long long dbg_local[16] = {0}
+#define DBG_FLUSH(cond) do { if (cond) for (int i_ = 0; i_ < 16; ++i_) if (dbg_local[i_]) atomicAdd((unsigned long long*)&g_mma_dbg[i_], (unsigned long long)dbg_local[i_]); } while (0)
+#else
+#define DBG_T() 0LL
+#define DBG_ADD(i, v)
+#define DBG_DECL()
+#define DBG_FLUSH(cond)
+#endif
+
 namespace {
 
 constexpr int kEpiWarps = 8;                    // 2 groups x 4 lane quarters
-constexpr int kThreads = 64 + 32 * kEpiWarps;   // warp 0: loads, warp 1: MMA issue + TMEM alloc, warps 2..9: epilogue
+constexpr int kIssuers = 2;                     // MMA-issuing warps (one elected thread each), alternating sub-tiles
+constexpr int kFirstEpiWarp = 1 + kIssuers;
+constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);   // warp 0: loads, warps 1-2: MMA issue (warp 1 owns TMEM), warps 3..10: epilogue
 constexpr int kMaxWStages = 4;
 constexpr int kAStages = 2;
 constexpr int kMaxAcc = 8;
@@ -70,6 +86,8 @@ struct MmaParams {
     int ntiles;
     int tiles_per_cta;
     uint32_t idesc;
+    uint32_t fd_mul[3], fd_shift[3];   // fast division by rows_per_sample, plane, Rp: q = (umulhi(n, mul) + n) >> shift, n < 2^31
+    int dbg_mode;           // CD_MMA_DEBUG builds only: 1 = epilogue does nothing but release slots, 2 = load A only once
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -130,6 +148,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 struct SmemCtl {
     uint64_t a_full[kAStages], a_empty[kAStages];
     uint64_t t_full[kMaxAcc], t_empty[kMaxAcc];
@@ -139,7 +166,8 @@ struct SmemCtl {
     uint32_t pad;
 };
 constexpr int kCtlBytes = 512;
-constexpr int kXchBytes = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64 * 4;   // 8 KB
+constexpr int kXchFloats = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64;
+constexpr int kXchBytes = kXchFloats * 4 + 256;   // 8 KB exchange + 64 floats of bias
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
 // sum over the 32 lanes of v[c] for every c in [0,32): lane l returns the total of channel l (31 shuffles)
@@ -169,11 +197,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Geom& g = p.g;
     constexpr int N = K3 ? 3 * CB : CB;
+    DBG_DECL();
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), 1); }
+        for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), kIssuers); }
         for (int s = 0; s < kMaxAcc; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 4); }
-        for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), 1); }
+        for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), kIssuers); }
         mbar_init(smem_u32(&ctl->w_res), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -185,6 +214,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = ctl->tmem_base;
+    // accumulator slot of sub-tile n: even sub-tiles (issuer 0 / epilogue group 0) and odd ones (issuer 1 / group 1)
+    // own disjoint halves of the slot ring, so every slot's full/empty chain has one producer and one consumer
+    const uint32_t hacc = (uint32_t)p.nacc >> 1;
+    auto slot_of = [&](uint32_t n) { return 2u * ((n >> 1) % hacc) + (n & 1u); };
+    auto phase_of = [&](uint32_t n) { return ((n >> 1) / hacc) & 1u; };
 
     const int cb = blockIdx.x % p.ncb;
     const int cta = blockIdx.x / p.ncb;
@@ -214,6 +248,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 const uint32_t ph = (it / p.astages) & 1;
                 const long long d0 = (long long)tile * p.tile_rows + p.d_lead;
                 mbar_wait(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
+#ifdef CD_MMA_DEBUG
+                if ((p.dbg_mode & 2) && it >= p.astages) { mbar_arrive(smem_u32(&ctl->a_full[stage])); continue; }
+#endif
                 mbar_expect_tx(smem_u32(&ctl->a_full[stage]), p.a_stage_bytes);
                 int ch = 0;
                 for (int s = 0; s < 2; ++s) {
@@ -242,108 +279,159 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer (one thread) =====================
+    } else if (warp < kFirstEpiWarp) {
+        // ===================== MMA issuers (one thread of each of two warps) =====================
+        // A single thread cannot issue M128xN96xK16 MMAs with changing descriptors faster than one per ~105 clk
+        // (measured, scripts/mma_microbench.cu: descriptor arithmetic -> R2UR -> UTCHMMA is a serial chain), while the
+        // tensor pipe executes one in 56 clk.  Two issuing warps, each owning every other sub-tile (its own TMEM
+        // accumulator slot), reach the 56 clk execution bound.  All offsets are precomputed in 16-byte descriptor units.
         if (lane == 0) {
+            const uint32_t iw = warp - 1;
+            constexpr int NS = K3 ? 9 : 1;
+            uint32_t soff[NS];
+#pragma unroll
+            for (int s = 0; s < NS; ++s) {
+                const int a = K3 ? s / 3 : 1, b = K3 ? s % 3 : 1;
+                const int win = p.nwin == 3 ? a : 0;
+                const int rowoff = -p.row0 + (a - 1) * p.off_dz + (b - 1) * p.off_dp;
+                soff[s] = (uint32_t)(win * (int)win_bytes + rowoff * 16) >> 4;
+            }
+            const uint64_t adesc_hi = make_desc(0, chunk_bytes, 128u);
+            const uint64_t bdesc_hi = make_desc(0, (uint32_t)N * 16u, 128u);
+            const uint32_t qstep = (2u * chunk_bytes) >> 4, bstep = (2u * N * 16u) >> 4;
+            const uint32_t jstep = ((uint32_t)p.sub_stride * 16u) >> 4;
+            const int nq = p.nchunks >> 1;
             uint32_t cnt = 0, wcount = 0;
             if (p.resident) mbar_wait(smem_u32(&ctl->w_res), 0);
             for (int it = 0; it < my_tiles; ++it) {
                 const int stage = it % p.astages;
                 const uint32_t ph = (it / p.astages) & 1;
-                const uint32_t a_base = abuf_s + stage * p.a_stage_bytes;
+                const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
+                const long long tA = DBG_T();
                 mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
+                if (blockIdx.x == 0 && iw == 0) { DBG_ADD(0, DBG_T() - tA); DBG_ADD(3, 1); }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                bool issued = false;
                 if (p.resident) {
                     for (int j = 0; j < p.MT; ++j, ++cnt) {
-                        const uint32_t slot = cnt % p.nacc, tph = (cnt / p.nacc) & 1;
+                        if ((cnt & 1u) != iw) continue;
+                        const uint32_t a_lo = a_lo0 + (uint32_t)j * jstep;
+                        const uint32_t slot = slot_of(cnt), tph = phase_of(cnt);
+                        const uint32_t dcol = tmem_base + slot * N;
+                        const long long tB = DBG_T();
                         mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                        const long long tC = DBG_T();
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        uint32_t accum = 0;
-                        for (int s = 0; s < p.nshift; ++s) {
-                            const int a = K3 ? s / 3 : 1, b = K3 ? s % 3 : 1;
-                            const int win = p.nwin == 3 ? a : 0;
-                            const int rowoff = -p.row0 + (a - 1) * p.off_dz + (b - 1) * p.off_dp + j * p.sub_stride;
-                            const uint32_t a_row0 = a_base + win * win_bytes + (uint32_t)rowoff * 16u;
-                            const uint32_t b0 = wbuf_s + (uint32_t)(s * p.nchunks) * N * 16u;
-                            for (int q = 0; q < (p.nchunks >> 1); ++q) {
-                                const uint64_t ad = make_desc(a_row0 + (uint32_t)(2 * q) * chunk_bytes, chunk_bytes, 128u);
-                                const uint64_t bd = make_desc(b0 + (uint32_t)(2 * q) * N * 16u, (uint32_t)N * 16u, 128u);
-                                umma_f16(tmem_base + slot * N, ad, bd, p.idesc, accum);
-                                accum = 1;
-                            }
+                        uint32_t b_lo = wbuf_s >> 4;
+#pragma unroll
+                        for (int s = 0; s < NS; ++s) {
+                            uint32_t al = a_lo + soff[s];
+                            for (int q = 0; q < nq; ++q, al += qstep, b_lo += bstep)
+                                umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (s | q) != 0);
                         }
                         umma_commit(smem_u32(&ctl->t_full[slot]));
+                        issued = true;
+                        if (blockIdx.x == 0 && iw == 0) { DBG_ADD(1, tC - tB); DBG_ADD(2, DBG_T() - tC); }
                     }
                 } else {
                     for (int j = 0; j < p.MT; ++j) {
-                        const uint32_t n = cnt + j, slot = n % p.nacc, tph = (n / p.nacc) & 1;
-                        mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                        const uint32_t n = cnt + j, slot = slot_of(n), tph = phase_of(n);
+                        if ((n & 1u) == iw) mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
                     }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    for (int s = 0; s < p.nshift; ++s) {
-                        const int a = K3 ? s / 3 : 1, b = K3 ? s % 3 : 1;
-                        const int win = p.nwin == 3 ? a : 0;
+#pragma unroll
+                    for (int s = 0; s < NS; ++s) {
                         for (int kg = 0; kg < nkg; ++kg, ++wcount) {
                             const uint32_t ws = wcount % p.nwstages, wph = (wcount / p.nwstages) & 1;
                             const int kc0 = kg * p.kgroup_chunks;
                             const int kcn = (p.nchunks - kc0) < p.kgroup_chunks ? (p.nchunks - kc0) : p.kgroup_chunks;
                             mbar_wait(smem_u32(&ctl->w_full[ws]), wph);
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                            const uint32_t b0 = wbuf_s + ws * p.wstage_bytes;
+                            const uint32_t b_lo0 = (wbuf_s + ws * p.wstage_bytes) >> 4;
+                            const uint32_t a_lo1 = a_lo0 + soff[s] + (uint32_t)kc0 * (chunk_bytes >> 4);
+                            bool used = false;
                             for (int j = 0; j < p.MT; ++j) {
-                                const uint32_t slot = (cnt + j) % p.nacc;
-                                const int rowoff = -p.row0 + (a - 1) * p.off_dz + (b - 1) * p.off_dp + j * p.sub_stride;
-                                const uint32_t a_row0 = a_base + win * win_bytes + (uint32_t)rowoff * 16u;
-                                for (int q = 0; q < (kcn >> 1); ++q) {
-                                    const uint64_t ad = make_desc(a_row0 + (uint32_t)(kc0 + 2 * q) * chunk_bytes, chunk_bytes, 128u);
-                                    const uint64_t bd = make_desc(b0 + (uint32_t)(2 * q) * N * 16u, (uint32_t)N * 16u, 128u);
-                                    umma_f16(tmem_base + slot * N, ad, bd, p.idesc, (s | kg | q) != 0);
-                                }
+                                if (((cnt + j) & 1u) != iw) continue;
+                                const uint32_t dcol = tmem_base + slot_of(cnt + j) * N;
+                                uint32_t al = a_lo1 + (uint32_t)j * jstep, b_lo = b_lo0;
+                                for (int q = 0; q < (kcn >> 1); ++q, al += qstep, b_lo += bstep)
+                                    umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (s | kg | q) != 0);
+                                used = true;
                             }
-                            umma_commit(smem_u32(&ctl->w_empty[ws]));
+                            if (used) umma_commit(smem_u32(&ctl->w_empty[ws]));
+                            else mbar_arrive(smem_u32(&ctl->w_empty[ws]));
+                            issued = issued || used;
                         }
                     }
-                    for (int j = 0; j < p.MT; ++j) umma_commit(smem_u32(&ctl->t_full[(cnt + j) % p.nacc]));
+                    for (int j = 0; j < p.MT; ++j)
+                        if (((cnt + j) & 1u) == iw) umma_commit(smem_u32(&ctl->t_full[slot_of(cnt + j)]));
                     cnt += p.MT;
                 }
-                umma_commit(smem_u32(&ctl->a_empty[stage]));
+                if (issued) umma_commit(smem_u32(&ctl->a_empty[stage]));
+                else mbar_arrive(smem_u32(&ctl->a_empty[stage]));
             }
         }
     } else {
         // ===================== epilogue: TMEM -> registers -> global (+ GroupNorm statistics) =====================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read (warp id % 4)
-        const int group = (warp - 2) >> 2;        // 0 / 1: the two groups alternate sub-tiles
+        const int group = (warp - kFirstEpiWarp) >> 2;   // 0 / 1: the two groups alternate sub-tiles
         const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
         constexpr int CBP = (CB + 31) / 32 * 32;  // channels padded to whole 32-blocks for the butterfly
         constexpr int NB = CBP / 32;
-        float bias[CB];
+        constexpr bool TS = CB <= 32;             // per-thread statistics accumulators fit the register budget
+        float* sbias = xch + kXchFloats;          // bias of this channel block, broadcast-read from shared memory
+        for (int c = threadIdx.x - 32 * kFirstEpiWarp; c < CB; c += 32 * kEpiWarps) sbias[c] = p.bias ? __ldg(p.bias + cb * CB + c) : 0.f;
+        asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        float ts[TS ? CB : 1], tq[TS ? CB : 1];   // TS: this thread's running sum / sum of squares per channel (sample cur_b)
+        double run_s[NB], run_q[NB];              // !TS: lane l's running totals of channel blk*32+l
 #pragma unroll
-        for (int c = 0; c < CB; ++c) bias[c] = p.bias ? __ldg(p.bias + cb * CB + c) : 0.f;
-        double run_s[NB], run_q[NB];              // lane l: running sums of channel blk*32+l for sample cur_b
+        for (int c = 0; c < (TS ? CB : 1); ++c) { ts[c] = 0.f; tq[c] = 0.f; }
 #pragma unroll
         for (int b = 0; b < NB; ++b) { run_s[b] = 0.0; run_q[b] = 0.0; }
         int cur_b = -1;
-        auto flush = [&]() {
+        auto flush = [&]() {   // warp-uniform call sites only
             if (cur_b >= 0) {
 #pragma unroll
                 for (int b = 0; b < NB; ++b) {
+                    double s_tot = run_s[b], q_tot = run_q[b];
+                    if constexpr (TS) {
+                        float v[32], w[32];
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) { v[c] = (b * 32 + c < CB) ? ts[(b * 32 + c < CB) ? b * 32 + c : 0] : 0.f; w[c] = (b * 32 + c < CB) ? tq[(b * 32 + c < CB) ? b * 32 + c : 0] : 0.f; }
+                        s_tot = (double)butterfly32(v, lane);
+                        q_tot = (double)butterfly32(w, lane);
+                    }
                     const int c = b * 32 + lane;
                     if (c < CB) {
                         double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + c) * 2;
-                        atomicAdd(d, run_s[b]);
-                        atomicAdd(d + 1, run_q[b]);
+                        atomicAdd(d, s_tot);
+                        atomicAdd(d + 1, q_tot);
                     }
                     run_s[b] = 0.0; run_q[b] = 0.0;
+                }
+                if constexpr (TS) {
+#pragma unroll
+                    for (int c = 0; c < CB; ++c) { ts[c] = 0.f; tq[c] = 0.f; }
                 }
             }
         };
         const int total_sub = my_tiles * p.MT;
         for (int n = group; n < total_sub; n += 2) {
             const int tile = tile_begin + n / p.MT, j = n % p.MT;
-            const uint32_t slot = n % p.nacc, tph = (n / p.nacc) & 1;
+            const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
             const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
+            const long long tE0 = DBG_T();
             mbar_wait(smem_u32(&ctl->t_full[slot]), tph);
+            const long long tE1 = DBG_T();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#ifdef CD_MMA_DEBUG
+            if (p.dbg_mode & 1) {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+                continue;
+            }
+#endif
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * N;
             float acc[CBP];
 #pragma unroll
@@ -354,39 +442,42 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 float* xdn = xch + (size_t)(((group * 2 + par) * 2 + 1) * 4) * 64;
 #pragma unroll
                 for (int c0 = 0; c0 < CB; c0 += 16) {
-                    float t[16];
-                    tmem_ld16(taddr + CB + c0, t);
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[c0 + k] = t[k] + bias[c0 + k];
-                }
-#pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += 16) {        // D_0 of row m-1
-                    float t[16];
-                    tmem_ld16(taddr + c0, t);
+                    uint32_t r1[16], r0[16], r2[16];
+                    tmem_ld16_issue(taddr + CB + c0, r1);       // D_1 of row m
+                    tmem_ld16_issue(taddr + c0, r0);            // D_0 of row m-1 (held by the lane below)
+                    tmem_ld16_issue(taddr + 2 * CB + c0, r2);   // D_2 of row m+1 (held by the lane above)
+                    tmem_ld_wait();
                     if (lane == 31) {
 #pragma unroll
-                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<float4*>(xup + q * 64 + c0 + k) = make_float4(t[k], t[k + 1], t[k + 2], t[k + 3]);
+                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
                     }
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) { const float u = __shfl_up_sync(0xffffffffu, t[k], 1); if (lane > 0) acc[c0 + k] += u; }
-                }
-#pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += 16) {        // D_2 of row m+1
-                    float t[16];
-                    tmem_ld16(taddr + 2 * CB + c0, t);
                     if (lane == 0) {
 #pragma unroll
-                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<float4*>(xdn + q * 64 + c0 + k) = make_float4(t[k], t[k + 1], t[k + 2], t[k + 3]);
+                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
                     }
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) { const float u = __shfl_down_sync(0xffffffffu, t[k], 1); if (lane < 31) acc[c0 + k] += u; }
+                    for (int k = 0; k < 16; k += 4) {
+                        const float4 bv = *reinterpret_cast<const float4*>(sbias + c0 + k);
+                        const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float a = __uint_as_float(r1[k + e]) + bb[e];
+                            const float u = __uint_as_float(__shfl_up_sync(0xffffffffu, r0[k + e], 1));
+                            const float d = __uint_as_float(__shfl_down_sync(0xffffffffu, r2[k + e], 1));
+                            if (lane > 0) a += u;
+                            if (lane < 31) a += d;
+                            acc[c0 + k + e] = a;
+                        }
+                    }
                 }
                 // the accumulator slot is free again
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+                if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(9, DBG_T() - tE1);
                 // quarter-boundary rows: exchange through shared memory within the group
                 asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
+                if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
                 if (lane == 0 && q > 0) {
 #pragma unroll
                     for (int c = 0; c < CB; c += 4) { const float4 u = *reinterpret_cast<const float4*>(xup + (q - 1) * 64 + c); acc[c] += u.x; acc[c + 1] += u.y; acc[c + 2] += u.z; acc[c + 3] += u.w; }
@@ -398,22 +489,29 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             } else {
 #pragma unroll
                 for (int c0 = 0; c0 < CB; c0 += 16) {
-                    float t[16];
-                    tmem_ld16(taddr + c0, t);
+                    uint32_t r1[16];
+                    tmem_ld16_issue(taddr + c0, r1);
+                    tmem_ld_wait();
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[c0 + k] = t[k] + bias[c0 + k];
+                    for (int k = 0; k < 16; ++k) acc[c0 + k] = __uint_as_float(r1[k]) + sbias[c0 + k];
                 }
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
             }
-            // which output row is this?
+            // which output row is this?  (fast division by the level's constant extents)
             bool valid = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
             int sample = -1;
             if (valid) {
-                const RowInfo ri = decode_row(g, row);
-                valid = ri.kind == 0;
-                sample = ri.b;
+                const uint32_t ur = (uint32_t)row;
+                const uint32_t b = (__umulhi(ur, p.fd_mul[0]) + ur) >> p.fd_shift[0];
+                const uint32_t rem = ur - b * (uint32_t)g.rows_per_sample;
+                const uint32_t z = (__umulhi(rem, p.fd_mul[1]) + rem) >> p.fd_shift[1];
+                const uint32_t rem2 = rem - z * (uint32_t)g.plane;
+                const uint32_t pp = (__umulhi(rem2, p.fd_mul[2]) + rem2) >> p.fd_shift[2];
+                const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
+                valid = z < (uint32_t)g.Z && rr < (uint32_t)g.R && pp >= 1u && pp <= (uint32_t)g.P;
+                sample = (int)b;
             }
 #pragma unroll
             for (int k = 0; k < CB / 8; ++k) {
@@ -421,6 +519,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 if (valid) *reinterpret_cast<Half8*>(p.dst + plcp_offset(g, cb * (CB / 8) + k, row)) = h;
                 unpack8(h, acc + 8 * k);      // statistics of the values as stored
             }
+            if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
             if (p.stats) {
                 const unsigned vmask = __ballot_sync(0xffffffffu, valid);
                 if (vmask) {
@@ -428,13 +527,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     const bool uniform = __all_sync(0xffffffffu, !valid || sample == b_first);
                     if (uniform) {
                         if (b_first != cur_b) { flush(); cur_b = b_first; }
+                        if constexpr (TS) {
+                            if (valid) {
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) {
-                            float v[32], w[32];
+                                for (int c = 0; c < CB; ++c) { ts[c] += acc[c]; tq[c] = fmaf(acc[c], acc[c], tq[c]); }
+                            }
+                        } else {
 #pragma unroll
-                            for (int c = 0; c < 32; ++c) { const float x = valid ? acc[b * 32 + c] : 0.f; v[c] = x; w[c] = x * x; }
-                            run_s[b] += (double)butterfly32(v, lane);
-                            run_q[b] += (double)butterfly32(w, lane);
+                            for (int b = 0; b < NB; ++b) {
+                                float v[32], w[32];
+#pragma unroll
+                                for (int c = 0; c < 32; ++c) { const float x = valid ? acc[b * 32 + c] : 0.f; v[c] = x; w[c] = x * x; }
+                                run_s[b] += (double)butterfly32(v, lane);
+                                run_q[b] += (double)butterfly32(w, lane);
+                            }
                         }
                     } else {
                         // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
@@ -451,9 +557,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                 }
             }
+            if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) { DBG_ADD(4, tE1 - tE0); DBG_ADD(5, DBG_T() - tE1); DBG_ADD(6, 1); }
         }
         if (p.stats) flush();
     }
+    DBG_FLUSH(blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == kFirstEpiWarp));
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
@@ -536,11 +644,23 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.sub_stride = k3 ? 126 : 128;
     p.d_lead = k3 ? -1 : 0;
     p.nacc = 512 / p.N; if (p.nacc > kMaxAcc) p.nacc = kMaxAcc;
+    p.nacc &= ~1;          // even: the two issuer / epilogue-group pairs own disjoint halves
+    if (p.nacc < 2) return 1;
     p.w_bytes_cb = p.nshift * cp.Cin_total * p.N * 2;
     p.kgroup_chunks = p.nchunks < 8 ? p.nchunks : 8;
     p.wstage_bytes = p.kgroup_chunks * p.N * 16;
     p.nwstages = 3;
     p.nrows = (long long)cp.B * g.rows_per_sample;
+    if (p.nrows + 4096 >= (1LL << 31)) return 1;
+    {
+        const int divs[3] = {g.rows_per_sample, g.plane, g.Rp};
+        for (int i = 0; i < 3; ++i) {
+            int l = 0;
+            while ((1LL << l) < divs[i]) ++l;
+            p.fd_mul[i] = (uint32_t)((((1ULL << l) - (unsigned long long)divs[i]) << 32) / (unsigned long long)divs[i] + 1ULL);
+            p.fd_shift[i] = (uint32_t)l;
+        }
+    }
 
     const size_t fixed = kCtlBytes + kXchBytes + 256;
     bool found = false;
@@ -576,6 +696,10 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.tiles_per_cta = (p.ntiles + ctas - 1) / ctas;
     ctas = (p.ntiles + p.tiles_per_cta - 1) / p.tiles_per_cta;
     p.idesc = (1u << 4) | ((uint32_t)(p.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32, K-major A and B
+    p.dbg_mode = 0;
+#ifdef CD_MMA_DEBUG
+    if (const char* e = getenv("CD_DBG_MODE")) p.dbg_mode = atoi(e);
+#endif
     const int grid = ctas * p.ncb;
     cudaError_t e = cudaSuccess;
     switch (p.CB * 2 + (k3 ? 1 : 0)) {
@@ -591,5 +715,12 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     }
     return e == cudaSuccess ? 0 : 1;
 }
+
+#ifdef CD_MMA_DEBUG
+extern "C" void cd_debug_counters(long long* out, int reset) {
+    cudaMemcpyFromSymbol(out, g_mma_dbg, sizeof(long long) * 16);
+    if (reset) { long long z[16] = {0}; cudaMemcpyToSymbol(g_mma_dbg, z, sizeof(z)); }
+}
+#endif
 
 }  // namespace cd
