@@ -1,0 +1,356 @@
+// Linear attention (models/models.py:301-318; heads = 1, dim_head = 32) on a raw 96-channel PLCP qkv tensor
+// (chunk planes 0-3 q, 4-7 k, 8-11 v), per sample:
+//   k_max[d]   = max_n k[d,n]                                   (stabiliser of the softmax over voxels)
+//   S[d]       = sum_n exp(k[d,n]-k_max[d]),   Ctx[d][e] = sum_n exp(k[d,n]-k_max[d]) v[e,n]
+//   att[e,n]   = 32^-0.5 * sum_d Ctx[d][e]/S[d] * softmax_d(q[:,n])[d]
+//   y[c,n]     = sum_e Wout[c][e] att[e,n] + bout[c]            (to_out 1x1x1 conv, models.py:289-293)
+// Three HBM-bound passes.  The two 32x32xn contractions run on the tensor cores with warp-level mma.sync
+// (m16n8k16, fp16 operands, fp32 accumulate): they are 1 % of the model's FLOPs and each warp only has to keep up
+// with its own 16-byte-per-lane global loads, so a TMEM pipeline would add nothing.  Each warp stages the 32 rows
+// it is about to contract in its private shared-memory slab (80-byte row stride: conflict-free ldmatrix), so the
+// kernels need no block-wide barriers in their main loops.
+//   * attn_kmax:    streams k, warp-shuffle max, ordered-uint atomicMax.
+//   * attn_context: A = exp(k-k_max)^T via ldmatrix.trans, B = v via ldmatrix.trans; S is the same MMA against a
+//                   ones column, so numerator and denominator see identically rounded weights.
+//   * attn_out:     softmax_d(q) per lane in fp32 -> fp16 A operand; B = (Wout * (Ctx/S)^T * 32^-0.5) folded once
+//                   per block, so the second einsum and the to_out convolution are one 32 x C GEMM; epilogue adds the
+//                   bias, writes the raw C-channel tensor and accumulates the GroupNorm(1,C) statistics.
+#include "cd_kernels.cuh"
+
+namespace cd {
+namespace {
+
+__device__ __forceinline__ unsigned f2ord(float f) {
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned k) {
+    unsigned u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int kRowStrideB = 80;   // bytes per staged 32-channel fp16 row (64 B payload + 16 B pad)
+constexpr int kWarps = 8;
+
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) attn_kmax_kernel(Geom g, const __half* __restrict__ qkv, unsigned* __restrict__ kmax,
+                                                        int rows_per_block) {
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k = warp & 3;                 // k chunk of this warp
+    const uint32_t r0 = blockIdx.x * rows_per_block;
+    uint32_t r1 = r0 + rows_per_block;
+    if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const __half* plane = qkv + plcp_offset(g, 4 + k, (long long)b * g.rows_per_sample);
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (uint32_t base = r0 + (warp >> 2) * 32; base < r1; base += 4 * 64) {
+        Half8 v[4];
+        bool ok[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t rem = base + u * 64 + lane;
+            ok[u] = rem < r1;
+            if (ok[u]) v[u] = *reinterpret_cast<const Half8*>(plane + (long long)rem * 8);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t rem = base + u * 64 + lane;
+            if (ok[u] && decode_subrow(g, rem).kind == 0) {
+                float f[8];
+                unpack8(v[u], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m[j] = fmaxf(m[j], __shfl_xor_sync(0xffffffffu, m[j], o));
+        if (lane == 0 && m[j] > -INFINITY) atomicMax(kmax + b * 32 + k * 8 + j, f2ord(m[j]));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// ctx layout: [B][33][32] floats: rows 0..31 = Ctx[d][e], row 32 = S[d]
+__global__ void __launch_bounds__(256) attn_context_kernel(Geom g, const __half* __restrict__ qkv, const unsigned* __restrict__ kmax,
+                                                           float* __restrict__ ctx, int rows_per_block, int use_atomics) {
+    __shared__ __align__(16) unsigned char slab[kWarps][2][32 * kRowStrideB];   // per warp: exp(k) rows, v rows
+    __shared__ float red[33 * 32];
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 33 * 32; i += 256) red[i] = 0.f;
+    float km[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) km[c] = ord2f(kmax[b * 32 + c]);
+    __syncthreads();
+    const uint32_t r0 = blockIdx.x * rows_per_block;
+    uint32_t r1 = r0 + rows_per_block;
+    if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const __half* base_k = qkv + plcp_offset(g, 4, (long long)b * g.rows_per_sample);
+    const __half* base_v = qkv + plcp_offset(g, 8, (long long)b * g.rows_per_sample);
+    const long long cs = g.chunk_stride * 8;   // halves between chunk planes
+    unsigned char* sk = slab[warp][0];
+    unsigned char* sv = slab[warp][1];
+    const uint32_t sk_s = smem_u32(sk), sv_s = smem_u32(sv);
+    // ldmatrix.trans lane address: matrix lane/8 of (n 0-7|8-15) x (col 0-7|8-15): stored row = lane%8 + 8*((lane/8)/2)... see below
+    //   A (exp k):  m0 = (n 0-7, d 0-7), m1 = (n 0-7, d 8-15), m2 = (n 8-15, d 0-7), m3 = (n 8-15, d 8-15)
+    //   B (v):      m0 = (n 0-7, e 0-7), m1 = (n 8-15, e 0-7), m2 = (n 0-7, e 8-15), m3 = (n 8-15, e 8-15)
+    const int mi = lane >> 3, mr = lane & 7;
+    const uint32_t a_off = (uint32_t)((mr + 8 * (mi >> 1)) * kRowStrideB + (mi & 1) * 16);
+    const uint32_t b_off = (uint32_t)((mr + 8 * (mi & 1)) * kRowStrideB + (mi >> 1) * 16);
+    float acc[2][4][4];     // [m tile: d 0-15 / 16-31][n tile: e 8-blocks][frag]
+    float sacc[2][4];       // S: column 0 of an MMA against a ones column
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int f = 0; f < 4; ++f) acc[i][j][f] = 0.f;
+        }
+#pragma unroll
+        for (int f = 0; f < 4; ++f) sacc[i][f] = 0.f;
+    }
+    const uint32_t ones = (lane >> 2) == 0 ? 0x3C003C00u : 0u;   // B fragment of the ones column: n' = lane/4 == 0
+    for (uint32_t base = r0 + warp * 32; base < r1; base += kWarps * 32) {
+        const uint32_t rem = base + lane;
+        const bool inb = rem < r1;
+        Half8 kv[4], vv[4];
+        if (inb) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                kv[c] = *reinterpret_cast<const Half8*>(base_k + c * cs + (long long)rem * 8);
+                vv[c] = *reinterpret_cast<const Half8*>(base_v + c * cs + (long long)rem * 8);
+            }
+        }
+        const bool interior = inb && decode_subrow(g, rem).kind == 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float f[8];
+            if (interior) {
+                unpack8(kv[c], f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - km[c * 8 + j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = 0.f;
+                vv[c] = pack8(f);
+            }
+            *reinterpret_cast<Half8*>(sk + lane * kRowStrideB + c * 16) = pack8(f);
+            *reinterpret_cast<Half8*>(sv + lane * kRowStrideB + c * 16) = vv[c];
+        }
+        __syncwarp();
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {          // 16 rows (K) per step
+            uint32_t a[2][4], bf[2][4];
+            ldsm_x4_t(sk_s + ks * 16 * kRowStrideB + a_off, a[0]);
+            ldsm_x4_t(sk_s + ks * 16 * kRowStrideB + a_off + 32, a[1]);
+            ldsm_x4_t(sv_s + ks * 16 * kRowStrideB + b_off, bf[0]);
+            ldsm_x4_t(sv_s + ks * 16 * kRowStrideB + b_off + 32, bf[1]);
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                mma16816(acc[i][0], a[i], bf[0][0], bf[0][1]);
+                mma16816(acc[i][1], a[i], bf[0][2], bf[0][3]);
+                mma16816(acc[i][2], a[i], bf[1][0], bf[1][1]);
+                mma16816(acc[i][3], a[i], bf[1][2], bf[1][3]);
+                mma16816(sacc[i], a[i], ones, ones);
+            }
+        }
+        __syncwarp();
+    }
+    // cross-warp reduction in shared memory, then one global update per block
+    const int gq = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int d0 = i * 16 + gq, e0 = j * 8 + 2 * tq;
+            atomicAdd(&red[d0 * 32 + e0], acc[i][j][0]);
+            atomicAdd(&red[d0 * 32 + e0 + 1], acc[i][j][1]);
+            atomicAdd(&red[(d0 + 8) * 32 + e0], acc[i][j][2]);
+            atomicAdd(&red[(d0 + 8) * 32 + e0 + 1], acc[i][j][3]);
+        }
+        if (tq == 0) {
+            atomicAdd(&red[32 * 32 + i * 16 + gq], sacc[i][0]);
+            atomicAdd(&red[32 * 32 + i * 16 + gq + 8], sacc[i][2]);
+        }
+    }
+    __syncthreads();
+    float* c = ctx + (long long)b * 33 * 32;
+    for (int i = threadIdx.x; i < 33 * 32; i += 256) {
+        if (use_atomics) atomicAdd(c + i, red[i]);
+        else c[i] = red[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+template <int NT>   // output channel 8-blocks (C = 8*NT)
+__global__ void __launch_bounds__(256) attn_out_kernel(Geom g, const __half* __restrict__ qkv, const float* __restrict__ ctx,
+                                                       const float* __restrict__ wout /* [C][32] */, const float* __restrict__ bout,
+                                                       __half* __restrict__ dst, double* __restrict__ stats, int rows_per_block) {
+    constexpr int C = NT * 8;
+    __shared__ __align__(16) unsigned char sq[kWarps][32 * kRowStrideB];   // per warp: softmax(q) rows (A operand)
+    __shared__ __align__(16) unsigned char sb[C * kRowStrideB];            // folded B operand [c][d]
+    __shared__ float M[32][33];
+    __shared__ float red[2][kWarps];
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    {
+        const float* c = ctx + (long long)b * 33 * 32;
+        for (int i = threadIdx.x; i < 1024; i += 256) {
+            const int d = i >> 5, e = i & 31;
+            M[d][e] = c[i] / c[1024 + d] * 0.17677669529663687f;  // 32^-0.5
+        }
+        __syncthreads();
+        // sb[c][d] = sum_e Wout[c][e] * M[d][e]
+        for (int i = threadIdx.x; i < C * 32; i += 256) {
+            const int co = i >> 5, d = i & 31;
+            float a = 0.f;
+#pragma unroll 8
+            for (int e = 0; e < 32; ++e) a = fmaf(__ldg(wout + co * 32 + e), M[d][e], a);
+            *reinterpret_cast<__half*>(sb + co * kRowStrideB + d * 2) = __float2half_rn(a);
+        }
+        __syncthreads();
+    }
+    // B fragments (whole K = 32 per 8-channel block): one ldmatrix.x4 of rows c 0-7, 16-byte columns d 0-7|8-15|16-23|24-31
+    uint32_t bfrag[NT][4];
+    {
+        const int mi = lane >> 3, mr = lane & 7;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) ldsm_x4(smem_u32(sb) + (j * 8 + mr) * kRowStrideB + mi * 16, bfrag[j]);
+    }
+    float bias[NT][2];
+    const int gq = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) { bias[j][0] = __ldg(bout + j * 8 + 2 * tq); bias[j][1] = __ldg(bout + j * 8 + 2 * tq + 1); }
+    const uint32_t r0 = blockIdx.x * rows_per_block;
+    uint32_t r1 = r0 + rows_per_block;
+    if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const long long srow0 = (long long)b * g.rows_per_sample;
+    const __half* base_q = qkv + plcp_offset(g, 0, srow0);
+    const long long cs = g.chunk_stride * 8;
+    unsigned char* sqw = sq[warp];
+    const uint32_t sq_s = smem_u32(sqw);
+    // A fragment lane address (non-transposed): m0 = rows 0-7 cols 0-7, m1 = rows 8-15 cols 0-7, m2 = rows 0-7 cols 8-15, m3 = rows 8-15 cols 8-15
+    const uint32_t a_off = (uint32_t)(((lane & 7) + 8 * ((lane >> 3) & 1)) * kRowStrideB + (lane >> 4) * 16);
+    float ssum = 0.f, ssq = 0.f;
+    for (uint32_t base = r0 + warp * 32; base < r1; base += kWarps * 32) {
+        const uint32_t rem = base + lane;
+        const bool inb = rem < r1;
+        float q[32];
+        if (inb) {
+            Half8 qv[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) qv[c] = *reinterpret_cast<const Half8*>(base_q + c * cs + (long long)rem * 8);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) unpack8(qv[c], q + 8 * c);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) q[j] = 0.f;
+        }
+        const bool interior = inb && decode_subrow(g, rem).kind == 0;
+        const unsigned vmask = __ballot_sync(0xffffffffu, interior);
+        float mx = q[0];
+#pragma unroll
+        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, q[j]);
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { q[j] = __expf(q[j] - mx); sum += q[j]; }
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q[8 * c + j] *= inv;
+            *reinterpret_cast<Half8*>(sqw + lane * kRowStrideB + c * 16) = pack8(q + 8 * c);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {           // 16 rows per m tile
+            uint32_t a[2][4];
+            ldsm_x4(sq_s + mt * 16 * kRowStrideB + a_off, a[0]);        // d 0-15
+            ldsm_x4(sq_s + mt * 16 * kRowStrideB + a_off + 32, a[1]);   // d 16-31
+            const bool v0 = (vmask >> (mt * 16 + gq)) & 1u, v1 = (vmask >> (mt * 16 + gq + 8)) & 1u;
+            const long long row_a = srow0 + base + mt * 16 + gq;
+#pragma unroll
+            for (int j = 0; j < NT; ++j) {
+                float c4[4] = {bias[j][0], bias[j][1], bias[j][0], bias[j][1]};
+                mma16816(c4, a[0], bfrag[j][0], bfrag[j][1]);
+                mma16816(c4, a[1], bfrag[j][2], bfrag[j][3]);
+                const __half2 h0 = __floats2half2_rn(c4[0], c4[1]), h1 = __floats2half2_rn(c4[2], c4[3]);
+                __half* o = dst + plcp_offset(g, j, row_a) + 2 * tq;
+                if (v0) {
+                    *reinterpret_cast<__half2*>(o) = h0;
+                    const float2 f = __half22float2(h0);
+                    ssum += f.x + f.y; ssq = fmaf(f.x, f.x, fmaf(f.y, f.y, ssq));
+                }
+                if (v1) {
+                    *reinterpret_cast<__half2*>(o + 64) = h1;      // row + 8
+                    const float2 f = __half22float2(h1);
+                    ssum += f.x + f.y; ssq = fmaf(f.x, f.x, fmaf(f.y, f.y, ssq));
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (stats) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { ssum += __shfl_xor_sync(0xffffffffu, ssum, o); ssq += __shfl_xor_sync(0xffffffffu, ssq, o); }
+        if (lane == 0) { red[0][warp] = ssum; red[1][warp] = ssq; }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            double t = 0.0;
+            for (int i = 0; i < kWarps; ++i) t += (double)red[threadIdx.x][i];
+            atomicAdd(stats + (long long)b * C * 2 + threadIdx.x, t);   // GroupNorm(1,C): one group, channel-0 slot
+        }
+    }
+}
+
+}  // namespace
+
+bool attention_out_supported(int C) { return C == 16 || C == 32 || C == 64 || C == 96 || C == 128; }
+
+int launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, const float* wout, const float* bout,
+                     __half* dst, int C, double* stats, int B, cudaStream_t st) {
+    // kmax, ctx and stats must be zero on entry (the engine clears its scratch once per forward)
+    if (!attention_out_supported(C)) return 1;
+    {
+        const int rpb = 2048;
+        dim3 grid((g.rows_per_sample + rpb - 1) / rpb, B);
+        attn_kmax_kernel<<<grid, 256, 0, st>>>(g, qkv, kmax, rpb);
+    }
+    {
+        // ~2048 rows per block (partial sums merged with fp32 atomics); smaller pieces when the batch alone cannot fill the GPU
+        int rows = 2048;
+        while (rows > 512 && (long long)B * ((g.rows_per_sample + rows - 1) / rows) < 592) rows >>= 1;
+        const int nblk = (g.rows_per_sample + rows - 1) / rows;
+        dim3 grid(nblk, B);
+        attn_context_kernel<<<grid, 256, 0, st>>>(g, qkv, kmax, ctx, rows, nblk > 1 ? 1 : 0);
+    }
+    {
+        const int rows = 1024;
+        dim3 grid((g.rows_per_sample + rows - 1) / rows, B);
+        switch (C) {
+            case 16: attn_out_kernel<2><<<grid, 256, 0, st>>>(g, qkv, ctx, wout, bout, dst, stats, rows); break;
+            case 32: attn_out_kernel<4><<<grid, 256, 0, st>>>(g, qkv, ctx, wout, bout, dst, stats, rows); break;
+            case 64: attn_out_kernel<8><<<grid, 256, 0, st>>>(g, qkv, ctx, wout, bout, dst, stats, rows); break;
+            case 96: attn_out_kernel<12><<<grid, 256, 0, st>>>(g, qkv, ctx, wout, bout, dst, stats, rows); break;
+            case 128: attn_out_kernel<16><<<grid, 256, 0, st>>>(g, qkv, ctx, wout, bout, dst, stats, rows); break;
+        }
+    }
+    return 0;
+}
+
+}  // namespace cd

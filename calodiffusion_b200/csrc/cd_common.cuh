@@ -25,7 +25,19 @@ struct Geom {       // one U-Net resolution level
     int rows_per_sample;  // (Z+1)*plane
     int guard;      // zero rows before/after the payload in each chunk plane
     long long chunk_stride;  // rows per chunk plane incl. guards (fixed by max batch)
+    // exact division of n < 2^31 by plane / Rp / rows_per_sample:  q = (umulhi(n, mul) + n) >> shift
+    uint32_t fd_mul[3], fd_shift[3];
 };
+
+__host__ inline void geom_init_fastdiv(Geom& g) {
+    const int divs[3] = {g.plane, g.Rp, g.rows_per_sample};
+    for (int i = 0; i < 3; ++i) {
+        int l = 0;
+        while ((1LL << l) < divs[i]) ++l;
+        g.fd_mul[i] = (uint32_t)((((1ULL << l) - (unsigned long long)divs[i]) << 32) / (unsigned long long)divs[i] + 1ULL);
+        g.fd_shift[i] = (uint32_t)l;
+    }
+}
 
 struct TensorRef {  // a PLCP tensor
     __half* base;   // start of chunk plane 0 (guard included)
@@ -66,6 +78,26 @@ __device__ __forceinline__ RowInfo decode_row(const Geom& g, long long row) {
     return ri;
 }
 
+// Row index within one sample (rem < rows_per_sample) -> z, pp, rr and kind, with 32-bit fast divisions.
+struct SubRow { int z, pp, rr, kind; int src_delta; };
+__device__ __forceinline__ uint32_t fdiv(const Geom& g, int which, uint32_t n) {
+    return (__umulhi(n, g.fd_mul[which]) + n) >> g.fd_shift[which];
+}
+__device__ __forceinline__ SubRow decode_subrow(const Geom& g, uint32_t rem) {
+    SubRow s;
+    const uint32_t z = fdiv(g, 0, rem);
+    const uint32_t rem2 = rem - z * (uint32_t)g.plane;
+    const uint32_t pp = fdiv(g, 1, rem2);
+    const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
+    s.z = (int)z; s.pp = (int)pp; s.rr = (int)rr;
+    s.src_delta = 0;
+    if ((int)z == g.Z || (int)rr == g.R) s.kind = 2;
+    else if (pp == 0) { s.kind = 1; s.src_delta = g.P * g.Rp; }
+    else if ((int)pp == g.P + 1) { s.kind = 1; s.src_delta = -g.P * g.Rp; }
+    else s.kind = 0;
+    return s;
+}
+
 __host__ __device__ inline long long interior_row(const Geom& g, int b, int z, int p, int r) {
     return (((long long)b * (g.Z + 1) + z) * g.Pp + (p + 1)) * g.Rp + r;
 }
@@ -91,6 +123,7 @@ struct ConvParams {
     int transposed;
     int write_halo;     // 1: produce all rows incl. halos (gather form); 0: interior rows only
     double* stats;      // [B][Cout][2] (sum, sumsq) or nullptr
+    int stats_cpg;      // channels per GroupNorm group: producers may accumulate a whole group into its first channel slot
     int B;
 };
 

@@ -19,10 +19,14 @@
 //   * D: TMEM accumulator slots of 128 lanes x N fp32 columns, ring-buffered so the epilogue of one 128-row
 //     sub-tile overlaps the MMAs of the next.  Sub-tiles advance by 126 rows (rows 0 and 127 of a sub-tile lack
 //     their m-1 / m+1 neighbour).
-//   * Epilogue (2 groups of 4 warps): tcgen05.ld, R-recombination by shuffles (+ a 2x32-float shared-memory
-//     exchange at the warp-quarter boundaries), bias, fp16 rounding, coalesced PLCP stores of the interior rows,
-//     and the GroupNorm statistics (per sample and channel sum / sum of squares) by a butterfly transpose-reduce
-//     kept in registers across the CTA's consecutive tiles and flushed with double atomics on sample change.
+//   * Epilogue (2 groups of 4 warps): tcgen05.ld of D_0/D_1/D_2, R-recombination by two rotate-shuffles per channel:
+//     lane 31 / lane 0 first publish their D_0 / D_2 rows in shared memory and, after one 128-thread named barrier,
+//     replace them by the neighbouring warp-quarter's values, so the rotation delivers the right row to every lane
+//     without per-element selects or boundary fix-ups; then bias, fp16 rounding, coalesced PLCP stores of the interior
+//     rows (optionally also of their circular phi halo copies) and the GroupNorm statistics: per-thread fp32 sum /
+//     sum of squares per (sample, group of CPG channels), kept in registers across the CTA's consecutive tiles and
+//     flushed with a warp reduction + fp64 atomics on sample change (into the group's first channel slot).
+//     The 1x1x1 form has no recombination and no statistics: it streams 16 columns at a time.
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
@@ -86,7 +90,7 @@ struct MmaParams {
     int ntiles;
     int tiles_per_cta;
     uint32_t idesc;
-    uint32_t fd_mul[3], fd_shift[3];   // fast division by rows_per_sample, plane, Rp: q = (umulhi(n, mul) + n) >> shift, n < 2^31
+    int write_halo;         // 1: interior rows with pp == 1 / pp == P are also stored to their phi halo copies
     int dbg_mode;           // CD_MMA_DEBUG builds only: 1 = epilogue does nothing but release slots, 2 = load A only once
 };
 
@@ -167,25 +171,10 @@ struct SmemCtl {
 };
 constexpr int kCtlBytes = 512;
 constexpr int kXchFloats = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64;
-constexpr int kXchBytes = kXchFloats * 4 + 256;   // 8 KB exchange + 64 floats of bias
+constexpr int kXchBytes = kXchFloats * 4 + 512;   // 8 KB exchange + 128 floats of bias
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
-// sum over the 32 lanes of v[c] for every c in [0,32): lane l returns the total of channel l (31 shuffles)
-__device__ __forceinline__ float butterfly32(float* v, int lane) {
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const bool hi = (lane & off) != 0;
-#pragma unroll
-        for (int i = 0; i < off; ++i) {
-            const float send = hi ? v[i] : v[i + off];
-            const float keep = hi ? v[i + off] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-        }
-    }
-    return v[0];
-}
-
-template <int CB, bool K3>
+template <int CB, bool K3, int CPG>   // CPG: channels per GroupNorm group for the statistics (divides CB)
 __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem);
@@ -376,50 +365,53 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
         const int q = warp & 3;                   // TMEM lane quarter this warp may read (warp id % 4)
         const int group = (warp - kFirstEpiWarp) >> 2;   // 0 / 1: the two groups alternate sub-tiles
         const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
-        constexpr int CBP = (CB + 31) / 32 * 32;  // channels padded to whole 32-blocks for the butterfly
-        constexpr int NB = CBP / 32;
-        constexpr bool TS = CB <= 32;             // per-thread statistics accumulators fit the register budget
         float* sbias = xch + kXchFloats;          // bias of this channel block, broadcast-read from shared memory
         for (int c = threadIdx.x - 32 * kFirstEpiWarp; c < CB; c += 32 * kEpiWarps) sbias[c] = p.bias ? __ldg(p.bias + cb * CB + c) : 0.f;
         asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
-        float ts[TS ? CB : 1], tq[TS ? CB : 1];   // TS: this thread's running sum / sum of squares per channel (sample cur_b)
-        double run_s[NB], run_q[NB];              // !TS: lane l's running totals of channel blk*32+l
+        constexpr int NG = K3 ? CB / CPG : 1;     // statistics groups per channel block
+        float gs[NG], gq[NG];                     // this thread's running sum / sum of squares per group (sample cur_b)
 #pragma unroll
-        for (int c = 0; c < (TS ? CB : 1); ++c) { ts[c] = 0.f; tq[c] = 0.f; }
-#pragma unroll
-        for (int b = 0; b < NB; ++b) { run_s[b] = 0.0; run_q[b] = 0.0; }
+        for (int i = 0; i < NG; ++i) { gs[i] = 0.f; gq[i] = 0.f; }
         int cur_b = -1;
         auto flush = [&]() {   // warp-uniform call sites only
             if (cur_b >= 0) {
 #pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    double s_tot = run_s[b], q_tot = run_q[b];
-                    if constexpr (TS) {
-                        float v[32], w[32];
+                for (int i = 0; i < NG; ++i) {
+                    float s_tot = gs[i], q_tot = gq[i];
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) { v[c] = (b * 32 + c < CB) ? ts[(b * 32 + c < CB) ? b * 32 + c : 0] : 0.f; w[c] = (b * 32 + c < CB) ? tq[(b * 32 + c < CB) ? b * 32 + c : 0] : 0.f; }
-                        s_tot = (double)butterfly32(v, lane);
-                        q_tot = (double)butterfly32(w, lane);
+                    for (int o = 16; o > 0; o >>= 1) { s_tot += __shfl_xor_sync(0xffffffffu, s_tot, o); q_tot += __shfl_xor_sync(0xffffffffu, q_tot, o); }
+                    if (lane == 0) {
+                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + i * CPG) * 2;
+                        atomicAdd(d, (double)s_tot);
+                        atomicAdd(d + 1, (double)q_tot);
                     }
-                    const int c = b * 32 + lane;
-                    if (c < CB) {
-                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + c) * 2;
-                        atomicAdd(d, s_tot);
-                        atomicAdd(d + 1, q_tot);
-                    }
-                    run_s[b] = 0.0; run_q[b] = 0.0;
-                }
-                if constexpr (TS) {
-#pragma unroll
-                    for (int c = 0; c < CB; ++c) { ts[c] = 0.f; tq[c] = 0.f; }
+                    gs[i] = 0.f; gq[i] = 0.f;
                 }
             }
         };
+        const int halo_delta = g.P * g.Rp;
         const int total_sub = my_tiles * p.MT;
         for (int n = group; n < total_sub; n += 2) {
             const int tile = tile_begin + n / p.MT, j = n % p.MT;
             const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
             const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
+            // which output row is this?  (fast division by the level's constant extents)
+            bool valid = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
+            int sample = -1;
+            uint32_t pp = 0;
+            if (valid) {
+                const uint32_t ur = (uint32_t)row;
+                const uint32_t b = fdiv(g, 2, ur);
+                const uint32_t rem = ur - b * (uint32_t)g.rows_per_sample;
+                const uint32_t z = fdiv(g, 0, rem);
+                const uint32_t rem2 = rem - z * (uint32_t)g.plane;
+                pp = fdiv(g, 1, rem2);
+                const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
+                valid = z < (uint32_t)g.Z && rr < (uint32_t)g.R && pp >= 1u && pp <= (uint32_t)g.P;
+                sample = (int)b;
+            }
+            const bool halo_up = valid && p.write_halo && pp == 1u;               // copy to pp = P+1
+            const bool halo_dn = valid && p.write_halo && pp == (uint32_t)g.P;    // copy to pp = 0
             const long long tE0 = DBG_T();
             mbar_wait(smem_u32(&ctl->t_full[slot]), tph);
             const long long tE1 = DBG_T();
@@ -433,133 +425,133 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             }
 #endif
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * N;
-            float acc[CBP];
-#pragma unroll
-            for (int c = CB; c < CBP; ++c) acc[c] = 0.f;
             if constexpr (K3) {
+                constexpr int CW = CB < 32 ? CB : 32;      // channels recombined per pass (CB = 16, 32, 48, 64)
                 const int par = (n >> 1) & 1;
                 float* xup = xch + (size_t)(((group * 2 + par) * 2 + 0) * 4) * 64;
                 float* xdn = xch + (size_t)(((group * 2 + par) * 2 + 1) * 4) * 64;
+                // sample bookkeeping for the statistics (warp-uniform decisions)
+                bool uniform = true;
+                if (p.stats) {
+                    const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+                    if (vmask) {
+                        const int b_first = __shfl_sync(0xffffffffu, sample, __ffs(vmask) - 1);
+                        uniform = __all_sync(0xffffffffu, !valid || sample == b_first);
+                        if (uniform) { if (b_first != cur_b) { flush(); cur_b = b_first; } }
+                        else { flush(); cur_b = -1; }
+                    }
+                }
 #pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += 16) {
-                    uint32_t r1[16], r0[16], r2[16];
-                    tmem_ld16_issue(taddr + CB + c0, r1);       // D_1 of row m
-                    tmem_ld16_issue(taddr + c0, r0);            // D_0 of row m-1 (held by the lane below)
-                    tmem_ld16_issue(taddr + 2 * CB + c0, r2);   // D_2 of row m+1 (held by the lane above)
+                for (int c0 = 0; c0 < CB; c0 += CW) {
+                    constexpr int W = CW;
+                    const int w = (CB - c0) < W ? (CB - c0) : W;   // 16 for the tail of CB = 48
+                    uint32_t r0[W], r1[W], r2[W];
+#pragma unroll
+                    for (int k = 0; k < W; k += 16) {
+                        if (k < w) {
+                            tmem_ld16_issue(taddr + CB + c0 + k, r1 + k);       // D_1 of row m
+                            tmem_ld16_issue(taddr + c0 + k, r0 + k);            // D_0 of row m   (wanted by lane + 1)
+                            tmem_ld16_issue(taddr + 2 * CB + c0 + k, r2 + k);   // D_2 of row m   (wanted by lane - 1)
+                        }
+                    }
                     tmem_ld_wait();
+                    if (c0 + CW >= CB) {
+                        // last TMEM read of this sub-tile: the accumulator slot is free again
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+                    }
+                    // publish the rows the neighbouring quarters need, then adopt theirs
                     if (lane == 31) {
 #pragma unroll
-                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
+                        for (int k = 0; k < W; k += 4) if (k < w) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
                     }
                     if (lane == 0) {
 #pragma unroll
-                        for (int k = 0; k < 16; k += 4) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
+                        for (int k = 0; k < W; k += 4) if (k < w) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
+                    }
+                    asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
+                    if (lane == 31) {       // row m-1 of the next quarter's lane 0 is this quarter's lane 31; it receives lane 31's r0 by rotation
+                        const float* src = xup + (q > 0 ? q - 1 : 0) * 64 + c0;
+#pragma unroll
+                        for (int k = 0; k < W; k += 4) if (k < w) { const uint4 u = *reinterpret_cast<const uint4*>(src + k); r0[k] = u.x; r0[k + 1] = u.y; r0[k + 2] = u.z; r0[k + 3] = u.w; }
+                    }
+                    if (lane == 0) {
+                        const float* src = xdn + (q < 3 ? q + 1 : 3) * 64 + c0;
+#pragma unroll
+                        for (int k = 0; k < W; k += 4) if (k < w) { const uint4 u = *reinterpret_cast<const uint4*>(src + k); r2[k] = u.x; r2[k + 1] = u.y; r2[k + 2] = u.z; r2[k + 3] = u.w; }
+                    }
+                    const int src_up = (lane + 31) & 31, src_dn = (lane + 1) & 31;
+                    float acc[W];
+#pragma unroll
+                    for (int k = 0; k < W; k += 4) {
+                        if (k < w) {
+                            const float4 bv = *reinterpret_cast<const float4*>(sbias + c0 + k);
+                            const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float u = __uint_as_float(__shfl_sync(0xffffffffu, r0[k + e], src_up));
+                                const float d = __uint_as_float(__shfl_sync(0xffffffffu, r2[k + e], src_dn));
+                                acc[k + e] = (__uint_as_float(r1[k + e]) + bb[e]) + (u + d);
+                            }
+                        }
                     }
 #pragma unroll
-                    for (int k = 0; k < 16; k += 4) {
-                        const float4 bv = *reinterpret_cast<const float4*>(sbias + c0 + k);
-                        const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+                    for (int k = 0; k < W; k += 8) {
+                        if (k < w) {
+                            const Half8 h = pack8(acc + k);
+                            __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
+                            if (valid) *reinterpret_cast<Half8*>(o) = h;
+                            if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
+                            if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
+                        }
+                    }
+                    if (p.stats && valid) {
+                        if (uniform) {
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            float a = __uint_as_float(r1[k + e]) + bb[e];
-                            const float u = __uint_as_float(__shfl_up_sync(0xffffffffu, r0[k + e], 1));
-                            const float d = __uint_as_float(__shfl_down_sync(0xffffffffu, r2[k + e], 1));
-                            if (lane > 0) a += u;
-                            if (lane < 31) a += d;
-                            acc[c0 + k + e] = a;
+                            for (int k = 0; k < W; ++k)
+                                if (k < w) { gs[(c0 + k) / CPG] += acc[k]; gq[(c0 + k) / CPG] = fmaf(acc[k], acc[k], gq[(c0 + k) / CPG]); }
+                        } else {
+                            // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
+#pragma unroll
+                            for (int k = 0; k < W; ++k) {
+                                if (k < w) {
+                                    double* d = p.stats + ((long long)sample * p.Cout + cb * CB + ((c0 + k) / CPG) * CPG) * 2;
+                                    atomicAdd(d, (double)acc[k]);
+                                    atomicAdd(d + 1, (double)(acc[k] * acc[k]));
+                                }
+                            }
                         }
                     }
                 }
-                // the accumulator slot is free again
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
-                if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(9, DBG_T() - tE1);
-                // quarter-boundary rows: exchange through shared memory within the group
-                asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
-                if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
-                if (lane == 0 && q > 0) {
-#pragma unroll
-                    for (int c = 0; c < CB; c += 4) { const float4 u = *reinterpret_cast<const float4*>(xup + (q - 1) * 64 + c); acc[c] += u.x; acc[c + 1] += u.y; acc[c + 2] += u.z; acc[c + 3] += u.w; }
-                }
-                if (lane == 31 && q < 3) {
-#pragma unroll
-                    for (int c = 0; c < CB; c += 4) { const float4 u = *reinterpret_cast<const float4*>(xdn + (q + 1) * 64 + c); acc[c] += u.x; acc[c + 1] += u.y; acc[c + 2] += u.z; acc[c + 3] += u.w; }
-                }
             } else {
+                // 1x1x1: no recombination, no statistics: stream 16 columns at a time
 #pragma unroll
                 for (int c0 = 0; c0 < CB; c0 += 16) {
                     uint32_t r1[16];
                     tmem_ld16_issue(taddr + c0, r1);
                     tmem_ld_wait();
+                    if (c0 + 16 >= CB) {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
+                    }
+                    float acc[16];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[c0 + k] = __uint_as_float(r1[k]) + sbias[c0 + k];
-                }
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
-            }
-            // which output row is this?  (fast division by the level's constant extents)
-            bool valid = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
-            int sample = -1;
-            if (valid) {
-                const uint32_t ur = (uint32_t)row;
-                const uint32_t b = (__umulhi(ur, p.fd_mul[0]) + ur) >> p.fd_shift[0];
-                const uint32_t rem = ur - b * (uint32_t)g.rows_per_sample;
-                const uint32_t z = (__umulhi(rem, p.fd_mul[1]) + rem) >> p.fd_shift[1];
-                const uint32_t rem2 = rem - z * (uint32_t)g.plane;
-                const uint32_t pp = (__umulhi(rem2, p.fd_mul[2]) + rem2) >> p.fd_shift[2];
-                const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
-                valid = z < (uint32_t)g.Z && rr < (uint32_t)g.R && pp >= 1u && pp <= (uint32_t)g.P;
-                sample = (int)b;
-            }
+                    for (int k = 0; k < 16; ++k) acc[k] = __uint_as_float(r1[k]) + sbias[c0 + k];
 #pragma unroll
-            for (int k = 0; k < CB / 8; ++k) {
-                const Half8 h = pack8(acc + 8 * k);
-                if (valid) *reinterpret_cast<Half8*>(p.dst + plcp_offset(g, cb * (CB / 8) + k, row)) = h;
-                unpack8(h, acc + 8 * k);      // statistics of the values as stored
-            }
-            if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
-            if (p.stats) {
-                const unsigned vmask = __ballot_sync(0xffffffffu, valid);
-                if (vmask) {
-                    const int b_first = __shfl_sync(0xffffffffu, sample, __ffs(vmask) - 1);
-                    const bool uniform = __all_sync(0xffffffffu, !valid || sample == b_first);
-                    if (uniform) {
-                        if (b_first != cur_b) { flush(); cur_b = b_first; }
-                        if constexpr (TS) {
-                            if (valid) {
-#pragma unroll
-                                for (int c = 0; c < CB; ++c) { ts[c] += acc[c]; tq[c] = fmaf(acc[c], acc[c], tq[c]); }
-                            }
-                        } else {
-#pragma unroll
-                            for (int b = 0; b < NB; ++b) {
-                                float v[32], w[32];
-#pragma unroll
-                                for (int c = 0; c < 32; ++c) { const float x = valid ? acc[b * 32 + c] : 0.f; v[c] = x; w[c] = x * x; }
-                                run_s[b] += (double)butterfly32(v, lane);
-                                run_q[b] += (double)butterfly32(w, lane);
-                            }
-                        }
-                    } else {
-                        // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
-                        flush();
-                        cur_b = -1;
-                        if (valid) {
-#pragma unroll
-                            for (int c = 0; c < CB; ++c) {
-                                double* d = p.stats + ((long long)sample * p.Cout + cb * CB + c) * 2;
-                                atomicAdd(d, (double)acc[c]);
-                                atomicAdd(d + 1, (double)(acc[c] * acc[c]));
-                            }
-                        }
+                    for (int k = 0; k < 16; k += 8) {
+                        const Half8 h = pack8(acc + k);
+                        __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
+                        if (valid) *reinterpret_cast<Half8*>(o) = h;
+                        if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
+                        if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
                     }
                 }
             }
             if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) { DBG_ADD(4, tE1 - tE0); DBG_ADD(5, DBG_T() - tE1); DBG_ADD(6, 1); }
         }
-        if (p.stats) flush();
+        if (K3 && p.stats) flush();
     }
     DBG_FLUSH(blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == kFirstEpiWarp));
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -574,21 +566,22 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 // ---------------------------------------------------------------------------------------------------------
 // host side: weight packing, tile planning, launch
 // ---------------------------------------------------------------------------------------------------------
-static int pick_cb(int Cout) {
+static int pick_cb(int Cout, int taps) {
+    if (taps == 1) return (Cout % 16 == 0 && Cout <= 128) ? Cout : 0;   // 1x1x1: one pass over the input, N = C_out
     const int cands[4] = {64, 48, 32, 16};
     for (int c : cands) if (Cout % c == 0) return c;
     return 0;
 }
 
 bool mma_conv_supported(int Cin, int Cout, int taps) {
-    return (taps == 27 || taps == 1) && Cin % 16 == 0 && Cin >= 16 && Cout % 16 == 0 && pick_cb(Cout) > 0;
+    return (taps == 27 || taps == 1) && Cin % 16 == 0 && Cin >= 16 && Cout % 16 == 0 && pick_cb(Cout, taps) > 0;
 }
 
 size_t mma_packed_elems(int Cin, int Cout, int taps) { return (size_t)taps * Cin * Cout; }
 
 // w: fp32 [tap][ci][co] (tap = (a*3+b)*3+c for 3x3x3).  out: fp16 [cb][shift][kc][n][8], n = g*CB + co_local
 void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out) {
-    const int CB = pick_cb(Cout), ncb = Cout / CB, nkc = Cin / 8;
+    const int CB = pick_cb(Cout, taps), ncb = Cout / CB, nkc = Cin / 8;
     const int nshift = taps == 27 ? 9 : 1, ng = taps == 27 ? 3 : 1, N = ng * CB;
     for (int cb = 0; cb < ncb; ++cb)
         for (int s = 0; s < nshift; ++s)
@@ -602,15 +595,15 @@ void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out) 
                     }
 }
 
-template <int CB, bool K3>
+template <int CB, bool K3, int CPG>
 static cudaError_t launch_inst(const MmaParams& p, int grid, size_t smem, int max_smem, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(conv_mma_kernel<CB, K3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        cudaError_t e = cudaFuncSetAttribute(conv_mma_kernel<CB, K3, CPG>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    conv_mma_kernel<CB, K3><<<grid, kThreads, smem, st>>>(p);
+    conv_mma_kernel<CB, K3, CPG><<<grid, kThreads, smem, st>>>(p);
     return cudaSuccess;
 }
 
@@ -622,6 +615,8 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     if (!mma_conv_supported(cp.Cin_total, cp.Cout, taps)) return 1;
     if (cp.gin.Z != cp.gout.Z || cp.gin.P != cp.gout.P || cp.gin.R != cp.gout.R) return 1;
     for (int s = 0; s < cp.nsrc; ++s) if (cp.src[s].C % 8 != 0) return 1;
+    if (cp.stats && !k3) return 1;          // the 1x1x1 form carries no statistics epilogue
+    if (cp.write_halo && cp.gout.P < 2) return 1;
 
     static int num_sms = 0, max_smem = 0;
     if (!num_sms) {
@@ -638,7 +633,20 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.nchunks = cp.Cin_total / 8;
     if (p.src_chunks[0] + p.src_chunks[1] != p.nchunks) return 1;
     p.w = packed_w; p.bias = cp.bias; p.dst = cp.dst; p.stats = cp.stats;
-    p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout); p.ncb = cp.Cout / p.CB;
+    p.write_halo = cp.write_halo;
+    p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout, taps); p.ncb = cp.Cout / p.CB;
+    // statistics are accumulated per GroupNorm group: the group size must match an instantiated (CB, CPG) pair
+    int cpg = 0;
+    if (k3) {
+        const int def_cpg[4] = {2, 4, 6, 8};                  // CB = 16, 32, 48, 64 with 8 groups over CB channels
+        cpg = def_cpg[p.CB / 16 - 1];
+        if (cp.stats) {
+            cpg = cp.stats_cpg;
+            const bool ok = (p.CB == 16 && cpg == 2) || (p.CB == 32 && cpg == 4) || (p.CB == 48 && (cpg == 6 || cpg == 12)) ||
+                            (p.CB == 64 && (cpg == 8 || cpg == 16));
+            if (!ok) return 1;
+        }
+    }
     p.N = k3 ? 3 * p.CB : p.CB;
     p.nshift = k3 ? 9 : 1;
     p.sub_stride = k3 ? 126 : 128;
@@ -652,15 +660,6 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.nwstages = 3;
     p.nrows = (long long)cp.B * g.rows_per_sample;
     if (p.nrows + 4096 >= (1LL << 31)) return 1;
-    {
-        const int divs[3] = {g.rows_per_sample, g.plane, g.Rp};
-        for (int i = 0; i < 3; ++i) {
-            int l = 0;
-            while ((1LL << l) < divs[i]) ++l;
-            p.fd_mul[i] = (uint32_t)((((1ULL << l) - (unsigned long long)divs[i]) << 32) / (unsigned long long)divs[i] + 1ULL);
-            p.fd_shift[i] = (uint32_t)l;
-        }
-    }
 
     const size_t fixed = kCtlBytes + kXchBytes + 256;
     bool found = false;
@@ -702,16 +701,28 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
 #endif
     const int grid = ctas * p.ncb;
     cudaError_t e = cudaSuccess;
-    switch (p.CB * 2 + (k3 ? 1 : 0)) {
-        case 16 * 2 + 1: e = launch_inst<16, true>(p, grid, smem_total, max_smem, st); break;
-        case 32 * 2 + 1: e = launch_inst<32, true>(p, grid, smem_total, max_smem, st); break;
-        case 48 * 2 + 1: e = launch_inst<48, true>(p, grid, smem_total, max_smem, st); break;
-        case 64 * 2 + 1: e = launch_inst<64, true>(p, grid, smem_total, max_smem, st); break;
-        case 16 * 2: e = launch_inst<16, false>(p, grid, smem_total, max_smem, st); break;
-        case 32 * 2: e = launch_inst<32, false>(p, grid, smem_total, max_smem, st); break;
-        case 48 * 2: e = launch_inst<48, false>(p, grid, smem_total, max_smem, st); break;
-        case 64 * 2: e = launch_inst<64, false>(p, grid, smem_total, max_smem, st); break;
-        default: return 1;
+    if (k3) {
+        switch (p.CB * 100 + cpg) {
+            case 1602: e = launch_inst<16, true, 2>(p, grid, smem_total, max_smem, st); break;
+            case 3204: e = launch_inst<32, true, 4>(p, grid, smem_total, max_smem, st); break;
+            case 4806: e = launch_inst<48, true, 6>(p, grid, smem_total, max_smem, st); break;
+            case 4812: e = launch_inst<48, true, 12>(p, grid, smem_total, max_smem, st); break;
+            case 6408: e = launch_inst<64, true, 8>(p, grid, smem_total, max_smem, st); break;
+            case 6416: e = launch_inst<64, true, 16>(p, grid, smem_total, max_smem, st); break;
+            default: return 1;
+        }
+    } else {
+        switch (p.CB) {
+            case 16: e = launch_inst<16, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 32: e = launch_inst<32, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 48: e = launch_inst<48, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 64: e = launch_inst<64, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 80: e = launch_inst<80, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 96: e = launch_inst<96, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 112: e = launch_inst<112, false, 1>(p, grid, smem_total, max_smem, st); break;
+            case 128: e = launch_inst<128, false, 1>(p, grid, smem_total, max_smem, st); break;
+            default: return 1;
+        }
     }
     return e == cudaSuccess ? 0 : 1;
 }

@@ -131,6 +131,7 @@ static Geom make_geom(int Z, int P, int R, int max_batch) {
     g.guard = ((g.plane + g.Rp + 1 + 7) / 8) * 8 + 1024;
     long long rows = (long long)max_batch * g.rows_per_sample + 2LL * g.guard;
     g.chunk_stride = (rows + 7) / 8 * 8;
+    geom_init_fastdiv(g);
     return g;
 }
 
@@ -230,7 +231,7 @@ struct Builder {
             int taps = w.kz * w.kp * w.kr;
             char nm[96];
             snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : ""), w.Cin, w.Cout,
-                     level_out, (w.wmma && stride == 1 && !w.transposed && !write_halo) ? "_mma" : (w.wgat ? "_gather" : "_simt"));
+                     level_out, (w.wmma && stride == 1 && !w.transposed) ? "_mma" : (w.wgat ? "_gather" : "_simt"));
             // FLOP = 2*MAC over output voxels as the reference executes them; bytes = fp16 in + out
             hh->op_info.push_back({nm, 2.0 * mo * w.Cin * w.Cout * taps, 2.0 * (mi * w.Cin + mo * w.Cout)});
         }
@@ -251,9 +252,10 @@ struct Builder {
             p.transposed = w.transposed;
             p.write_halo = write_halo;
             p.stats = stats_off >= 0 ? (double*)(hh->scratch + (size_t)stats_off * r.B) : nullptr;
+            p.stats_cpg = w.Cout / (hh->d.groups > 0 ? hh->d.groups : 1);
             p.B = r.B;
             hh->launches += 1;
-            if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed && !write_halo) {
+            if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed) {
                 if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
             }
             if (hh->conv_backend == 0 && w.wgat) {
@@ -264,13 +266,14 @@ struct Builder {
     }
 
     // GroupNorm finalize + apply:  dst = act(GN(src)) + addvec + residual   (all rows incl. halos)
+    // out_stats_off >= 0: also accumulate the per-sample sum / sum of squares of dst (GroupNorm(1,C) of a following PreNorm)
     void gn(const std::string& gname, const std::string& bname, int level, int src, int dst, int C, int groups, long long stats_off,
-            int act, int addvec_off /* -1 none */, int residual /* -1 none */, int residual2 = -1) {
+            int act, int addvec_off /* -1 none */, int residual /* -1 none */, int residual2 = -1, long long out_stats_off = -1) {
         cd_unet* hh = h;
         float* gamma = upload_vec(hh, gname, C);
         float* beta = upload_vec(hh, bname, C);
         if (!gamma || !beta) { ok = false; return; }
-        float2* affine = hh->dalloc<float2>((size_t)hh->d.max_batch * C, false);
+        if (C > 256) { fail("GroupNorm over more than 256 channels is not supported"); ok = false; return; }
         {
             const Geom& g = hh->geom[level];
             double m = (double)g.Z * g.P * g.R;
@@ -281,16 +284,17 @@ struct Builder {
         hh->ops.push_back([=](Run& r) {
             const Geom& g = hh->geom[level];
             double cnt = (double)g.Z * g.P * g.R;
-            launch_gn_finalize((const double*)(hh->scratch + (size_t)stats_off * r.B), gamma, beta, affine, r.B, C, groups, cnt, r.st);
-            launch_gn_apply(g, hh->bufs[src].ptr, affine, addvec_off >= 0 ? hh->addvec + addvec_off : nullptr, hh->addvec_stride,
+            launch_gn_apply(g, hh->bufs[src].ptr, (const double*)(hh->scratch + (size_t)stats_off * r.B), gamma, beta, groups, cnt,
+                            addvec_off >= 0 ? hh->addvec + addvec_off : nullptr, hh->addvec_stride,
                             residual >= 0 ? hh->bufs[residual].ptr : nullptr, residual2 >= 0 ? hh->bufs[residual2].ptr : nullptr,
-                            residual >= 0 ? hh->bufs[residual].C / 8 : 0, hh->bufs[dst].ptr, C, act, r.B, r.st);
-            hh->launches += 2;
+                            residual >= 0 ? hh->bufs[residual].C / 8 : 0, hh->bufs[dst].ptr, C, act,
+                            out_stats_off >= 0 ? (double*)(hh->scratch + (size_t)out_stats_off * r.B) : nullptr, r.B, r.st);
+            hh->launches += 1;
         });
     }
 
     // ResnetBlock (models.py:172-200).  srcs at `level`; returns output buffer (caller releases inputs)
-    int resblock(const std::string& pre, int level, std::vector<int> srcs, int Cin, int Cout, bool has_cond) {
+    int resblock(const std::string& pre, int level, std::vector<int> srcs, int Cin, int Cout, bool has_cond, long long out_stats_off = -1) {
         int groups = h->d.groups;
         ConvW c1, c2, cres;
         if (!pack_conv(h, pre + "block1.proj.conv.weight", pre + "block1.proj.conv.bias", Cin, Cin, Cout, 3, 3, 3, 0, true, &c1) ||
@@ -330,56 +334,50 @@ struct Builder {
         }
         // hbuf is free again as the destination: gn_apply reads t1 + residual only
         int res2 = (!has_res && srcs.size() == 2) ? srcs[1] : -1;  // identity residual over a concatenated input
-        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res, res2);
+        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res, res2, out_stats_off);
         release(h, t1);
         if (rbuf >= 0) release(h, rbuf);
         return hbuf;
     }
 
-    // Residual(PreNorm(LinearAttention)) (models.py:111-117, 281-329); returns output buffer
-    int attention(const std::string& pre, int level, int x, int C) {
+    // Residual(PreNorm(LinearAttention)) (models.py:111-117, 281-329); returns output buffer.
+    // s0: scratch slot holding the GroupNorm(1,C) statistics of x (accumulated by the gn() that produced x)
+    int attention(const std::string& pre, int level, int x, int C, size_t s0) {
         cd_unet* hh = h;
-        ConvW cq, co;
-        if (!pack_conv(h, pre + "fn.fn.to_qkv.conv.weight", "", C, C, 96, 1, 1, 1, 0, true, &cq) ||
-            !pack_conv(h, pre + "fn.fn.to_out.0.conv.weight", pre + "fn.fn.to_out.0.conv.bias", 32, 32, C, 1, 1, 1, 0, true, &co)) {
-            ok = false; return -1;
+        ConvW cq;
+        if (!pack_conv(h, pre + "fn.fn.to_qkv.conv.weight", "", C, C, 96, 1, 1, 1, 0, true, &cq)) { ok = false; return -1; }
+        if (!attention_out_supported(C)) { fail("attention over %d channels is not supported", C); ok = false; return -1; }
+        const HostTensor* wo = find_w(h, pre + "fn.fn.to_out.0.conv.weight");
+        if (!wo || wo->shape.size() != 5 || wo->shape[0] != C || wo->shape[1] != 32) {
+            fail("weight %sfn.fn.to_out.0.conv.weight missing or of unexpected shape", pre.c_str()); ok = false; return -1;
         }
-        size_t s0 = slot((size_t)C * 16), s1 = slot((size_t)C * 16);
+        float* wout = upload_vec(h, pre + "fn.fn.to_out.0.conv.weight", C * 32);
+        float* bout = upload_vec(h, pre + "fn.fn.to_out.0.conv.bias", C);
+        if (!wout || !bout) { ok = false; return -1; }
+        size_t s1 = slot((size_t)C * 16);
         size_t skm = slot(32 * 4), sctx = slot(33 * 32 * 4);
-        {
-            const Geom& g = hh->geom[level];
-            double m = (double)g.Z * g.P * g.R;
-            char nm[96];
-            snprintf(nm, sizeof(nm), "row_stats_c%d_L%d", C, level);
-            hh->op_info.push_back({nm, 0.0, 2.0 * m * C});
-        }
-        hh->ops.push_back([=](Run& r) {
-            launch_row_stats(hh->geom[level], hh->bufs[x].ptr, (double*)(hh->scratch + s0 * r.B), C, r.B, r.st);
-            hh->launches += 1;
-        });
         int xn = acquire(h, level, C);
         gn(pre + "fn.norm.weight", pre + "fn.norm.bias", level, x, xn, C, 1, (long long)s0, 0, -1, -1);
         int qkv = acquire(h, level, 96);
         conv(cq, level, level, {xn}, qkv, 1, 0, 0, 0, 0, -1);
-        int ao = acquire(h, level, 32);
         {
             const Geom& g = hh->geom[level];
             double m = (double)g.Z * g.P * g.R;
             char nm[96];
             snprintf(nm, sizeof(nm), "attention_L%d", level);
-            // two 32x32xn einsums; bytes: k read twice, v, q read once, out written
-            hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m, 2.0 * m * 32 * 5});
+            // two 32x32xn einsums + the to_out 1x1x1 conv; bytes: k read twice, v and q once, C channels written
+            hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m + 2.0 * 32 * C * m, 2.0 * m * (32 * 4 + C)});
         }
+        // attention + to_out conv -> xn reused as the raw output (+ its GroupNorm(1,C) statistics), then GN(1) + residual x
         hh->ops.push_back([=](Run& r) {
             launch_attention(hh->geom[level], hh->bufs[qkv].ptr, (unsigned*)(hh->scratch + skm * r.B),
-                             (float*)(hh->scratch + sctx * r.B), hh->bufs[ao].ptr, r.B, r.st);
+                             (float*)(hh->scratch + sctx * r.B), wout, bout, hh->bufs[xn].ptr, C,
+                             (double*)(hh->scratch + s1 * r.B), r.B, r.st);
             hh->launches += 3;
         });
-        // to_out conv -> xn reused as raw output, then GN(1) + residual x
-        conv(co, level, level, {ao}, xn, 1, 0, 0, 0, 0, (long long)s1);
         int out = acquire(h, level, C);
         gn(pre + "fn.fn.to_out.1.weight", pre + "fn.fn.to_out.1.bias", level, xn, out, C, 1, (long long)s1, 0, -1, x);
-        release(h, xn); release(h, qkv); release(h, ao);
+        release(h, xn); release(h, qkv);
         return out;
     }
 };
@@ -418,19 +416,19 @@ static int build_plan(cd_unet* h) {
         h->launches += 1;
     });
 
-    // input + init conv (geometry channels are generated in-kernel; Cin padded to 8)
-    int tin_buf = acquire(h, 0, 8);
+    // input + init conv (geometry channels are generated in-kernel; Cin zero-padded to the tensor-core K granularity 16)
+    int tin_buf = acquire(h, 0, 16);
     {
         double m = (double)d.Z * d.P * d.R;
         h->op_info.push_back({"prep_input", 0.0, m * 4 + m * 16});
     }
     h->ops.push_back([h, tin_buf](Run& r) {
         launch_prep_input(h->geom[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f, h->r_vals,
-                          h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, r.B, r.st);
+                          h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, 2, r.B, r.st);
         h->launches += 1;
     });
     ConvW cinit;
-    if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 8, ls[0], 3, 3, 3, 0, false, &cinit, true)) return 1;
+    if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 16, ls[0], 3, 3, 3, 0, true, &cinit, true)) return 1;
     int x = acquire(h, 0, ls[0]);
     b.conv(cinit, 0, 0, {tin_buf}, x, 1, 1, 1, 1, 1, -1);
     release(h, tin_buf);
@@ -442,10 +440,11 @@ static int build_plan(cd_unet* h) {
         int y = b.resblock(p + "0.", i, {x}, cin_, cout_, true);
         if (!b.ok) return 1;
         release(h, x);
-        int y2 = b.resblock(p + "1.", i, {y}, cout_, cout_, true);
+        size_t sa = b.slot((size_t)cout_ * 16);
+        int y2 = b.resblock(p + "1.", i, {y}, cout_, cout_, true, (long long)sa);
         if (!b.ok) return 1;
         release(h, y);
-        int a = b.attention(M + "downs_attn." + std::to_string(i) + ".", i, y2, cout_);
+        int a = b.attention(M + "downs_attn." + std::to_string(i) + ".", i, y2, cout_, sa);
         if (!b.ok) return 1;
         release(h, y2);
         skips.push_back(a);
@@ -461,10 +460,11 @@ static int build_plan(cd_unet* h) {
     int mid = ls[nl];
     int lv = nl - 1;
     {
-        int y = b.resblock(M + "mid_block1.", lv, {x}, mid, mid, true);
+        size_t sa = b.slot((size_t)mid * 16);
+        int y = b.resblock(M + "mid_block1.", lv, {x}, mid, mid, true, (long long)sa);
         if (!b.ok) return 1;
         // x is the last skip: keep it
-        int a = b.attention(M + "mid_attn.", lv, y, mid);
+        int a = b.attention(M + "mid_attn.", lv, y, mid, sa);
         if (!b.ok) return 1;
         release(h, y);
         int y2 = b.resblock(M + "mid_block2.", lv, {a}, mid, mid, true);
@@ -481,10 +481,11 @@ static int build_plan(cd_unet* h) {
         int y = b.resblock(p + "0.", lev, {x, skip}, dim_out * 2, dim_in, true);
         if (!b.ok) return 1;
         release(h, x); release(h, skip);
-        int y2 = b.resblock(p + "1.", lev, {y}, dim_in, dim_in, true);
+        size_t sa = b.slot((size_t)dim_in * 16);
+        int y2 = b.resblock(p + "1.", lev, {y}, dim_in, dim_in, true, (long long)sa);
         if (!b.ok) return 1;
         release(h, y);
-        int a = b.attention(M + "ups_attn." + std::to_string(i) + ".", lev, y2, dim_in);
+        int a = b.attention(M + "ups_attn." + std::to_string(i) + ".", lev, y2, dim_in, sa);
         if (!b.ok) return 1;
         release(h, y2);
         if (i < nl - 1) {
@@ -923,7 +924,7 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     p.sz = stride[0]; p.sp = stride[1]; p.sr = stride[2];
     bool is1 = taps == 1;
     p.pz = is1 ? 0 : 1; p.cp = is1 ? 0 : 1; p.pr = is1 ? 0 : 1;
-    p.transposed = transposed; p.write_halo = 0; p.stats = nullptr; p.B = B;
+    p.transposed = transposed; p.write_halo = 0; p.stats = nullptr; p.stats_cpg = 1; p.B = B;
     int rc = 0;
     if (backend == 0) {
         if (!cw.wmma || launch_conv_mma(p, cw.wmma, st) != 0) rc = fail("tcgen05 conv does not support this shape");

@@ -8,35 +8,36 @@ namespace cd {
 // prep_input: x (B,Z,P,R) fp32 -> PLCP tensor with 8 channels: [x*c_in, R, Z, (phi), 0...]
 // Replaces calodiffusion.py:121-142 add_RZPhi (repeat+cat) and the c_in multiply of :159.
 // =================================================================================================
-__global__ void prep_input_kernel(Geom g, const float* __restrict__ x, const float* __restrict__ sigma, int sigma_stride,
-                                  float sigma_data, const float* __restrict__ r_vals, int rz_input, int phi_input,
-                                  __half* __restrict__ dst, long long nrows) {
-    long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= nrows) return;
-    RowInfo ri = decode_row(g, row);
+__global__ void __launch_bounds__(256) prep_input_kernel(Geom g, const float* __restrict__ x, const float* __restrict__ sigma,
+                                                         int sigma_stride, float sigma_data, const float* __restrict__ r_vals,
+                                                         int rz_input, int phi_input, __half* __restrict__ dst, int out_chunks) {
+    const int b = blockIdx.y;
+    const uint32_t rem = blockIdx.x * 256 + threadIdx.x;
+    if (rem >= (uint32_t)g.rows_per_sample) return;
+    const SubRow sr = decode_subrow(g, rem);
+    const long long row = (long long)b * g.rows_per_sample + rem;
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (ri.kind != 2) {
-        int p = ri.pp - 1;
+    if (sr.kind != 2) {
+        int p = sr.pp - 1;
         if (p < 0) p += g.P;
         if (p >= g.P) p -= g.P;
-        float s = sigma[(long long)ri.b * sigma_stride];
-        float c_in = sigma_data > 0.f ? rsqrtf(s * s + sigma_data * sigma_data) : 1.f;
-        long long vox = (((long long)ri.b * g.Z + ri.z) * g.P + p) * g.R + ri.rr;
+        const float s = sigma[(long long)b * sigma_stride];
+        const float c_in = sigma_data > 0.f ? rsqrtf(s * s + sigma_data * sigma_data) : 1.f;
+        const long long vox = (((long long)b * g.Z + sr.z) * g.P + p) * g.R + sr.rr;
         f[0] = x[vox] * c_in;
         int c = 1;
-        if (rz_input) { f[c++] = r_vals[ri.rr]; f[c++] = (float)ri.z / (float)g.Z; }
+        if (rz_input) { f[c++] = r_vals[sr.rr]; f[c++] = (float)sr.z / (float)g.Z; }
         if (phi_input) { f[c++] = (g.P > 1) ? (float)p / (float)(g.P - 1) : 0.f; }
     }
     *reinterpret_cast<Half8*>(dst + plcp_offset(g, 0, row)) = pack8(f);
+    // channel padding up to the tensor-core K granularity (the buffer may have been used by another layer)
+    for (int k = 1; k < out_chunks; ++k) *reinterpret_cast<uint4*>(dst + plcp_offset(g, k, row)) = make_uint4(0u, 0u, 0u, 0u);
 }
 
 void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,
-                       const float* r_vals, int rz_input, int phi_input, __half* dst, int B, cudaStream_t st) {
-    long long nrows = (long long)B * g.rows_per_sample;
-    int threads = 256;
-    long long blocks = (nrows + threads - 1) / threads;
-    prep_input_kernel<<<(unsigned)blocks, threads, 0, st>>>(g, x, sigma, sigma_stride, sigma_data, r_vals, rz_input,
-                                                            phi_input, dst, nrows);
+                       const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks, int B, cudaStream_t st) {
+    dim3 grid((g.rows_per_sample + 255) / 256, B);
+    prep_input_kernel<<<grid, 256, 0, st>>>(g, x, sigma, sigma_stride, sigma_data, r_vals, rz_input, phi_input, dst, out_chunks);
 }
 
 // =================================================================================================
@@ -178,308 +179,146 @@ void launch_conv_generic(const ConvParams& p, cudaStream_t st) {
 }
 
 // =================================================================================================
-// GroupNorm pieces (models/models.py:155,162 GroupNorm(8,C); :293,325 GroupNorm(1,C); eps 1e-5).
-// Statistics are per-(sample, channel) double sums produced by the conv epilogues (or row_stats);
-// gn_finalize folds them per group into a per-(sample, channel) affine  y = x*scale + shift.
+// GroupNorm finalize + apply (models/models.py:155,162 GroupNorm(8,C); :293,325 GroupNorm(1,C); eps 1e-5).
+// Statistics are per-(sample, channel) double sums (sum, sum of squares) produced by the conv epilogues or by
+// the producer noted at the call site; every block folds its sample's sums per group into a per-channel
+// affine y = x*scale + shift (shared memory), then streams rows:
+//     out = act(x*scale+shift) + addvec[b][c] + residual          written for every row incl. halos
+// Covers Block's GN+SiLU (models.py:160-169), the additive conditioning (:194-197), the ResnetBlock residual
+// (:200), PreNorm (:327-329) and Residual(to_out GN) (:117,:293).  HBM-bound: one thread owns one padded-linear
+// row (decoded once with 32-bit fast divisions) and moves all of its 16-byte channel chunks, four loads in
+// flight per operand; a warp's access to one chunk plane is 512 contiguous bytes.
+// Optionally accumulates the per-sample sum / sum of squares of its own (fp16-rounded) output over interior rows
+// into out_stats[b][channel 0] for the GroupNorm(1, C) of the attention block that follows (models.py:325).
 // =================================================================================================
-__global__ void gn_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
-                                   const float* __restrict__ beta, float2* __restrict__ affine, int B, int C, int groups,
-                                   double count_per_channel, float eps) {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= B * C) return;
-    int b = idx / C, c = idx - b * C;
-    int cpg = C / groups;
-    int g0 = (c / cpg) * cpg;
-    double s = 0.0, q = 0.0;
-    for (int j = 0; j < cpg; ++j) {
-        const double* d = stats + ((long long)b * C + g0 + j) * 2;
-        s += d[0]; q += d[1];
-    }
-    double n = count_per_channel * cpg;
-    double mean = s / n;
-    double var = q / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    float rstd = (float)(1.0 / sqrt(var + (double)eps));
-    float sc = gamma[c] * rstd;
-    affine[idx] = make_float2(sc, beta[c] - (float)mean * sc);
+constexpr int kGnThreads = 256;
+constexpr int kGnRowsPerThread = 4;      // rows per thread: amortises the per-block statistics prologue
+constexpr int kGnMaxC = 256;
+
+// SiLU through one MUFU: x*sigmoid(x) = 0.5*x*(1 + tanh(x/2)); tanh.approx error (2^-11) is below the fp16 store rounding
+__device__ __forceinline__ float silu_fast(float v) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * v));
+    const float h = 0.5f * v;
+    return fmaf(h, t, h);
 }
 
-void launch_gn_finalize(const double* stats, const float* gamma, const float* beta, float2* affine, int B, int C,
-                        int groups, double count_per_channel, cudaStream_t st) {
-    int n = B * C;
-    gn_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(stats, gamma, beta, affine, B, C, groups, count_per_channel, 1e-5f);
-}
-
-// out = act(x*scale+shift) + addvec[b][c] + residual ; written for every row incl. halos (gather form)
-// Covers Block's GN+SiLU (models.py:160-169), the additive conditioning (:194-197), the ResnetBlock
-// residual (:200), PreNorm (:327-329) and Residual(to_out GN) (:117,:293).
-__global__ void gn_apply_kernel(Geom g, const __half* __restrict__ src, const float2* __restrict__ affine,
-                                const float* __restrict__ addvec, int addvec_stride, const __half* __restrict__ residual,
-                                const __half* __restrict__ residual2, int res_split,
-                                __half* __restrict__ dst, int C, int act, long long nrows) {
-    long long row = (long long)blockIdx.x * 32 + threadIdx.x;
-    int k = threadIdx.y + blockIdx.y * blockDim.y;
-    if (row >= nrows || k >= (C >> 3)) return;
-    RowInfo ri = decode_row(g, row);
-    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (ri.kind != 2) {
-        Half8 v = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k, ri.src));
-        unpack8(v, f);
-        const float2* af = affine + (long long)ri.b * C + k * 8;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            float2 a = af[j];
-            float y = f[j] * a.x + a.y;
-            if (act) y = silu_f(y);
-            f[j] = y;
+__global__ void __launch_bounds__(kGnThreads, 4) gn_apply_kernel(
+    Geom g, const __half* __restrict__ src, const double* __restrict__ stats, const float* __restrict__ gamma,
+    const float* __restrict__ beta, int groups, double count_per_channel, const float* __restrict__ addvec, int addvec_stride,
+    const __half* __restrict__ residual, const __half* __restrict__ residual2, int res_split, __half* __restrict__ dst, int C,
+    int act, double* __restrict__ out_stats) {
+    __shared__ __align__(16) float s_scale[kGnMaxC];
+    __shared__ __align__(16) float s_shift[kGnMaxC];
+    __shared__ __align__(16) float s_add[kGnMaxC];
+    __shared__ float red[2][kGnThreads / 32];
+    const int b = blockIdx.y;
+    const int nch = C >> 3;
+    for (int c = threadIdx.x; c < C; c += kGnThreads) {
+        const int cpg = C / groups;
+        const int g0 = (c / cpg) * cpg;
+        double s = 0.0, q = 0.0;
+        for (int j = 0; j < cpg; ++j) {
+            const double* d = stats + ((long long)b * C + g0 + j) * 2;
+            s += d[0]; q += d[1];
         }
-        if (addvec) {
-            const float* av = addvec + (long long)ri.b * addvec_stride + k * 8;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] += av[j];
-        }
-        if (residual) {
-            // the residual may be the channel concatenation of two tensors (torch.cat skip, models.py:741)
-            const __half* rb = (k < res_split) ? residual + plcp_offset(g, k, ri.src) : residual2 + plcp_offset(g, k - res_split, ri.src);
-            Half8 rv = *reinterpret_cast<const Half8*>(rb);
-            float r[8];
-            unpack8(rv, r);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] += r[j];
-        }
+        const double n = count_per_channel * cpg;
+        const float mean = (float)(s / n);
+        float var = (float)(q / n - (s / n) * (s / n));
+        if (var < 0.f) var = 0.f;
+        const float sc = gamma[c] * rsqrtf(var + 1e-5f);
+        const float av = addvec ? addvec[(long long)b * addvec_stride + c] : 0.f;
+        s_scale[c] = sc;
+        // without an activation the additive conditioning folds into the shift
+        s_shift[c] = beta[c] - mean * sc + (act ? 0.f : av);
+        s_add[c] = act ? av : 0.f;
     }
-    *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = pack8(f);
-}
-
-void launch_gn_apply(const Geom& g, const __half* src, const float2* affine, const float* addvec, int addvec_stride,
-                     const __half* residual, const __half* residual2, int res_split, __half* dst, int C, int act, int B,
-                     cudaStream_t st) {
-    long long nrows = (long long)B * g.rows_per_sample;
-    int chunks = C >> 3;
-    int by = chunks < 8 ? chunks : 8;
-    dim3 block(32, by);
-    dim3 grid((unsigned)((nrows + 31) / 32), (chunks + by - 1) / by);
-    gn_apply_kernel<<<grid, block, 0, st>>>(g, src, affine, addvec, addvec_stride, residual, residual2,
-                                            residual2 ? res_split : (C >> 3), dst, C, act, nrows);
-}
-
-// per-(sample, channel) sum / sumsq over interior rows of an existing tensor (GroupNorm(1,C) PreNorm input)
-__global__ void row_stats_kernel(Geom g, const __half* __restrict__ src, double* __restrict__ stats, int C,
-                                 int rows_per_block) {
-    int b = blockIdx.y;
-    int k = threadIdx.y;
-    long long r0 = (long long)b * g.rows_per_sample + (long long)blockIdx.x * rows_per_block;
-    long long r1 = r0 + rows_per_block;
-    long long rend = (long long)(b + 1) * g.rows_per_sample;
-    if (r1 > rend) r1 = rend;
-    float s[8], q[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
-    for (long long row = r0 + threadIdx.x; row < r1; row += 32) {
-        RowInfo ri = decode_row(g, row);
-        if (ri.kind != 0) continue;
-        Half8 v = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k, row));
-        float f[8];
-        unpack8(v, f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] += f[j] * f[j]; }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            s[j] += __shfl_xor_sync(0xffffffffu, s[j], o);
-            q[j] += __shfl_xor_sync(0xffffffffu, q[j], o);
-        }
-        if (threadIdx.x == 0) {
-            double* d = stats + ((long long)b * C + k * 8 + j) * 2;
-            atomicAdd(d, (double)s[j]);
-            atomicAdd(d + 1, (double)q[j]);
-        }
-    }
-}
-
-void launch_row_stats(const Geom& g, const __half* src, double* stats, int C, int B, cudaStream_t st) {
-    int rows_per_block = 1024;
-    dim3 block(32, C >> 3);
-    dim3 grid((g.rows_per_sample + rows_per_block - 1) / rows_per_block, B);
-    row_stats_kernel<<<grid, block, 0, st>>>(g, src, stats, C, rows_per_block);
-}
-
-// =================================================================================================
-// Linear attention (models/models.py:301-318; heads=1, dim_head=32).  qkv is a raw 96-channel PLCP
-// tensor: chunks 0-3 q, 4-7 k, 8-11 v.
-//   k_max[b][d]          = max_n k[d,n]                       (softmax over voxels, stabiliser)
-//   S[b][d]              = sum_n exp(k[d,n]-k_max)
-//   Ctx[b][d][e]         = sum_n exp(k[d,n]-k_max) v[e,n]
-//   out[e,n]             = 32^-0.5 * sum_d Ctx[d][e]/S[d] * softmax_d(q[:,n])[d]
-// =================================================================================================
-__device__ __forceinline__ unsigned f2ord(float f) {
-    unsigned u = __float_as_uint(f);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-__device__ __forceinline__ float ord2f(unsigned k) {
-    unsigned u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
-    return __uint_as_float(u);
-}
-
-__global__ void attn_kmax_kernel(Geom g, const __half* __restrict__ qkv, unsigned* __restrict__ kmax, int rows_per_block) {
-    int b = blockIdx.y;
-    int k = threadIdx.y;  // 0..3 -> k chunk
-    long long r0 = (long long)b * g.rows_per_sample + (long long)blockIdx.x * rows_per_block;
-    long long r1 = r0 + rows_per_block;
-    long long rend = (long long)(b + 1) * g.rows_per_sample;
-    if (r1 > rend) r1 = rend;
-    float m[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
-    for (long long row = r0 + threadIdx.x; row < r1; row += 32) {
-        RowInfo ri = decode_row(g, row);
-        if (ri.kind != 0) continue;
-        Half8 v = *reinterpret_cast<const Half8*>(qkv + plcp_offset(g, 4 + k, row));
-        float f[8];
-        unpack8(v, f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m[j] = fmaxf(m[j], __shfl_xor_sync(0xffffffffu, m[j], o));
-        if (threadIdx.x == 0 && m[j] > -INFINITY) atomicMax(kmax + b * 32 + k * 8 + j, f2ord(m[j]));
-    }
-}
-
-// ctx layout: [B][33][32] floats: rows 0..31 = Ctx[d][e], row 32 = S[d]
-__global__ void __launch_bounds__(256) attn_context_kernel(Geom g, const __half* __restrict__ qkv,
-                                                           const unsigned* __restrict__ kmax, float* __restrict__ ctx,
-                                                           int rows_per_block, int use_atomics) {
-    __shared__ float ek[128][33];
-    __shared__ float vv[128][33];
-    __shared__ float km[32];
-    int b = blockIdx.y;
-    int tid = threadIdx.x;
-    if (tid < 32) km[tid] = ord2f(kmax[b * 32 + tid]);
-    long long r0 = (long long)b * g.rows_per_sample + (long long)blockIdx.x * rows_per_block;
-    long long r1 = r0 + rows_per_block;
-    long long rend = (long long)(b + 1) * g.rows_per_sample;
-    if (r1 > rend) r1 = rend;
-    int d = tid >> 3;          // 0..31
-    int e0 = (tid & 7) * 4;    // 4 consecutive e
-    float acc[4] = {0, 0, 0, 0};
-    float sacc = 0.f;
     __syncthreads();
-    for (long long base = r0; base < r1; base += 128) {
-        // stage 128 rows: thread -> (row = tid&127, half = tid>>7 : 0 -> k, 1 -> v)
-        {
-            int lr = tid & 127;
-            int which = tid >> 7;
-            long long row = base + lr;
-            bool ok = row < r1;
-            if (ok) { RowInfo ri = decode_row(g, row); ok = (ri.kind == 0); }
-            float (*dstm)[33] = which ? vv : ek;
+    float ssum = 0.f, ssq = 0.f;
+    const uint32_t rem0 = blockIdx.x * (kGnThreads * kGnRowsPerThread) + threadIdx.x;
+#pragma unroll 1
+    for (int it = 0; it < kGnRowsPerThread; ++it) {
+        const uint32_t rem = rem0 + it * kGnThreads;
+        if (rem >= (uint32_t)g.rows_per_sample) break;
+        const SubRow sr = decode_subrow(g, rem);
+        const long long row = (long long)b * g.rows_per_sample + rem;
+        const long long srow = row + sr.src_delta;
+        if (sr.kind == 2) {
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            for (int k = 0; k < nch; ++k) *reinterpret_cast<uint4*>(dst + plcp_offset(g, k, row)) = z;
+            continue;
+        }
+        for (int k0 = 0; k0 < nch; k0 += 4) {
+            Half8 v[4], rv[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-                if (ok) {
-                    Half8 v = *reinterpret_cast<const Half8*>(qkv + plcp_offset(g, (which ? 8 : 4) + k, row));
-                    unpack8(v, f);
-                    if (!which) {
+            for (int i = 0; i < 4; ++i)
+                if (k0 + i < nch) v[i] = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k0 + i, srow));
+            if (residual) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - km[k * 8 + j]);
+                for (int i = 0; i < 4; ++i)
+                    if (k0 + i < nch) {
+                        const int k = k0 + i;
+                        const __half* rb = (k < res_split) ? residual + plcp_offset(g, k, srow) : residual2 + plcp_offset(g, k - res_split, srow);
+                        rv[i] = *reinterpret_cast<const Half8*>(rb);
                     }
-                }
+            }
 #pragma unroll
-                for (int j = 0; j < 8; ++j) dstm[lr][k * 8 + j] = f[j];
+            for (int i = 0; i < 4; ++i) {
+                if (k0 + i >= nch) break;
+                const int k = k0 + i;
+                float f[8], sc[8], sh[8];
+                unpack8(v[i], f);
+                *reinterpret_cast<float4*>(sc) = *reinterpret_cast<const float4*>(s_scale + k * 8);
+                *reinterpret_cast<float4*>(sc + 4) = *reinterpret_cast<const float4*>(s_scale + k * 8 + 4);
+                *reinterpret_cast<float4*>(sh) = *reinterpret_cast<const float4*>(s_shift + k * 8);
+                *reinterpret_cast<float4*>(sh + 4) = *reinterpret_cast<const float4*>(s_shift + k * 8 + 4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+                if (act) {
+                    float ad[8];
+                    *reinterpret_cast<float4*>(ad) = *reinterpret_cast<const float4*>(s_add + k * 8);
+                    *reinterpret_cast<float4*>(ad + 4) = *reinterpret_cast<const float4*>(s_add + k * 8 + 4);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]) + ad[j];
+                }
+                if (residual) {
+                    float r[8];
+                    unpack8(rv[i], r);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] += r[j];
+                }
+                const Half8 o = pack8(f);
+                *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = o;
+                if (out_stats && sr.kind == 0) {
+                    unpack8(o, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { ssum += f[j]; ssq = fmaf(f[j], f[j], ssq); }
+                }
             }
         }
-        __syncthreads();
-#pragma unroll 4
-        for (int n = 0; n < 128; ++n) {
-            float e = ek[n][d];
-            acc[0] += e * vv[n][e0]; acc[1] += e * vv[n][e0 + 1]; acc[2] += e * vv[n][e0 + 2]; acc[3] += e * vv[n][e0 + 3];
-            sacc += e;
-        }
-        __syncthreads();
     }
-    float* c = ctx + (long long)b * 33 * 32;
-    if (use_atomics) {
+    if (out_stats) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) atomicAdd(c + d * 32 + e0 + i, acc[i]);
-        if ((tid & 7) == 0) atomicAdd(c + 32 * 32 + d, sacc);
-    } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) c[d * 32 + e0 + i] = acc[i];
-        if ((tid & 7) == 0) c[32 * 32 + d] = sacc;
+        for (int o = 16; o > 0; o >>= 1) { ssum += __shfl_xor_sync(0xffffffffu, ssum, o); ssq += __shfl_xor_sync(0xffffffffu, ssq, o); }
+        const int w = threadIdx.x >> 5;
+        if ((threadIdx.x & 31) == 0) { red[0][w] = ssum; red[1][w] = ssq; }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            double t = 0.0;
+            for (int i = 0; i < kGnThreads / 32; ++i) t += (double)red[threadIdx.x][i];
+            atomicAdd(out_stats + (long long)b * C * 2 + threadIdx.x, t);
+        }
     }
 }
 
-__global__ void __launch_bounds__(128) attn_out_kernel(Geom g, const __half* __restrict__ qkv, const float* __restrict__ ctx,
-                                                       __half* __restrict__ dst, int rows_per_block) {
-    __shared__ float M[32][33];  // M[d][e] = Ctx[d][e]/S[d]*scale
-    int b = blockIdx.y;
-    const float* c = ctx + (long long)b * 33 * 32;
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
-        int d = i >> 5, e = i & 31;
-        M[d][e] = c[i] / c[1024 + d] * 0.17677669529663687f;  // 32^-0.5
-    }
-    __syncthreads();
-    long long r0 = (long long)b * g.rows_per_sample + (long long)blockIdx.x * rows_per_block;
-    long long r1 = r0 + rows_per_block;
-    long long rend = (long long)(b + 1) * g.rows_per_sample;
-    if (r1 > rend) r1 = rend;
-    for (long long row = r0 + threadIdx.x; row < r1; row += blockDim.x) {
-        RowInfo ri = decode_row(g, row);
-        if (ri.kind != 0) continue;
-        float q[32];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            Half8 v = *reinterpret_cast<const Half8*>(qkv + plcp_offset(g, k, row));
-            unpack8(v, q + k * 8);
-        }
-        float mx = q[0];
-#pragma unroll
-        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, q[j]);
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) { q[j] = __expf(q[j] - mx); sum += q[j]; }
-        float inv = 1.0f / sum;
-        float o[32];
-#pragma unroll
-        for (int e = 0; e < 32; ++e) o[e] = 0.f;
-#pragma unroll
-        for (int d = 0; d < 32; ++d) {
-            float qd = q[d] * inv;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) o[e] += qd * M[d][e];
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = pack8(o + k * 8);
-    }
-}
-
-void launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, __half* dst, int B, cudaStream_t st) {
-    // kmax and ctx must be zero on entry (the engine clears its scratch once per forward)
-    int rpb = 2048;
-    {
-        dim3 block(32, 4), grid((g.rows_per_sample + rpb - 1) / rpb, B);
-        attn_kmax_kernel<<<grid, block, 0, st>>>(g, qkv, kmax, rpb);
-    }
-    {
-        int nsplit = 1;
-        while ((long long)B * nsplit < 296 && (g.rows_per_sample / (nsplit * 2)) >= 512) nsplit *= 2;
-        int rows = (g.rows_per_sample + nsplit - 1) / nsplit;
-        rows = (rows + 127) / 128 * 128;
-        int nblk = (g.rows_per_sample + rows - 1) / rows;
-        dim3 grid(nblk, B);
-        attn_context_kernel<<<grid, 256, 0, st>>>(g, qkv, kmax, ctx, rows, nblk > 1 ? 1 : 0);
-    }
-    {
-        int rows = 512;
-        dim3 grid((g.rows_per_sample + rows - 1) / rows, B);
-        attn_out_kernel<<<grid, 128, 0, st>>>(g, qkv, ctx, dst, rows);
-    }
+void launch_gn_apply(const Geom& g, const __half* src, const double* stats, const float* gamma, const float* beta, int groups,
+                     double count_per_channel, const float* addvec, int addvec_stride, const __half* residual,
+                     const __half* residual2, int res_split, __half* dst, int C, int act, double* out_stats, int B,
+                     cudaStream_t st) {
+    const int rpb = kGnThreads * kGnRowsPerThread;
+    dim3 grid((g.rows_per_sample + rpb - 1) / rpb, B);
+    gn_apply_kernel<<<grid, kGnThreads, 0, st>>>(g, src, stats, gamma, beta, groups, count_per_channel, addvec, addvec_stride,
+                                                residual, residual2, residual2 ? res_split : (C >> 3), dst, C, act, out_stats);
 }
 
 // =================================================================================================

@@ -28,15 +28,16 @@ struct FinalParams {
 };
 
 void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,
-                       const float* r_vals, int rz_input, int phi_input, __half* dst, int B, cudaStream_t st);
+                       const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks, int B, cudaStream_t st);
 void launch_conv_generic(const ConvParams& p, cudaStream_t st);
-void launch_gn_finalize(const double* stats, const float* gamma, const float* beta, float2* affine, int B, int C,
-                        int groups, double count_per_channel, cudaStream_t st);
-void launch_gn_apply(const Geom& g, const __half* src, const float2* affine, const float* addvec, int addvec_stride,
-                     const __half* residual, const __half* residual2, int res_split, __half* dst, int C, int act, int B,
+void launch_gn_apply(const Geom& g, const __half* src, const double* stats, const float* gamma, const float* beta, int groups,
+                     double count_per_channel, const float* addvec, int addvec_stride, const __half* residual,
+                     const __half* residual2, int res_split, __half* dst, int C, int act, double* out_stats, int B,
                      cudaStream_t st);
-void launch_row_stats(const Geom& g, const __half* src, double* stats, int C, int B, cudaStream_t st);
-void launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, __half* dst, int B, cudaStream_t st);
+// linear attention + to_out 1x1x1 conv + GroupNorm(1,C) statistics (cd_attention.cu); 3 launches; returns 0 if C is supported
+int launch_attention(const Geom& g, const __half* qkv, unsigned* kmax, float* ctx, const float* wout, const float* bout,
+                     __half* dst, int C, double* stats, int B, cudaStream_t st);
+bool attention_out_supported(int C);
 void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, const float* cond, float* addvec, int B,
                   cudaStream_t st);
 void launch_final(const FinalParams& p, int B, cudaStream_t st);
