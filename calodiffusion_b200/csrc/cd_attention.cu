@@ -86,16 +86,15 @@ __global__ void __launch_bounds__(256) attn_kmax_kernel(Geom g, const __half* __
 
 // ---------------------------------------------------------------------------------------------------------
 // ctx layout: [B][33][32] floats: rows 0..31 = Ctx[d][e], row 32 = S[d]
-__global__ void __launch_bounds__(256) attn_context_kernel(Geom g, const __half* __restrict__ qkv, const unsigned* __restrict__ kmax,
+__global__ void __launch_bounds__(256, 3) attn_context_kernel(Geom g, const __half* __restrict__ qkv, const unsigned* __restrict__ kmax,
                                                            float* __restrict__ ctx, int rows_per_block, int use_atomics) {
     __shared__ __align__(16) unsigned char slab[kWarps][2][32 * kRowStrideB];   // per warp: exp(k) rows, v rows
     __shared__ float red[33 * 32];
     const int b = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < 33 * 32; i += 256) red[i] = 0.f;
-    float km[32];
-#pragma unroll
-    for (int c = 0; c < 32; ++c) km[c] = ord2f(kmax[b * 32 + c]);
+    __shared__ __align__(16) float km[32];
+    if (threadIdx.x < 32) km[threadIdx.x] = ord2f(kmax[b * 32 + threadIdx.x]);
     __syncthreads();
     const uint32_t r0 = blockIdx.x * rows_per_block;
     uint32_t r1 = r0 + rows_per_block;
@@ -142,8 +141,10 @@ __global__ void __launch_bounds__(256) attn_context_kernel(Geom g, const __half*
             float f[8];
             if (interior) {
                 unpack8(kv[c], f);
+                const float4 m0 = *reinterpret_cast<const float4*>(km + c * 8), m1 = *reinterpret_cast<const float4*>(km + c * 8 + 4);
+                const float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - km[c * 8 + j]);
+                for (int j = 0; j < 8; ++j) f[j] = __expf(f[j] - mm[j]);
             } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = 0.f;
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(256) attn_context_kernel(Geom g, const __half*
 
 // ---------------------------------------------------------------------------------------------------------
 template <int NT>   // output channel 8-blocks (C = 8*NT)
-__global__ void __launch_bounds__(256) attn_out_kernel(Geom g, const __half* __restrict__ qkv, const float* __restrict__ ctx,
+__global__ void __launch_bounds__(256, NT <= 4 ? 3 : 2) attn_out_kernel(Geom g, const __half* __restrict__ qkv, const float* __restrict__ ctx,
                                                        const float* __restrict__ wout /* [C][32] */, const float* __restrict__ bout,
                                                        __half* __restrict__ dst, double* __restrict__ stats, int rows_per_block) {
     constexpr int C = NT * 8;

@@ -55,7 +55,7 @@ constexpr int kIssuers = 2;                     // MMA-issuing warps (one electe
 constexpr int kFirstEpiWarp = 1 + kIssuers;
 constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);   // warp 0: loads, warps 1-2: MMA issue (warp 1 owns TMEM), warps 3..10: epilogue
 constexpr int kMaxWStages = 4;
-constexpr int kAStages = 2;
+constexpr int kAStages = 4;
 constexpr int kMaxAcc = 8;
 
 struct MmaParams {
@@ -85,7 +85,8 @@ struct MmaParams {
     int kgroup_chunks;      // chunks per ring stage
     int nwstages;
     int a_stage_bytes;
-    int astages;            // activation window stages (2, or 1 when shared memory is short)
+    int astages;            // activation window stages (up to 4; 1 when shared memory is short)
+    int ksplit, gchunks;    // resident form: a tile's K (input chunks) is staged in ksplit groups of gchunks chunks
     long long nrows;        // B * rows_per_sample
     int ntiles;
     int tiles_per_cta;
@@ -231,25 +232,23 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 }
             }
             uint32_t wcount = 0;
-            for (int it = 0; it < my_tiles; ++it) {
+            for (int item = 0; item < my_tiles * p.ksplit; ++item) {
+                const int it = item / p.ksplit, kgi = item - it * p.ksplit;
                 const int tile = tile_begin + it;
-                const int stage = it % p.astages;
-                const uint32_t ph = (it / p.astages) & 1;
+                const int stage = item % p.astages;
+                const uint32_t ph = (item / p.astages) & 1;
                 const long long d0 = (long long)tile * p.tile_rows + p.d_lead;
                 mbar_wait(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
-#ifdef CD_MMA_DEBUG
-                if ((p.dbg_mode & 2) && it >= p.astages) { mbar_arrive(smem_u32(&ctl->a_full[stage])); continue; }
-#endif
                 mbar_expect_tx(smem_u32(&ctl->a_full[stage]), p.a_stage_bytes);
-                int ch = 0;
-                for (int s = 0; s < 2; ++s) {
-                    for (int k = 0; k < p.src_chunks[s]; ++k, ++ch) {
-                        const __half* plane0 = p.src[s] + plcp_offset(g, k, 0);
-                        for (int w = 0; w < p.nwin; ++w) {
-                            const long long r0 = d0 + p.row0 + (long long)(w - (p.nwin >> 1)) * p.win_dz;
-                            bulk_g2s(abuf_s + stage * p.a_stage_bytes + ch * chunk_bytes + w * win_bytes, plane0 + r0 * 8, win_bytes,
-                                     smem_u32(&ctl->a_full[stage]));
-                        }
+                for (int ch = 0; ch < p.gchunks; ++ch) {
+                    const int c = kgi * p.gchunks + ch;                     // chunk of the (concatenated) input
+                    const int sidx = c < p.src_chunks[0] ? 0 : 1;
+                    const int k = sidx ? c - p.src_chunks[0] : c;
+                    const __half* plane0 = p.src[sidx] + plcp_offset(g, k, 0);
+                    for (int w = 0; w < p.nwin; ++w) {
+                        const long long r0 = d0 + p.row0 + (long long)(w - (p.nwin >> 1)) * p.win_dz;
+                        bulk_g2s(abuf_s + stage * p.a_stage_bytes + ch * chunk_bytes + w * win_bytes, plane0 + r0 * 8, win_bytes,
+                                 smem_u32(&ctl->a_full[stage]));
                     }
                 }
                 if (!p.resident) {
@@ -292,37 +291,57 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             const int nq = p.nchunks >> 1;
             uint32_t cnt = 0, wcount = 0;
             if (p.resident) mbar_wait(smem_u32(&ctl->w_res), 0);
+            const int gq = p.gchunks >> 1;                       // K16 steps per staged K group
+            const uint32_t bshift = (uint32_t)p.nchunks * N;     // weight offset (16-byte units) between (dz,dp) shifts
             for (int it = 0; it < my_tiles; ++it) {
+                if (p.resident) {
+                    // a tile's K range arrives in ksplit stages; every sub-tile accumulator stays open until the last one
+                    for (int kgi = 0; kgi < p.ksplit; ++kgi) {
+                        const int item = it * p.ksplit + kgi;
+                        const int stage = item % p.astages;
+                        const uint32_t ph = (item / p.astages) & 1;
+                        const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
+                        const uint32_t b_lo0 = (wbuf_s >> 4) + (uint32_t)(kgi * p.gchunks) * N;
+                        const long long tA = DBG_T();
+                        mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
+                        if (blockIdx.x == 0 && iw == 0) { DBG_ADD(0, DBG_T() - tA); DBG_ADD(3, 1); }
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        bool issued = false;
+                        for (int j = 0; j < p.MT; ++j) {
+                            const uint32_t n = cnt + j;
+                            if ((n & 1u) != iw) continue;
+                            const uint32_t a_lo = a_lo0 + (uint32_t)j * jstep;
+                            const uint32_t slot = slot_of(n), tph = phase_of(n);
+                            const uint32_t dcol = tmem_base + slot * N;
+                            const long long tB = DBG_T();
+                            if (kgi == 0) {
+                                mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            }
+                            const long long tC = DBG_T();
+#pragma unroll
+                            for (int s = 0; s < NS; ++s) {
+                                uint32_t al = a_lo + soff[s], b_lo = b_lo0 + (uint32_t)s * bshift;
+                                for (int q = 0; q < gq; ++q, al += qstep, b_lo += bstep)
+                                    umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (kgi | s | q) != 0);
+                            }
+                            if (kgi == p.ksplit - 1) umma_commit(smem_u32(&ctl->t_full[slot]));
+                            issued = true;
+                            if (blockIdx.x == 0 && iw == 0) { DBG_ADD(1, tC - tB); DBG_ADD(2, DBG_T() - tC); }
+                        }
+                        if (issued) umma_commit(smem_u32(&ctl->a_empty[stage]));
+                        else mbar_arrive(smem_u32(&ctl->a_empty[stage]));
+                    }
+                    cnt += p.MT;
+                    continue;
+                }
                 const int stage = it % p.astages;
                 const uint32_t ph = (it / p.astages) & 1;
                 const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
-                const long long tA = DBG_T();
                 mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
-                if (blockIdx.x == 0 && iw == 0) { DBG_ADD(0, DBG_T() - tA); DBG_ADD(3, 1); }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 bool issued = false;
-                if (p.resident) {
-                    for (int j = 0; j < p.MT; ++j, ++cnt) {
-                        if ((cnt & 1u) != iw) continue;
-                        const uint32_t a_lo = a_lo0 + (uint32_t)j * jstep;
-                        const uint32_t slot = slot_of(cnt), tph = phase_of(cnt);
-                        const uint32_t dcol = tmem_base + slot * N;
-                        const long long tB = DBG_T();
-                        mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
-                        const long long tC = DBG_T();
-                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        uint32_t b_lo = wbuf_s >> 4;
-#pragma unroll
-                        for (int s = 0; s < NS; ++s) {
-                            uint32_t al = a_lo + soff[s];
-                            for (int q = 0; q < nq; ++q, al += qstep, b_lo += bstep)
-                                umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (s | q) != 0);
-                        }
-                        umma_commit(smem_u32(&ctl->t_full[slot]));
-                        issued = true;
-                        if (blockIdx.x == 0 && iw == 0) { DBG_ADD(1, tC - tB); DBG_ADD(2, DBG_T() - tC); }
-                    }
-                } else {
+                {
                     for (int j = 0; j < p.MT; ++j) {
                         const uint32_t n = cnt + j, slot = slot_of(n), tph = phase_of(n);
                         if ((n & 1u) == iw) mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
@@ -455,6 +474,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         }
                     }
                     tmem_ld_wait();
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(9, DBG_T() - tE1);
                     if (c0 + CW >= CB) {
                         // last TMEM read of this sub-tile: the accumulator slot is free again
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -471,6 +491,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         for (int k = 0; k < W; k += 4) if (k < w) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
                     }
                     asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
                     if (lane == 31) {       // row m-1 of the next quarter's lane 0 is this quarter's lane 31; it receives lane 31's r0 by rotation
                         const float* src = xup + (q > 0 ? q - 1 : 0) * 64 + c0;
 #pragma unroll
@@ -496,6 +517,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             }
                         }
                     }
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
 #pragma unroll
                     for (int k = 0; k < W; k += 8) {
                         if (k < w) {
@@ -506,6 +528,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
                         }
                     }
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(12, DBG_T() - tE1);
                     if (p.stats && valid) {
                         if (uniform) {
 #pragma unroll
@@ -525,23 +548,29 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                 }
             } else {
-                // 1x1x1: no recombination, no statistics: stream 16 columns at a time
+                // 1x1x1: no recombination, no statistics: batches of up to 48 columns with all TMEM loads in flight at once
+                constexpr int BW = (CB % 48 == 0) ? 48 : ((CB % 32 == 0) ? 32 : 16);
 #pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += 16) {
-                    uint32_t r1[16];
-                    tmem_ld16_issue(taddr + c0, r1);
+                for (int c0 = 0; c0 < CB; c0 += BW) {
+                    uint32_t r1[BW];
+#pragma unroll
+                    for (int k = 0; k < BW; k += 16) tmem_ld16_issue(taddr + c0 + k, r1 + k);
                     tmem_ld_wait();
-                    if (c0 + 16 >= CB) {
+                    if (c0 + BW >= CB) {
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         __syncwarp();
                         if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
                     }
-                    float acc[16];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[k] = __uint_as_float(r1[k]) + sbias[c0 + k];
-#pragma unroll
-                    for (int k = 0; k < 16; k += 8) {
-                        const Half8 h = pack8(acc + k);
+                    for (int k = 0; k < BW; k += 8) {
+                        const float4 b0 = *reinterpret_cast<const float4*>(sbias + c0 + k);
+                        const float4 b1 = *reinterpret_cast<const float4*>(sbias + c0 + k + 4);
+                        float acc[8];
+                        acc[0] = __uint_as_float(r1[k]) + b0.x; acc[1] = __uint_as_float(r1[k + 1]) + b0.y;
+                        acc[2] = __uint_as_float(r1[k + 2]) + b0.z; acc[3] = __uint_as_float(r1[k + 3]) + b0.w;
+                        acc[4] = __uint_as_float(r1[k + 4]) + b1.x; acc[5] = __uint_as_float(r1[k + 5]) + b1.y;
+                        acc[6] = __uint_as_float(r1[k + 6]) + b1.z; acc[7] = __uint_as_float(r1[k + 7]) + b1.w;
+                        const Half8 h = pack8(acc);
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
                         if (valid) *reinterpret_cast<Half8*>(o) = h;
                         if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
@@ -664,29 +693,45 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     const size_t fixed = kCtlBytes + kXchBytes + 256;
     bool found = false;
     size_t smem_total = 0;
-    for (int astages = kAStages; astages >= 1 && !found; --astages) {
-        for (int resident = 1; resident >= 0 && !found; --resident) {
-            const size_t wbytes = resident ? (size_t)p.w_bytes_cb : (size_t)p.nwstages * p.wstage_bytes;
-            for (int mt = 4; mt >= 1 && !found; --mt) {
-                if (resident ? (p.nacc < 2 && mt > 1) : (mt > p.nacc)) continue;
-                const int span = p.sub_stride * (mt - 1) + 128;
-                int nwin = 1, wrows = span, row0 = 0, win_dz = 0, off_dz = 0, off_dp = 0;
-                if (k3) {
-                    const int uni = span + 2 * g.plane + 2 * g.Rp, three = 3 * (span + 2 * g.Rp);
-                    if (uni <= three) { nwin = 1; wrows = uni; row0 = -(g.plane + g.Rp); win_dz = 0; off_dz = g.plane; off_dp = g.Rp; }
-                    else { nwin = 3; wrows = span + 2 * g.Rp; row0 = -g.Rp; win_dz = g.plane; off_dz = 0; off_dp = g.Rp; }
-                }
-                const size_t a_stage = (size_t)p.nchunks * nwin * wrows * 16;
-                const size_t total = fixed + (wbytes + 127) / 128 * 128 + astages * a_stage;
-                if (total > (size_t)max_smem) continue;
-                if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
-                p.resident = resident; p.MT = mt; p.nwin = nwin; p.wrows = wrows; p.row0 = row0; p.win_dz = win_dz;
-                p.off_dz = off_dz; p.off_dp = off_dp; p.a_stage_bytes = (int)a_stage; p.astages = astages;
-                smem_total = total;
-                found = true;
-            }
+    // window geometry of a tile of mt sub-tiles: one union window per chunk, or one window per dz when planes are large
+    auto window = [&](int mt, int& nwin, int& wrows, int& row0, int& win_dz, int& off_dz, int& off_dp) {
+        const int span = p.sub_stride * (mt - 1) + 128;
+        nwin = 1; wrows = span; row0 = 0; win_dz = 0; off_dz = 0; off_dp = 0;
+        if (k3) {
+            const int uni = span + 2 * g.plane + 2 * g.Rp, three = 3 * (span + 2 * g.Rp);
+            if (uni <= three) { nwin = 1; wrows = uni; row0 = -(g.plane + g.Rp); win_dz = 0; off_dz = g.plane; off_dp = g.Rp; }
+            else { nwin = 3; wrows = span + 2 * g.Rp; row0 = -g.Rp; win_dz = g.plane; off_dz = 0; off_dp = g.Rp; }
         }
+    };
+    auto accept = [&](int resident, int ksplit, int mt, int astages) -> bool {
+        int nwin, wrows, row0, win_dz, off_dz, off_dp;
+        window(mt, nwin, wrows, row0, win_dz, off_dz, off_dp);
+        const int gchunks = p.nchunks / ksplit;
+        const size_t wbytes = resident ? (size_t)p.w_bytes_cb : (size_t)p.nwstages * p.wstage_bytes;
+        const size_t a_stage = (size_t)gchunks * nwin * wrows * 16;
+        const size_t total = fixed + (wbytes + 127) / 128 * 128 + astages * a_stage;
+        if (total > (size_t)max_smem) return false;
+        p.resident = resident; p.ksplit = ksplit; p.gchunks = gchunks; p.MT = mt; p.nwin = nwin; p.wrows = wrows; p.row0 = row0;
+        p.win_dz = win_dz; p.off_dz = off_dz; p.off_dp = off_dp; p.a_stage_bytes = (int)a_stage; p.astages = astages;
+        smem_total = total;
+        return true;
+    };
+    // 1) weights resident, >= 2 activation stages; K staged in as few groups as fit; largest tile first (least halo re-read).
+    //    With K staged in groups all of a tile's accumulators stay open together: keep one slot free for the epilogue.
+    for (int ksplit = 1; ksplit <= 8 && !found; ksplit *= 2) {
+        if (p.nchunks % ksplit != 0 || (p.nchunks / ksplit) % 2 != 0) continue;
+        const int mt_max = ksplit > 1 ? (p.nacc - 1 < 4 ? p.nacc - 1 : 4) : 4;
+        for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
+            for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
     }
+    // 2) otherwise: weights streamed through the ring (K unsplit), then single-stage forms
+    for (int astages = 2; astages >= 1 && !found; --astages)
+        for (int resident = (astages == 1 ? 1 : 0); resident >= 0 && !found; --resident)
+            for (int mt = 4; mt >= 1 && !found; --mt) {
+                if (!resident && mt > p.nacc) continue;
+                if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
+                found = accept(resident, 1, mt, astages);
+            }
     if (!found) return 1;
     p.tile_rows = p.sub_stride * p.MT;
     p.ntiles = (int)((p.nrows + p.tile_rows - 1) / p.tile_rows);

@@ -326,19 +326,26 @@ void launch_gn_apply(const Geom& g, const __half* src, const double* stats, cons
 // SiLU -> Linear(cond_dim, C) projection (:176-178, :195), one block per sample.
 // time input = do_time_embed(sigma) (calodiffusion.py:144-155).
 // =================================================================================================
+// out[o] = act(bias[o] + sum_i W[o][i] in[i]): one warp per output row so the weight reads are coalesced
 __device__ void dense_layer(const float* __restrict__ W, const float* __restrict__ bias, const float* in, float* out,
                             int n_in, int n_out, int act) {
-    for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
-        float a = bias ? bias[o] : 0.f;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int o = warp; o < n_out; o += nwarps) {
         const float* w = W + (long long)o * n_in;
-        for (int i = 0; i < n_in; ++i) a += w[i] * in[i];
-        if (act == 1) a = gelu_erf(a);
-        out[o] = a;
+        float a = 0.f;
+        for (int i = lane; i < n_in; i += 32) a = fmaf(__ldg(w + i), in[i], a);
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) a += __shfl_xor_sync(0xffffffffu, a, s);
+        if (lane == 0) {
+            a += bias ? bias[o] : 0.f;
+            if (act == 1) a = gelu_erf(a);
+            out[o] = a;
+        }
     }
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(128) embed_kernel(EmbedParams p, const float* __restrict__ sigma, int sigma_stride,
+__global__ void __launch_bounds__(256) embed_kernel(EmbedParams p, const float* __restrict__ sigma, int sigma_stride,
                                                     const float* __restrict__ cond, float* __restrict__ addvec) {
     __shared__ float buf0[256], buf1[256], cvec[256];
     int b = blockIdx.x;
@@ -358,23 +365,27 @@ __global__ void __launch_bounds__(128) embed_kernel(EmbedParams p, const float* 
     dense_layer(p.cw[2], p.cb[2], buf0, cvec + half_dim, half_dim, half_dim, 0);  // conditions[half:] = c
     for (int i = threadIdx.x; i < p.cond_dim; i += blockDim.x) cvec[i] = silu_f(cvec[i]);
     __syncthreads();
+    // every ResnetBlock's Linear(cond_dim, C) on the shared SiLU(conditions) (models.py:176-178,195): warp per output
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
     for (int k = 0; k < p.n_proj; ++k) {
         const float* W = p.pw[k];
         const float* bias = p.pb[k];
-        int C = p.pC[k];
+        const int C = p.pC[k];
         float* out = addvec + (long long)b * p.addvec_stride + p.poff[k];
-        for (int o = threadIdx.x; o < C; o += blockDim.x) {
-            float a = bias[o];
+        for (int o = warp; o < C; o += nwarps) {
             const float* w = W + (long long)o * p.cond_dim;
-            for (int i = 0; i < p.cond_dim; ++i) a += w[i] * cvec[i];
-            out[o] = a;
+            float a = 0.f;
+            for (int i = lane; i < p.cond_dim; i += 32) a = fmaf(__ldg(w + i), cvec[i], a);
+#pragma unroll
+            for (int s = 16; s > 0; s >>= 1) a += __shfl_xor_sync(0xffffffffu, a, s);
+            if (lane == 0) out[o] = a + bias[o];
         }
     }
 }
 
 void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, const float* cond, float* addvec, int B,
                   cudaStream_t st) {
-    embed_kernel<<<B, 128, 0, st>>>(p, sigma, sigma_stride, cond, addvec);
+    embed_kernel<<<B, 256, 0, st>>>(p, sigma, sigma_stride, cond, addvec);
 }
 
 // =================================================================================================
