@@ -217,6 +217,8 @@ def run_gpu_arm(args, wl):
     cfg, B, steps = dict(wl["cfg"]), int(args.batch or wl["batch"]), int(args.sampling_steps or wl["steps"])
     torch.manual_seed(0)                                   # identical random-init weights on every rank
     model = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=B)
+    if os.environ.get("CD_NO_GRAPH"):
+        model.use_graph = False                            # diagnostics: eager launches instead of one CUDA graph
     sampler = model.sampler_algorithm
     sampler.shower_offset = rank * B                       # global shower index keys the Philox stream
     if wl["sampler"] == "Heun":
@@ -238,7 +240,7 @@ def run_gpu_arm(args, wl):
     def device_step():
         x, _, _ = sampler(model, start_dev, E_dev, L_dev, steps, 0, False)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, x.reshape(B, vox))
+            dist.all_gather_into_tensor(gathered, x.reshape(B, vox))   # the one collective of the path
         return x
 
     def api_step():

@@ -183,6 +183,14 @@ class CaloDiffusion(Diffusion):
     def noise_generation(self, shape):
         return super().noise_generation(shape)
 
+    def philox_normal(self, n_showers, seed, shower_offset=0, slot=0):
+        """N(0,1) of shape (n_showers, *data_shape) from the library's Philox stream, keyed by global shower index
+        (`shower_offset` + row): a sharded batch regenerates exactly the rows of the unsharded one."""
+        out = torch.empty([int(n_showers)] + list(self._data_shape), device=self.device, dtype=torch.float32)
+        _lib.check(self._lib.cd_fill_normal(out.data_ptr(), int(n_showers), self._voxels, int(seed) & (2 ** 64 - 1),
+                                            int(shower_offset), int(slot), self._stream()), "fill_normal")
+        return out
+
     def load_state_dict(self, state_dict, strict=True):
         """models/calodiffusion.py:31-37: strip a foreign top-level prefix (peeks at the 11th key)."""
         base = list(state_dict.keys())[10].split(".")[0]

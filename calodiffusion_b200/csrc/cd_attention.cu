@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) attn_kmax_kernel(Geom g, const __half* __
 
 // ---------------------------------------------------------------------------------------------------------
 // ctx layout: [B][33][32] floats: rows 0..31 = Ctx[d][e], row 32 = S[d]
-__global__ void __launch_bounds__(256, 3) attn_context_kernel(Geom g, const __half* __restrict__ qkv, const unsigned* __restrict__ kmax,
+__global__ void __launch_bounds__(256, 2) attn_context_kernel(Geom g, const __half* __restrict__ qkv, const unsigned* __restrict__ kmax,
                                                            float* __restrict__ ctx, int rows_per_block, int use_atomics) {
     __shared__ __align__(16) unsigned char slab[kWarps][2][32 * kRowStrideB];   // per warp: exp(k) rows, v rows
     __shared__ float red[33 * 32];
@@ -264,6 +264,7 @@ __global__ void __launch_bounds__(256, NT <= 4 ? 3 : 2) attn_out_kernel(Geom g, 
         }
         const bool interior = inb && decode_subrow(g, rem).kind == 0;
         const unsigned vmask = __ballot_sync(0xffffffffu, interior);
+        const unsigned imask = __ballot_sync(0xffffffffu, inb);     // rows to store: all of them (whole sectors); zeros outside the interior
         float mx = q[0];
 #pragma unroll
         for (int j = 1; j < 32; ++j) mx = fmaxf(mx, q[j]);
@@ -284,24 +285,21 @@ __global__ void __launch_bounds__(256, NT <= 4 ? 3 : 2) attn_out_kernel(Geom g, 
             ldsm_x4(sq_s + mt * 16 * kRowStrideB + a_off, a[0]);        // d 0-15
             ldsm_x4(sq_s + mt * 16 * kRowStrideB + a_off + 32, a[1]);   // d 16-31
             const bool v0 = (vmask >> (mt * 16 + gq)) & 1u, v1 = (vmask >> (mt * 16 + gq + 8)) & 1u;
+            const bool s0 = (imask >> (mt * 16 + gq)) & 1u, s1 = (imask >> (mt * 16 + gq + 8)) & 1u;
             const long long row_a = srow0 + base + mt * 16 + gq;
 #pragma unroll
             for (int j = 0; j < NT; ++j) {
                 float c4[4] = {bias[j][0], bias[j][1], bias[j][0], bias[j][1]};
                 mma16816(c4, a[0], bfrag[j][0], bfrag[j][1]);
                 mma16816(c4, a[1], bfrag[j][2], bfrag[j][3]);
-                const __half2 h0 = __floats2half2_rn(c4[0], c4[1]), h1 = __floats2half2_rn(c4[2], c4[3]);
+                const __half2 zero2 = __floats2half2_rn(0.f, 0.f);
+                const __half2 h0 = v0 ? __floats2half2_rn(c4[0], c4[1]) : zero2, h1 = v1 ? __floats2half2_rn(c4[2], c4[3]) : zero2;
                 __half* o = dst + plcp_offset(g, j, row_a) + 2 * tq;
-                if (v0) {
-                    *reinterpret_cast<__half2*>(o) = h0;
-                    const float2 f = __half22float2(h0);
-                    ssum += f.x + f.y; ssq = fmaf(f.x, f.x, fmaf(f.y, f.y, ssq));
-                }
-                if (v1) {
-                    *reinterpret_cast<__half2*>(o + 64) = h1;      // row + 8
-                    const float2 f = __half22float2(h1);
-                    ssum += f.x + f.y; ssq = fmaf(f.x, f.x, fmaf(f.y, f.y, ssq));
-                }
+                if (s0) *reinterpret_cast<__half2*>(o) = h0;
+                if (s1) *reinterpret_cast<__half2*>(o + 64) = h1;      // row + 8
+                const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);   // zeros outside the interior: no effect on the sums
+                ssum += (f0.x + f0.y) + (f1.x + f1.y);
+                ssq = fmaf(f0.x, f0.x, fmaf(f0.y, f0.y, fmaf(f1.x, f1.x, fmaf(f1.y, f1.y, ssq))));
             }
         }
         __syncwarp();

@@ -415,10 +415,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
             const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
             // which output row is this?  (fast division by the level's constant extents)
-            bool valid = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
+            // 1x1x1 stores cover every row of the sub-tile (whole 32-byte sectors, no read-modify-write in L2/HBM): interior rows
+            // get the result, zero rows get zeros (the invariant every consumer relies on), phi halo rows get a don't-care value
+            // (re-derived from the interior by whoever needs them) unless this launch maintains them (write_halo).
+            const bool inrange = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
+            bool valid = inrange, phi_halo = false;
             int sample = -1;
             uint32_t pp = 0;
-            if (valid) {
+            if (inrange) {
                 const uint32_t ur = (uint32_t)row;
                 const uint32_t b = fdiv(g, 2, ur);
                 const uint32_t rem = ur - b * (uint32_t)g.rows_per_sample;
@@ -426,9 +430,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 const uint32_t rem2 = rem - z * (uint32_t)g.plane;
                 pp = fdiv(g, 1, rem2);
                 const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
-                valid = z < (uint32_t)g.Z && rr < (uint32_t)g.R && pp >= 1u && pp <= (uint32_t)g.P;
+                const bool nonzero_row = z < (uint32_t)g.Z && rr < (uint32_t)g.R;
+                valid = nonzero_row && pp >= 1u && pp <= (uint32_t)g.P;
+                phi_halo = nonzero_row && !valid;
                 sample = (int)b;
             }
+            // 1x1x1 (HBM-bound): whole-sector stores of every row.  3x3x3 (epilogue-bound): interior rows only, measured faster.
+            const bool do_store = K3 ? valid : (inrange && !(p.write_halo && phi_halo));
+            const bool keep = valid || (!K3 && phi_halo && !p.write_halo);
             const bool halo_up = valid && p.write_halo && pp == 1u;               // copy to pp = P+1
             const bool halo_dn = valid && p.write_halo && pp == (uint32_t)g.P;    // copy to pp = 0
             const long long tE0 = DBG_T();
@@ -521,9 +530,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #pragma unroll
                     for (int k = 0; k < W; k += 8) {
                         if (k < w) {
-                            const Half8 h = pack8(acc + k);
+                            Half8 h = pack8(acc + k);
+                            if (!keep) h = Half8{};
                             __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
-                            if (valid) *reinterpret_cast<Half8*>(o) = h;
+                            if (do_store) *reinterpret_cast<Half8*>(o) = h;
                             if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
                             if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
                         }
@@ -570,9 +580,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         acc[2] = __uint_as_float(r1[k + 2]) + b0.z; acc[3] = __uint_as_float(r1[k + 3]) + b0.w;
                         acc[4] = __uint_as_float(r1[k + 4]) + b1.x; acc[5] = __uint_as_float(r1[k + 5]) + b1.y;
                         acc[6] = __uint_as_float(r1[k + 6]) + b1.z; acc[7] = __uint_as_float(r1[k + 7]) + b1.w;
-                        const Half8 h = pack8(acc);
+                        Half8 h = pack8(acc);
+                        if (!keep) h = Half8{};
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
-                        if (valid) *reinterpret_cast<Half8*>(o) = h;
+                        if (do_store) *reinterpret_cast<Half8*>(o) = h;
                         if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
                         if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
                     }
@@ -724,14 +735,20 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
             for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
     }
-    // 2) otherwise: weights streamed through the ring (K unsplit), then single-stage forms
-    for (int astages = 2; astages >= 1 && !found; --astages)
-        for (int resident = (astages == 1 ? 1 : 0); resident >= 0 && !found; --resident)
-            for (int mt = 4; mt >= 1 && !found; --mt) {
-                if (!resident && mt > p.nacc) continue;
-                if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
-                found = accept(resident, 1, mt, astages);
-            }
+    // 2) otherwise: weights streamed through the 3-stage ring (K unsplit), two activation stages, largest tile that fits
+    //    (a 2-stage ring would admit larger tiles for 128-wide inputs but faulted on multi-tile CTAs: not used)
+    for (int mt = 4; mt >= 1 && !found; --mt) {
+        if (mt > p.nacc) continue;
+        found = accept(0, 1, mt, 2);
+    }
+    // 3) single-stage forms
+    p.nwstages = 3;
+    for (int resident = 1; resident >= 0 && !found; --resident)
+        for (int mt = 4; mt >= 1 && !found; --mt) {
+            if (!resident && mt > p.nacc) continue;
+            if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
+            found = accept(resident, 1, mt, 1);
+        }
     if (!found) return 1;
     p.tile_rows = p.sub_stride * p.MT;
     p.ntiles = (int)((p.nrows + p.tile_rows - 1) / p.tile_rows);

@@ -1,6 +1,9 @@
 // Engine: builds the CondUnet evaluation plan from a cd_unet_desc + reference-named weights, owns the
 // PLCP activation workspaces, and exposes the C ABI of include/calodiffusion_b200.h.
 #include <cmath>
+#include <csignal>
+#include <execinfo.h>
+#include <unistd.h>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -75,6 +78,7 @@ struct cd_unet {
     std::vector<cd::OpInfo> op_info;      // parallel to ops: name + algorithmic flops/bytes per shower
     std::map<std::string, cd::ProfAcc> prof;
     int profile = 0;
+    int debug_sync = 0;
     std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
     int conv_backend = 0;
@@ -536,7 +540,7 @@ static int build_plan(cd_unet* h) {
 
 static int run_forward(cd_unet* h, Run& r) {
     if (h->scratch_per_sample)
-        cudaMemsetAsync(h->scratch, 0, h->scratch_per_sample * (size_t)r.B, r.st);
+        { launch_copy_bytes(nullptr, h->scratch, h->scratch_per_sample * (size_t)r.B, r.st); h->launches += 1; }
     if (h->profile) {
         // eager per-op timing with CUDA events on the launch stream (diagnostic mode; not capturable):
         // events are recorded between the ops without host synchronisation, read back after the last op
@@ -551,6 +555,13 @@ static int run_forward(cd_unet* h, Run& r) {
             ProfAcc& a = h->prof[h->op_info[i].name];
             a.count += 1; a.ms += ms;
             a.flops += h->op_info[i].flops * r.B; a.bytes += h->op_info[i].bytes * r.B;
+        }
+    } else if (h->debug_sync) {
+        // diagnostic: synchronise after every op so a faulting kernel is reported by name
+        for (size_t i = 0; i < h->ops.size(); ++i) {
+            h->ops[i](r);
+            cudaError_t es = cudaStreamSynchronize(r.st);
+            if (es != cudaSuccess) return fail("op %zu (%s) failed: %s", i, h->op_info[i].name.c_str(), cudaGetErrorString(es));
         }
     } else {
         for (auto& op : h->ops) op(r);
@@ -670,6 +681,7 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
         if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
         return 0;
     }
+    if (!strcmp(key, "debug_sync")) { h->debug_sync = value; return 0; }
     if (!strcmp(key, "profile")) {
         h->profile = value;
         if (value == 2) { h->prof.clear(); h->profile = 1; }   // 2 = enable and reset
@@ -805,11 +817,12 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
         }
         if (run_forward(h, r)) return 1;
         if (e.x0_buf >= 0 && e.rec_x0 >= 0 && a.x0s)
-            cudaMemcpyAsync(a.x0s + (size_t)e.rec_x0 * n, h->state[e.x0_buf], bytes, cudaMemcpyDeviceToDevice, st);
+            { launch_copy_bytes(h->state[e.x0_buf], a.x0s + (size_t)e.rec_x0 * n, bytes, st); h->launches += 1; }
         if (e.rec_x >= 0 && a.xs)
-            cudaMemcpyAsync(a.xs + (size_t)e.rec_x * n, h->state[e.rec_x_buf], bytes, cudaMemcpyDeviceToDevice, st);
+            { launch_copy_bytes(h->state[e.rec_x_buf], a.xs + (size_t)e.rec_x * n, bytes, st); h->launches += 1; }
     }
-    cudaMemcpyAsync(a.x_final, h->state[a.final_buf], bytes, cudaMemcpyDeviceToDevice, st);
+    launch_copy_bytes(h->state[a.final_buf], a.x_final, bytes, st);
+    h->launches += 1;
     cudaError_t err = cudaPeekAtLastError();
     if (err != cudaSuccess) return fail("sample enqueue: %s", cudaGetErrorString(err));
     return 0;
@@ -817,9 +830,20 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
 
 }  // namespace cd
 
+static void cd_segv_handler(int sig) {
+    void* frames[64];
+    int n = backtrace(frames, 64);
+    const char msg[] = "calodiffusion_b200: fatal signal, native backtrace:\n";
+    (void)!write(2, msg, sizeof(msg) - 1);
+    backtrace_symbols_fd(frames, n, 2);
+    signal(sig, SIG_DFL);
+    raise(sig);
+}
+
 extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_scale, const float* cond_dev, const cd_eval* evals,
                              int n_evals, const float* noise_bank_dev, uint64_t seed, int shower_offset, int final_buf,
                              float* x_final_dev, float* xs_dev, float* x0s_dev, int B, void* stream, int use_graph) {
+    if (getenv("CD_SEGV_TRACE")) signal(SIGSEGV, cd_segv_handler);   // diagnostic: native backtrace on a crash
     if (check_call(h, B)) return 1;
     if (n_evals < 1 || n_evals + 1 > h->coef_cap) return fail("n_evals %d outside [1, %d]", n_evals, h->coef_cap - 1);
     if (final_buf < 0 || final_buf >= CD_NUM_STATE_BUFS) return fail("bad final_buf");

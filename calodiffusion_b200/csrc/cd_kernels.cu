@@ -488,6 +488,25 @@ void launch_axpby(const float* x, const float* noise, float* out, const float* c
                                                               rng_enabled);
 }
 
+// plain device copy / clear as kernels: inside the captured sampling graph these replace cudaMemcpyAsync / cudaMemsetAsync
+// nodes (a graph holding large copy-engine memcpy nodes crashed cuGraphLaunch when NCCL peer mappings were active)
+__global__ void copy16_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, long long n16, const unsigned char* __restrict__ src_tail,
+                              unsigned char* __restrict__ dst_tail, int tail) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) dst[i] = src ? src[i] : make_uint4(0u, 0u, 0u, 0u);
+    if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail ? src_tail[threadIdx.x] : 0;
+}
+void launch_copy_bytes(const void* src, void* dst, size_t bytes, cudaStream_t st) {
+    // src == nullptr clears dst.  Both pointers must be 16-byte aligned (all library and torch allocations are).
+    const long long n16 = (long long)(bytes / 16);
+    const int tail = (int)(bytes % 16);
+    long long blocks = (n16 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    const unsigned char* st_ = src ? (const unsigned char*)src + n16 * 16 : nullptr;
+    copy16_kernel<<<(unsigned)blocks, 256, 0, st>>>((const uint4*)src, (uint4*)dst, n16, st_, (unsigned char*)dst + n16 * 16, tail);
+}
+
 __global__ void fill_normal_kernel(float* out, long long n, int vps, uint64_t seed, int shower_offset, int step) {
     long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;

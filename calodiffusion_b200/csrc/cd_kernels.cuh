@@ -43,6 +43,7 @@ void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, co
 void launch_final(const FinalParams& p, int B, cudaStream_t st);
 void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps,
                   unsigned long long seed, int shower_offset, int step, int rng_enabled, cudaStream_t st);
+void launch_copy_bytes(const void* src /* nullptr: clear */, void* dst, size_t bytes, cudaStream_t st);
 void launch_fill_normal(float* out, long long n, int vps, unsigned long long seed, int shower_offset, int step,
                         cudaStream_t st);
 

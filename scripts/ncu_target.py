@@ -25,6 +25,10 @@ E = torch.rand(B, 1, generator=g).cuda()
 L = torch.randn(B, wl["n_layers"], generator=g).cuda() if wl["n_layers"] else None
 x = torch.randn([B] + cfg["SHAPE_PAD"][1:], device="cuda")
 sig = torch.full((B,), 1.5, device="cuda")
+if os.environ.get("CD_DEBUG_SYNC"):
+    m.denoise(x[:1], E=E[:1], sigma=sig[:1], layers=None if L is None else L[:1])
+    from calodiffusion_b200 import _lib
+    _lib.check(m._lib.cd_unet_set_option(m._handle, b"debug_sync", 1), "set_option")
 for _ in range(a.evals):
     y = m.denoise(x, E=E, sigma=sig, layers=L)
 torch.cuda.synchronize()

@@ -126,6 +126,21 @@ def test_tcgen05_conv_variants(models, case):
     assert max(errs.values()) < TOL_LAYER, errs
 
 
+def test_tcgen05_conv_many_tiles_per_cta():
+    """Batches large enough that every persistent CTA walks several tiles (stage/phase wrap-around of all pipelines):
+    resident, K-staged resident and streamed-weight forms."""
+    m, c = _model("ds2", max_batch=48)
+    lib = m._lib
+    errs = {}
+    errs["k3_l1_128_32_stream"] = _conv_case(m, lib, 1, 1, 128, 32, (3, 3, 3), (1, 1, 1), False, 0, B=48)
+    errs["k3_l1_64_64_stream"] = _conv_case(m, lib, 1, 1, 64, 64, (3, 3, 3), (1, 1, 1), False, 0, B=48)
+    errs["k3_l0_64_32_kstaged"] = _conv_case(m, lib, 0, 0, 64, 32, (3, 3, 3), (1, 1, 1), False, 0, B=24)
+    errs["k3_l0_32_32"] = _conv_case(m, lib, 0, 0, 32, 32, (3, 3, 3), (1, 1, 1), False, 0, B=24)
+    errs["k1_l0_32_96"] = _conv_case(m, lib, 0, 0, 32, 96, (1, 1, 1), (1, 1, 1), False, 0, B=24)
+    print({k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
 @pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
 def test_denoise_generic_backend(models, case):
     """Same golden check with the SIMT convolution everywhere (conv_backend=1)."""
