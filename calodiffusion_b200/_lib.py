@@ -11,7 +11,7 @@ CD_NUM_STATE_BUFS = 4
 EXPORTS = [
     "cd_last_error", "cd_version", "cd_device_check", "cd_unet_create", "cd_unet_destroy", "cd_unet_set_weight",
     "cd_unet_finalize", "cd_unet_set_option", "cd_unet_workspace_bytes", "cd_unet_launch_count", "cd_unet_forward",
-    "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
+    "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_reverse_norm", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
 ]
 
 
@@ -35,6 +35,14 @@ class Eval(C.Structure):
         ("noise_index", C.c_int),
         ("pre_a", C.c_float), ("pre_b", C.c_float), ("pre_noise_index", C.c_int),
         ("rec_x0", C.c_int), ("rec_x", C.c_int), ("rec_x_buf", C.c_int),
+    ]
+
+
+class ReverseNormDesc(C.Structure):
+    _fields_ = [
+        ("Z", C.c_int), ("PR", C.c_int), ("logit_mean", C.c_float), ("logit_std", C.c_float),
+        ("totalE_mean", C.c_float), ("totalE_std", C.c_float), ("layers_mean", C.c_float), ("layers_std", C.c_float),
+        ("emin", C.c_float), ("emax", C.c_float), ("max_deposit", C.c_float), ("ecut", C.c_float),
     ]
 
 
@@ -74,6 +82,7 @@ def load():
     lib.cd_denoise.argtypes = [vp, vp, vp, vp, vp, i32, vp]
     lib.cd_sample_run.argtypes = [vp, vp, f32, vp, C.POINTER(Eval), i32, vp, u64, i32, i32, vp, vp, vp, i32, vp, i32]
     lib.cd_fill_normal.argtypes = [vp, i64, i64, u64, i32, i32, vp]
+    lib.cd_reverse_norm.argtypes = [C.POINTER(ReverseNormDesc), vp, vp, vp, vp, vp, i32, vp]
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
     lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]

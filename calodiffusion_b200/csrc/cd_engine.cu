@@ -769,6 +769,24 @@ int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t s
     return 0;
 }
 
+int cd_reverse_norm(const cd_reverse_norm_desc* d, const float* vox_dev, const float* e_dev, const float* layerE_dev,
+                    float* out_dev, float* energy_out_dev, int B, void* stream) {
+    if (!d || !vox_dev || !e_dev || !out_dev) return fail("null argument");
+    if (cd_device_check()) return 1;
+    if (B < 1 || B > 65535 || d->Z < 1 || d->Z > 65535 || d->PR < 1) return fail("bad reverse_norm shape");
+    if (!(d->emin > 0.f) || !(d->emax > 0.f) || !(d->logit_std > 0.f)) return fail("bad reverse_norm constants");
+    RevNormParams p;
+    p.vox = vox_dev; p.e = e_dev; p.layerE = layerE_dev; p.out = out_dev; p.energy_out = energy_out_dev;
+    p.Z = d->Z; p.PR = d->PR;
+    p.logit_mean = d->logit_mean; p.logit_std = d->logit_std; p.totalE_mean = d->totalE_mean; p.totalE_std = d->totalE_std;
+    p.layers_mean = d->layers_mean; p.layers_std = d->layers_std; p.emin = d->emin; p.emax = d->emax;
+    p.max_deposit = d->max_deposit; p.ecut = d->ecut;
+    launch_reverse_norm(p, B, (cudaStream_t)stream);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("reverse_norm: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 }  // extern "C"
 
 // -------------------------------------------------------------------------------------------------

@@ -27,6 +27,15 @@ struct FinalParams {
     int rng_enabled; unsigned long long seed; int shower_offset; int step;
 };
 
+struct RevNormParams {
+    const float* vox; const float* e; const float* layerE;   // (B,Z,PR), (B), (B,Z+1) or nullptr
+    float* out; float* energy_out;                          // (B,Z*PR), (B) or nullptr
+    int Z, PR;
+    float logit_mean, logit_std, totalE_mean, totalE_std, layers_mean, layers_std;
+    float emin, emax, max_deposit, ecut;
+};
+void launch_reverse_norm(const RevNormParams& p, int B, cudaStream_t st);
+
 void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,
                        const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks, int B, cudaStream_t st);
 void launch_conv_generic(const ConvParams& p, cudaStream_t st);

@@ -18,6 +18,8 @@
  *           EDMAbstract.for_loop + Euler/Heun.in_loop_sampler (models/sample.py:631-662, 784-821),
  *           expressed as a table of evaluations (see cd_eval) built by the host-side sampler classes
  *   cd_fill_normal   -> Diffusion.noise_generation (models/diffusion.py:58-61)
+ *   cd_reverse_norm  -> ReverseNormCaloChall (utils/utils.py:446-573; called at models/diffusion.py:171-191) for the
+ *           CaloChallenge '*logit-norm' shower maps (dataset 2 / 3)
  */
 #ifndef CALODIFFUSION_B200_H
 #define CALODIFFUSION_B200_H
@@ -108,6 +110,19 @@ int cd_sample_run(cd_unet* h, const float* start_dev, float start_scale, const f
 /* out[b][v] = N(0,1) from the library's Philox stream (slot = `slot`) */
 int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t seed, int shower_offset,
                    int slot, void* stream);
+
+/* Post-processing of sampled showers.  Constants come from utils/consts.py:dataset_params[dataset_num]. */
+typedef struct cd_reverse_norm_desc {
+    int Z, PR;                        /* calorimeter layers, voxels per layer (P*R) */
+    float logit_mean, logit_std;
+    float totalE_mean, totalE_std, layers_mean, layers_std;   /* used only with layerE ('layer' shower maps) */
+    float emin, emax;                 /* incident energy = emin*(emax/emin)^e (logE) */
+    float max_deposit, ecut;          /* ecut <= 0: no threshold */
+} cd_reverse_norm_desc;
+/* vox_dev (B,Z,PR) network-space showers, e_dev (B) scaled incident energies, layerE_dev (B,Z+1) = [totalE, layers] or
+ * NULL; writes out_dev (B,Z*PR) deposited energies and, if not NULL, energy_out_dev (B) incident energies. */
+int cd_reverse_norm(const cd_reverse_norm_desc* desc, const float* vox_dev, const float* e_dev, const float* layerE_dev,
+                    float* out_dev, float* energy_out_dev, int B, void* stream);
 
 /* test hooks: one layer in isolation on PLCP tensors held by the handle (used by tests/ only) */
 int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,
