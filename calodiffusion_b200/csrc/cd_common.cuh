@@ -124,6 +124,13 @@ struct ConvParams {
     int write_halo;     // 1: produce all rows incl. halos (gather form); 0: interior rows only
     double* stats;      // [B][Cout][2] (sum, sumsq) or nullptr
     int stats_cpg;      // channels per GroupNorm group: producers may accumulate a whole group into its first channel slot
+    // Folded PreNorm (1x1x1 tcgen05 form only): the input is x, the weights are W*diag(gamma) of a GroupNorm(1,C) and the
+    // epilogue applies  y = rstd_b * acc - mean_b*rstd_b*pn_wsum[o] + pn_wb[o]  with the per-sample statistics pn_stats
+    const double* pn_stats;   // [B][pn_C][2]: whole-sample (sum, sumsq) in the channel-0 slot; nullptr = plain conv
+    const float* pn_wsum;     // [Cout] sum_c W'[o][c] (of the fp16-rounded folded weights)
+    const float* pn_wb;       // [Cout] sum_c W[o][c]*beta[c]
+    int pn_C;                 // channels of the normalised tensor
+    double pn_count;          // elements per sample (C * voxels)
     int B;
 };
 

@@ -92,6 +92,7 @@ struct MmaParams {
     int tiles_per_cta;
     uint32_t idesc;
     int write_halo;         // 1: interior rows with pp == 1 / pp == P are also stored to their phi halo copies
+    const double* pn_stats; const float* pn_wsum; const float* pn_wb; int pn_C; float pn_inv_count;   // folded PreNorm (1x1x1)
     int dbg_mode;           // CD_MMA_DEBUG builds only: 1 = epilogue does nothing but release slots, 2 = load A only once
 };
 
@@ -172,7 +173,7 @@ struct SmemCtl {
 };
 constexpr int kCtlBytes = 512;
 constexpr int kXchFloats = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64;
-constexpr int kXchBytes = kXchFloats * 4 + 512;   // 8 KB exchange + 128 floats of bias
+constexpr int kXchBytes = kXchFloats * 4 + 1024;  // 8 KB exchange + 128 floats of bias + 128 floats of folded-PreNorm weight sums
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
 template <int CB, bool K3, int CPG>   // CPG: channels per GroupNorm group for the statistics (divides CB)
@@ -385,7 +386,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
         const int group = (warp - kFirstEpiWarp) >> 2;   // 0 / 1: the two groups alternate sub-tiles
         const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
         float* sbias = xch + kXchFloats;          // bias of this channel block, broadcast-read from shared memory
-        for (int c = threadIdx.x - 32 * kFirstEpiWarp; c < CB; c += 32 * kEpiWarps) sbias[c] = p.bias ? __ldg(p.bias + cb * CB + c) : 0.f;
+        float* swsum = sbias + 128;              // folded PreNorm: sum_c W'[o][c]; sbias then holds sum_c W[o][c]*beta[c]
+        for (int c = threadIdx.x - 32 * kFirstEpiWarp; c < CB; c += 32 * kEpiWarps) {
+            sbias[c] = p.pn_stats ? __ldg(p.pn_wb + cb * CB + c) : (p.bias ? __ldg(p.bias + cb * CB + c) : 0.f);
+            swsum[c] = p.pn_stats ? __ldg(p.pn_wsum + cb * CB + c) : 0.f;
+        }
         asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
         constexpr int NG = K3 ? CB / CPG : 1;     // statistics groups per channel block
         float gs[NG], gq[NG];                     // this thread's running sum / sum of squares per group (sample cur_b)
@@ -560,6 +565,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             } else {
                 // 1x1x1: no recombination, no statistics: batches of up to 48 columns with all TMEM loads in flight at once
                 constexpr int BW = (CB % 48 == 0) ? 48 : ((CB % 32 == 0) ? 32 : 16);
+                // folded PreNorm: y = rstd*acc + (wb - mean*rstd*wsum), statistics of this row's sample
+                float pn_a = 1.f, pn_m = 0.f;
+                if (p.pn_stats && inrange) {
+                    const double* st = p.pn_stats + (long long)sample * p.pn_C * 2;
+                    const double mean = st[0] * (double)p.pn_inv_count;
+                    double var = st[1] * (double)p.pn_inv_count - mean * mean;
+                    if (var < 0.0) var = 0.0;
+                    pn_a = rsqrtf((float)var + 1e-5f);
+                    pn_m = -(float)mean * pn_a;
+                }
 #pragma unroll
                 for (int c0 = 0; c0 < CB; c0 += BW) {
                     uint32_t r1[BW];
@@ -576,10 +591,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         const float4 b0 = *reinterpret_cast<const float4*>(sbias + c0 + k);
                         const float4 b1 = *reinterpret_cast<const float4*>(sbias + c0 + k + 4);
                         float acc[8];
-                        acc[0] = __uint_as_float(r1[k]) + b0.x; acc[1] = __uint_as_float(r1[k + 1]) + b0.y;
-                        acc[2] = __uint_as_float(r1[k + 2]) + b0.z; acc[3] = __uint_as_float(r1[k + 3]) + b0.w;
-                        acc[4] = __uint_as_float(r1[k + 4]) + b1.x; acc[5] = __uint_as_float(r1[k + 5]) + b1.y;
-                        acc[6] = __uint_as_float(r1[k + 6]) + b1.z; acc[7] = __uint_as_float(r1[k + 7]) + b1.w;
+                        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                        if (p.pn_stats) {
+                            const float4 w0 = *reinterpret_cast<const float4*>(swsum + c0 + k);
+                            const float4 w1 = *reinterpret_cast<const float4*>(swsum + c0 + k + 4);
+                            const float ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) acc[e] = fmaf(pn_a, __uint_as_float(r1[k + e]), fmaf(pn_m, ws[e], bb[e]));
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) acc[e] = __uint_as_float(r1[k + e]) + bb[e];
+                        }
                         Half8 h = pack8(acc);
                         if (!keep) h = Half8{};
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
@@ -674,6 +696,9 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     if (p.src_chunks[0] + p.src_chunks[1] != p.nchunks) return 1;
     p.w = packed_w; p.bias = cp.bias; p.dst = cp.dst; p.stats = cp.stats;
     p.write_halo = cp.write_halo;
+    if (cp.pn_stats && k3) return 1;        // the folded PreNorm exists in the 1x1x1 epilogue only
+    p.pn_stats = cp.pn_stats; p.pn_wsum = cp.pn_wsum; p.pn_wb = cp.pn_wb; p.pn_C = cp.pn_C;
+    p.pn_inv_count = cp.pn_stats ? (float)(1.0 / cp.pn_count) : 0.f;
     p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout, taps); p.ncb = cp.Cout / p.CB;
     // statistics are accumulated per GroupNorm group: the group size must match an instantiated (CB, CPG) pair
     int cpg = 0;

@@ -257,6 +257,7 @@ struct Builder {
             p.write_halo = write_halo;
             p.stats = stats_off >= 0 ? (double*)(hh->scratch + (size_t)stats_off * r.B) : nullptr;
             p.stats_cpg = w.Cout / (hh->d.groups > 0 ? hh->d.groups : 1);
+            p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
             p.B = r.B;
             hh->launches += 1;
             if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed) {
@@ -361,9 +362,68 @@ struct Builder {
         size_t s1 = slot((size_t)C * 16);
         size_t skm = slot(32 * 4), sctx = slot(33 * 32 * 4);
         int xn = acquire(h, level, C);
-        gn(pre + "fn.norm.weight", pre + "fn.norm.bias", level, x, xn, C, 1, (long long)s0, 0, -1, -1);
         int qkv = acquire(h, level, 96);
-        conv(cq, level, level, {xn}, qkv, 1, 0, 0, 0, 0, -1);
+        // PreNorm (GroupNorm(1,C), models.py:321-329) folded into the to_qkv 1x1x1 conv on the tcgen05 path:
+        //   W (gamma*(x-mean)*rstd + beta) = rstd * (W diag(gamma)) x - mean*rstd * rowsum(W diag(gamma)) + W beta
+        // so the conv reads x directly (no normalised copy) and its epilogue applies the per-sample scalars.
+        ConvW cqf;
+        float *pn_wsum = nullptr, *pn_wb = nullptr;
+        {
+            const HostTensor* wq = find_w(h, pre + "fn.fn.to_qkv.conv.weight");
+            const HostTensor* gm = find_w(h, pre + "fn.norm.weight");
+            const HostTensor* bt = find_w(h, pre + "fn.norm.bias");
+            if (!wq || !gm || !bt || (int)gm->data.size() != C || (int)bt->data.size() != C) { fail("missing PreNorm weights %s", pre.c_str()); ok = false; return -1; }
+            HostTensor folded = *wq;
+            std::vector<float> wsum(96, 0.f), wb(96, 0.f);
+            for (int o = 0; o < 96; ++o)
+                for (int ci = 0; ci < C; ++ci) {
+                    const float wf = wq->data[(size_t)o * C + ci] * gm->data[ci];
+                    folded.data[(size_t)o * C + ci] = wf;
+                    wsum[o] += __half2float(__float2half_rn(wf));     // of the weights as the tensor cores see them
+                    wb[o] += wq->data[(size_t)o * C + ci] * bt->data[ci];
+                }
+            h->weights["__folded_qkv"] = folded;
+            bool okp = pack_conv(h, "__folded_qkv", "", C, C, 96, 1, 1, 1, 0, true, &cqf);
+            h->weights.erase("__folded_qkv");
+            if (!okp) { ok = false; return -1; }
+            pn_wsum = h->upload(wsum);
+            pn_wb = h->upload(wb);
+        }
+        float* pn_gamma = upload_vec(h, pre + "fn.norm.weight", C);
+        float* pn_beta = upload_vec(h, pre + "fn.norm.bias", C);
+        if (!pn_gamma || !pn_beta) { ok = false; return -1; }
+        {
+            const Geom& g = hh->geom[level];
+            double m = (double)g.Z * g.P * g.R;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "conv_k1_prenorm_c%d_96_L%d_mma", C, level);
+            hh->op_info.push_back({nm, 2.0 * m * C * 96, 2.0 * m * (C + 96)});
+        }
+        hh->ops.push_back([=](Run& r) {
+            const Geom& g = hh->geom[level];
+            ConvParams p;
+            p.gin = g; p.gout = g; p.nsrc = 1; p.Cin_total = C;
+            p.src[0].C = C; p.src[1].base = nullptr; p.src[1].C = 0;
+            p.dst = hh->bufs[qkv].ptr; p.Cout = 96; p.bias = nullptr;
+            p.kz = p.kp = p.kr = 1; p.sz = p.sp = p.sr = 1; p.pz = p.cp = p.pr = 0;
+            p.transposed = 0; p.write_halo = 0; p.stats = nullptr; p.stats_cpg = 1; p.B = r.B;
+            p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
+            const double* st = (const double*)(hh->scratch + s0 * r.B);
+            if (hh->conv_backend == 0 && cqf.wmma) {
+                p.src[0].base = hh->bufs[x].ptr; p.w = cqf.w;
+                p.pn_stats = st; p.pn_wsum = pn_wsum; p.pn_wb = pn_wb; p.pn_C = C; p.pn_count = (double)C * g.Z * g.P * g.R;
+                hh->launches += 1;
+                if (launch_conv_mma(p, cqf.wmma, r.st) == 0) return;
+                p.pn_stats = nullptr;
+            }
+            // unfused form: normalised copy, then the plain conv (SIMT backend / unsupported widths)
+            launch_gn_apply(g, hh->bufs[x].ptr, st, pn_gamma, pn_beta, 1, (double)g.Z * g.P * g.R, nullptr, hh->addvec_stride, nullptr,
+                            nullptr, 0, hh->bufs[xn].ptr, C, 0, nullptr, r.B, r.st);
+            p.src[0].base = hh->bufs[xn].ptr; p.w = cq.w;
+            hh->launches += 2;
+            if (hh->conv_backend == 0 && cq.wmma && launch_conv_mma(p, cq.wmma, r.st) == 0) return;
+            launch_conv_generic(p, r.st);
+        });
         {
             const Geom& g = hh->geom[level];
             double m = (double)g.Z * g.P * g.R;
@@ -967,6 +1027,7 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     bool is1 = taps == 1;
     p.pz = is1 ? 0 : 1; p.cp = is1 ? 0 : 1; p.pr = is1 ? 0 : 1;
     p.transposed = transposed; p.write_halo = 0; p.stats = nullptr; p.stats_cpg = 1; p.B = B;
+    p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
     int rc = 0;
     if (backend == 0) {
         if (!cw.wmma || launch_conv_mma(p, cw.wmma, st) != 0) rc = fail("tcgen05 conv does not support this shape");
