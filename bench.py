@@ -39,6 +39,14 @@ WORKLOADS = {
                  NOISE_SCHED="cosine", TIME_EMBED="sigma", SAMPLER="Heun", BATCH=64),
         name="CaloChallenge Dataset-3 (45x50x18), cylindrical U-Net, EDM Heun 50 steps", sampler="Heun", steps=50,
         evals_per_shower=100, batch=256, n_layers=0, gflop_per_eval=30.351),
+    # BASELINE config 4: the HGCal pytest-fixture shape (tests/test_execution.py:178-190), pre-embedded showers
+    "hgcal": dict(
+        cfg=dict(_COMMON, DATASET_NUM=111, HGCAL=True, SHAPE_ORIG=[-1, 28, 1988], SHAPE_PAD=[-1, 1, 28, 12, 21],
+                 SHAPE_FINAL=[-1, 1, 28, 12, 21], LAYER_SIZE_UNET=[32, 32, 64, 96], SHOWERMAP="layer-logit-norm",
+                 SHOWER_EMBED="NN-pre-embed", PHI_INPUT=True, NOISE_SCHED="log", TIME_EMBED="log", SAMPLER="DDim", BATCH=128,
+                 MAX_CELLS=1988),
+        name="HGCal test-fixture shape (28x12x21, pre-embedded), cylindrical U-Net, DDIM 200 steps", sampler="DDim", steps=200,
+        evals_per_shower=200, batch=128, n_layers=29, gflop_per_eval=6.4713, cond_e=3),
 }
 
 
@@ -95,12 +103,13 @@ def cpu_reference_leg(wl, budget_s=12.0, batch=16):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     zpr = cfg["SHAPE_FINAL"][2:]
-    cond_size = 1 + wl["n_layers"]
-    shapes = {"model." + k: v for k, v in unet_param_shapes(cfg["LAYER_SIZE_UNET"], 3, cond_size, cfg["COND_SIZE_UNET"], zpr).items()}
+    cond_size = wl.get("cond_e", 1) + wl["n_layers"]
+    in_ch = 1 + (2 if cfg.get("R_Z_INPUT") else 0) + (1 if cfg.get("PHI_INPUT") else 0)
+    shapes = {"model." + k: v for k, v in unet_param_shapes(cfg["LAYER_SIZE_UNET"], in_ch, cond_size, cfg["COND_SIZE_UNET"], zpr).items()}
     sd = synth_state_dict(shapes, seed=0)
     o = DenoiserOracle(cfg, sd)
     g = torch.Generator().manual_seed(1)
-    E = torch.rand(batch, 1, generator=g)
+    E = torch.rand(batch, wl.get("cond_e", 1), generator=g)
     layers = torch.randn(batch, wl["n_layers"], generator=g) if wl["n_layers"] else None
     start = torch.randn([batch] + cfg["SHAPE_PAD"][1:], generator=torch.Generator().manual_seed(2))
     evals_done, t_total, n = 0, 0.0, 1
@@ -243,7 +252,7 @@ def run_gpu_arm(args, wl):
         sampler.last_step_euler = True                     # finite showers; 2 evals on all other steps
     vox = int(np.prod(cfg["SHAPE_PAD"][1:]))
     g = torch.Generator().manual_seed(1 + rank)
-    E_host = torch.rand(B, 1, generator=g).pin_memory()
+    E_host = torch.rand(B, wl.get("cond_e", 1), generator=g).pin_memory()
     L_host = torch.randn(B, wl["n_layers"], generator=g).pin_memory() if wl["n_layers"] else None
     E_dev = E_host.to(dev)
     L_dev = L_host.to(dev) if L_host is not None else None
@@ -301,7 +310,7 @@ def run_gpu_arm(args, wl):
     total_showers = world * B * args.steps
     value = total_showers / (ms * 1e-3)
     e2e = total_showers / (e2e_ms * 1e-3)
-    h2d = 4 * B * (1 + wl["n_layers"])
+    h2d = 4 * B * (wl.get("cond_e", 1) + wl["n_layers"])
     d2h = 4 * B * vox
 
     if rank == 0:

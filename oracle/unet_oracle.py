@@ -168,13 +168,15 @@ def cond_unet_forward(sd, x, cond, time, groups=8, pre="model."):
 class DenoiserOracle:
     """State-dict + config → `denoise(x, E, sigma, layers)`; mirrors CaloDiffusion.denoise."""
 
-    def __init__(self, config, state_dict, dtype=torch.float32):
+    def __init__(self, config, state_dict, dtype=torch.float32, device="cpu"):
         self.config = config
         self.dtype = dtype
-        self.sd = {k: v.detach().to("cpu", dtype) for k, v in state_dict.items()}
+        self.device = torch.device(device)   # "cuda": the same torch ops on cuDNN/cuBLAS (scripts/torch_gpu_baseline.py only)
+        self.sd = {k: v.detach().to(self.device, dtype) for k, v in state_dict.items()}
         shape = config["SHAPE_FINAL"][1:]
         self.Z, self.P, self.R = shape[1], shape[2], shape[3]
-        self.r_img, self.z_img, self.phi_img = geometry_channels(config.get("DATASET_NUM", 2), self.Z, self.P, self.R, dtype)
+        self.r_img, self.z_img, self.phi_img = (t.to(self.device) for t in
+                                                geometry_channels(config.get("DATASET_NUM", 2), self.Z, self.P, self.R, dtype))
         self.layer_cond = "layer" in config.get("SHOWERMAP", "")
         self.time_embed = config.get("TIME_EMBED", "sin")
         # loss.py:16-25: sigma_data 1.0 for 'log' noise schedules, else 0.5
