@@ -12,6 +12,7 @@ EXPORTS = [
     "cd_last_error", "cd_version", "cd_device_check", "cd_unet_create", "cd_unet_destroy", "cd_unet_set_weight",
     "cd_unet_finalize", "cd_unet_set_option", "cd_unet_workspace_bytes", "cd_unet_launch_count", "cd_unet_forward",
     "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_reverse_norm", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
+    "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply",
 ]
 
 
@@ -86,6 +87,10 @@ def load():
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
     lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]
+    lib.cd_unet_set_geom_map.argtypes = [vp, i32, i32, i32, vp, vp, vp]
+    lib.cd_unet_voxels.argtypes = [vp]
+    lib.cd_unet_voxels.restype = i32
+    lib.cd_geom_apply.argtypes = [vp, vp, vp, i32, i32, vp, vp, i32, vp]
     _lib = lib
     return lib
 

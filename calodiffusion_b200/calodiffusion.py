@@ -13,7 +13,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-from . import _lib, utils
+from . import _lib, geometry, utils
 from .diffusion import Diffusion
 
 
@@ -140,9 +140,6 @@ class CaloDiffusion(Diffusion):
         self.hgcal = cfg.get("HGCAL", False)
         if "FCN" in cfg.get("SHOWER_EMBED", ""):
             raise ValueError("SHOWER_EMBED 'FCN' (dense ResNet) is outside the B200 hot path")
-        if ("NN" in cfg.get("SHOWER_EMBED", "") and not self.hgcal) or (self.hgcal and not self.pre_embed):
-            raise ValueError("in-loop geometry embedding (NNConverter/HGCalConverter) is not on the B200 path; "
-                             "use a '*-pre-embed' SHOWER_EMBED")
         self.time_embed = cfg.get("TIME_EMBED", "sin")
         if self.time_embed not in ("sigma", "log"):
             raise KeyError(self.time_embed)  # models/calodiffusion.py:148-152
@@ -166,6 +163,13 @@ class CaloDiffusion(Diffusion):
         self._lib = _lib.load()
         _lib.check(self._lib.cd_device_check(), "device check")
         self.model = self.init_model()
+        self.NN_embed = self.init_embedding_model()
+        self.do_embed = self.NN_embed is not None and (not self.pre_embed)
+        if self.do_embed:   # the caller-facing tensors are the flat voxels; the maps run inside every evaluation on the device
+            if int(np.prod(self.NN_embed.flat_shape())) != int(np.prod(self._data_shape)):
+                raise ValueError(f"geometry embedding maps {tuple(self.NN_embed.flat_shape())} voxels but the config's data "
+                                 f"shape is {tuple(self._data_shape)}")
+            self._voxels = int(np.prod(self._data_shape))
         self.use_graph = True
         self.conv_backend = 0
 
@@ -179,6 +183,25 @@ class CaloDiffusion(Diffusion):
         self._in_channels, self._cond_size = in_channels, cond_size
         shapes = unet_param_shapes(cfg["LAYER_SIZE_UNET"], in_channels, cond_size, cfg["COND_SIZE_UNET"], self._zpr)
         return CondUnetB200(shapes).to(self.device)
+
+    def init_embedding_model(self, embed=None):
+        """models/calodiffusion.py:100-119.  Dataset 1: NNConverter from the binning XML (`BIN_FILE`).  HGCal without
+        pre-embedding: the reference builds HGCalConverter from a geometry pickle on the host; here the per-layer matrices
+        come in through config['GEOM_EMBED'] = dict(enc_mat, dec_mat[, enc_mask, dec_mask]) (geometry.MatrixConverter)."""
+        cfg = self.config
+        shower_embed = cfg.get("SHOWER_EMBED", "")
+        if "NN" in shower_embed and not self.hgcal:
+            particle = "photon" if self.dataset_num == 1 else "pion"
+            bins = geometry.BinningXML(particle, cfg["BIN_FILE"])
+            return geometry.NNConverter(bins=bins).to(device=self.device)
+        if self.hgcal and not self.pre_embed:
+            mats = cfg.get("GEOM_EMBED")
+            if mats is None:
+                raise ValueError("HGCal in-loop embedding needs config['GEOM_EMBED'] (enc_mat, dec_mat of the reference's "
+                                 "HGCalConverter); building them from the geometry pickle is host code outside the B200 path")
+            return geometry.MatrixConverter(cfg["SHAPE_FINAL"], mats["enc_mat"], mats["dec_mat"], mats.get("enc_mask"),
+                                            mats.get("dec_mask"), trainable=cfg.get("TRAINABLE_EMBED", False)).to(self.device)
+        return None
 
     def noise_generation(self, shape):
         return super().noise_generation(shape)
@@ -226,6 +249,8 @@ class CaloDiffusion(Diffusion):
 
     def _engine(self, batch):
         versions = tuple(p._version for p in self.model.parameters())
+        if self.do_embed:
+            versions += self.NN_embed._weights_version()
         if self._handle is not None and versions == self._handle_versions and batch <= self._max_batch:
             return self._handle
         if batch > self._max_batch:
@@ -241,8 +266,14 @@ class CaloDiffusion(Diffusion):
                 t = p.detach().to("cpu", torch.float32).contiguous()
                 shp = (C.c_int64 * t.dim())(*t.shape)
                 _lib.check(lib.cd_unet_set_weight(h, ("model." + name).encode(), t.data_ptr(), shp, t.dim()), "set_weight")
+            if self.do_embed:
+                for which, m in enumerate(self.NN_embed.csr_maps()):
+                    _lib.check(lib.cd_unet_set_geom_map(h, which, m["n_rows"], m["n_cols"], m["rowptr"].ctypes.data,
+                                                        m["col"].ctypes.data, m["val"].ctypes.data), "set_geom_map")
             _lib.check(lib.cd_unet_set_option(h, b"conv_backend", int(self.conv_backend)), "set_option")
             _lib.check(lib.cd_unet_finalize(h), "finalize")
+            if int(lib.cd_unet_voxels(h)) != self._voxels:
+                raise RuntimeError(f"engine works on {int(lib.cd_unet_voxels(h))} voxels per shower, host expects {self._voxels}")
         except Exception:
             lib.cd_unet_destroy(h)
             raise

@@ -97,6 +97,12 @@ struct cd_unet {
     int final_C = 0;
     const __half* final_h = nullptr;
     EmbedParams embed;
+    // in-loop geometry embedding (cd_unet_set_geom_map): host CSR until finalize, device CSR afterwards
+    struct HostCsr { std::vector<int> rowptr, col; std::vector<float> val; int n_rows = 0, n_cols = 0; } geom_host[2];
+    GeomMap geom_map[2] = {};
+    bool has_geom = false;
+    float* grid_pred = nullptr;   // (max_batch, Z*P*R) raw network output before decoding
+    int voxels() const { return has_geom ? geom_map[1].n_rows : d.Z * d.P * d.R; }
     // sampling state
     float* state[CD_NUM_STATE_BUFS] = {nullptr, nullptr, nullptr, nullptr};
     float* coef_tab = nullptr;  // [max_evals][8]
@@ -487,8 +493,12 @@ static int build_plan(cd_unet* h) {
         h->op_info.push_back({"prep_input", 0.0, m * 4 + m * 16});
     }
     h->ops.push_back([h, tin_buf](Run& r) {
-        launch_prep_input(h->geom[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f, h->r_vals,
-                          h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, 2, r.B, r.st);
+        if (h->has_geom)
+            launch_prep_input_geom(h->geom[0], h->geom_map[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f,
+                                   h->r_vals, h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, 2, r.B, r.st);
+        else
+            launch_prep_input(h->geom[0], r.x, r.sigma, r.sigma_stride, r.scale_input ? h->d.sigma_data : -1.f, h->r_vals,
+                              h->d.rz_input, h->d.phi_input, h->bufs[tin_buf].ptr, 2, r.B, r.st);
         h->launches += 1;
     });
     ConvW cinit;
@@ -586,6 +596,18 @@ static int build_plan(cd_unet* h) {
         f.h = h->final_h; f.C = h->final_C; f.w = h->final_w; f.bias = h->final_b;
         f.x = r.x; f.sigma = r.sigma; f.sigma_stride = r.sigma_stride;
         f.sigma_data = r.scale_input ? h->d.sigma_data : -1.f;
+        if (h->has_geom) {
+            // grid-space raw output first, then decode + pre-conditioning + sampler update on the flat voxels
+            FinalParams fg;
+            memset(&fg, 0, sizeof(fg));
+            fg.g = f.g; fg.h = f.h; fg.C = f.C; fg.w = f.w; fg.bias = f.bias;
+            fg.sigma = r.sigma; fg.sigma_stride = r.sigma_stride; fg.sigma_data = -1.f;
+            fg.pred_out = h->grid_pred;
+            launch_final(fg, r.B, r.st);
+            launch_geom_decode(f, h->geom_map[1], h->grid_pred, r.B, r.st);
+            h->launches += 2;
+            return;
+        }
         launch_final(f, r.B, r.st);
         h->launches += 1;
     });
@@ -734,6 +756,32 @@ int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, con
     return 0;
 }
 
+int cd_unet_set_geom_map(cd_unet* h, int which, int n_rows, int n_cols, const int32_t* rowptr, const int32_t* col,
+                         const float* val) {
+    if (!h || !rowptr) return fail("null argument");
+    if (h->finalized) return fail("geometry maps are frozen after cd_unet_finalize; create a new handle");
+    if (which < 0 || which > 1 || n_rows < 1 || n_cols < 1) return fail("bad geometry map request (which=%d, %dx%d)", which, n_rows, n_cols);
+    if (rowptr[0] != 0) return fail("geometry map: rowptr[0] must be 0");
+    for (int i = 0; i < n_rows; ++i)
+        if (rowptr[i + 1] < rowptr[i]) return fail("geometry map: rowptr is not non-decreasing at row %d", i);
+    const int nnz = rowptr[n_rows];
+    if (nnz > 0 && (!col || !val)) return fail("null argument");
+    for (int k = 0; k < nnz; ++k)
+        if (col[k] < 0 || col[k] >= n_cols) return fail("geometry map: column %d outside [0,%d) at entry %d", col[k], n_cols, k);
+    auto& m = h->geom_host[which];
+    m.n_rows = n_rows; m.n_cols = n_cols;
+    m.rowptr.assign(rowptr, rowptr + n_rows + 1);
+    m.col.assign(col, col + nnz);
+    m.val.assign(val, val + nnz);
+    return 0;
+}
+
+int cd_unet_voxels(const cd_unet* h) {
+    if (!h) return 0;
+    if (!h->finalized && h->geom_host[1].n_rows > 0) return h->geom_host[1].n_rows;
+    return h->voxels();
+}
+
 int cd_unet_set_option(cd_unet* h, const char* key, int value) {
     if (!h || !key) return fail("null argument");
     if (!strcmp(key, "conv_backend")) {
@@ -755,8 +803,33 @@ int cd_unet_finalize(cd_unet* h) {
     if (h->finalized) return 0;
     std::vector<float> rv(h->d.r_centres, h->d.r_centres + h->d.R);
     h->r_vals = h->upload(rv);
+    const int ngrid = h->d.Z * h->d.P * h->d.R;
+    if ((h->geom_host[0].n_rows > 0) != (h->geom_host[1].n_rows > 0)) return fail("geometry maps: both enc (0) and dec (1) must be set");
+    if (h->geom_host[0].n_rows > 0) {
+        const auto& en = h->geom_host[0];
+        const auto& de = h->geom_host[1];
+        if (en.n_rows != ngrid || de.n_cols != ngrid || en.n_cols != de.n_rows)
+            return fail("geometry maps: enc is %dx%d, dec is %dx%d; expected %dxN and Nx%d", en.n_rows, en.n_cols, de.n_rows, de.n_cols,
+                        ngrid, ngrid);
+        for (int w = 0; w < 2; ++w) {
+            const auto& m = h->geom_host[w];
+            int* rp = h->dalloc<int>(m.rowptr.size(), false);
+            int* cl = h->dalloc<int>(m.col.size() ? m.col.size() : 1, false);
+            float* vl = h->dalloc<float>(m.val.size() ? m.val.size() : 1, false);
+            if (!rp || !cl || !vl) return fail("out of device memory for geometry maps");
+            cudaMemcpy(rp, m.rowptr.data(), m.rowptr.size() * sizeof(int), cudaMemcpyHostToDevice);
+            if (!m.col.empty()) {
+                cudaMemcpy(cl, m.col.data(), m.col.size() * sizeof(int), cudaMemcpyHostToDevice);
+                cudaMemcpy(vl, m.val.data(), m.val.size() * sizeof(float), cudaMemcpyHostToDevice);
+            }
+            h->geom_map[w] = GeomMap{rp, cl, vl, m.n_rows, m.n_cols};
+        }
+        h->grid_pred = h->dalloc<float>((size_t)h->d.max_batch * ngrid, true);
+        if (!h->grid_pred) return fail("out of device memory for the grid output");
+        h->has_geom = true;
+    }
     if (build_plan(h)) return 1;
-    size_t nv = (size_t)h->d.max_batch * h->d.Z * h->d.P * h->d.R;
+    size_t nv = (size_t)h->d.max_batch * h->voxels();
     for (int i = 0; i < CD_NUM_STATE_BUFS; ++i) {
         h->state[i] = h->dalloc<float>(nv, true);
         if (!h->state[i]) return fail("out of device memory for sampler state");
@@ -829,6 +902,18 @@ int cd_fill_normal(float* out_dev, int64_t n_showers, int64_t voxels, uint64_t s
     return 0;
 }
 
+int cd_geom_apply(const int32_t* rowptr_dev, const int32_t* col_dev, const float* val_dev, int n_rows, int n_cols,
+                  const float* x_dev, float* y_dev, int B, void* stream) {
+    if (!rowptr_dev || !col_dev || !val_dev || !x_dev || !y_dev) return fail("null argument");
+    if (cd_device_check()) return 1;
+    if (n_rows < 1 || n_cols < 1 || B < 1) return fail("bad geom_apply shape");
+    GeomMap m{rowptr_dev, col_dev, val_dev, n_rows, n_cols};
+    launch_geom_apply(m, x_dev, y_dev, B, (cudaStream_t)stream);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("geom_apply: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 int cd_reverse_norm(const cd_reverse_norm_desc* d, const float* vox_dev, const float* e_dev, const float* layerE_dev,
                     float* out_dev, float* energy_out_dev, int B, void* stream) {
     if (!d || !vox_dev || !e_dev || !out_dev) return fail("null argument");
@@ -860,7 +945,7 @@ struct SampleArgs {
 };
 
 static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
-    const int V = h->d.Z * h->d.P * h->d.R;
+    const int V = h->voxels();
     const long long n = (long long)a.B * V;
     const size_t bytes = (size_t)n * sizeof(float);
     float* tab = h->coef_tab;

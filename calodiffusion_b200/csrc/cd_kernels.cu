@@ -40,6 +40,45 @@ void launch_prep_input(const Geom& g, const float* x, const float* sigma, int si
     prep_input_kernel<<<grid, 256, 0, st>>>(g, x, sigma, sigma_stride, sigma_data, r_vals, rz_input, phi_input, dst, out_chunks);
 }
 
+// prep_input with the in-loop geometry embedding: the grid value is  sum_k val[k] * x_flat[col[k]]  over the CSR row of
+// the grid cell (NNConverter.enc utils/utils.py:610-634; HGCal Embeder.forward HGCal_utils.py:315-320).
+__global__ void __launch_bounds__(256) prep_input_geom_kernel(Geom g, GeomMap enc, const float* __restrict__ x,
+                                                              const float* __restrict__ sigma, int sigma_stride, float sigma_data,
+                                                              const float* __restrict__ r_vals, int rz_input, int phi_input,
+                                                              __half* __restrict__ dst, int out_chunks) {
+    const int b = blockIdx.y;
+    const uint32_t rem = blockIdx.x * 256 + threadIdx.x;
+    if (rem >= (uint32_t)g.rows_per_sample) return;
+    const SubRow sr = decode_subrow(g, rem);
+    const long long row = (long long)b * g.rows_per_sample + rem;
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (sr.kind != 2) {
+        int p = sr.pp - 1;
+        if (p < 0) p += g.P;
+        if (p >= g.P) p -= g.P;
+        const float s = sigma[(long long)b * sigma_stride];
+        const float c_in = sigma_data > 0.f ? rsqrtf(s * s + sigma_data * sigma_data) : 1.f;
+        const int cell = (sr.z * g.P + p) * g.R + sr.rr;
+        const float* xb = x + (long long)b * enc.n_cols;
+        float acc = 0.f;
+        for (int k = enc.rowptr[cell], ke = enc.rowptr[cell + 1]; k < ke; ++k) acc = fmaf(enc.val[k], xb[enc.col[k]], acc);
+        f[0] = acc * c_in;
+        int c = 1;
+        if (rz_input) { f[c++] = r_vals[sr.rr]; f[c++] = (float)sr.z / (float)g.Z; }
+        if (phi_input) { f[c++] = (g.P > 1) ? (float)p / (float)(g.P - 1) : 0.f; }
+    }
+    *reinterpret_cast<Half8*>(dst + plcp_offset(g, 0, row)) = pack8(f);
+    for (int k = 1; k < out_chunks; ++k) *reinterpret_cast<uint4*>(dst + plcp_offset(g, k, row)) = make_uint4(0u, 0u, 0u, 0u);
+}
+
+void launch_prep_input_geom(const Geom& g, const GeomMap& enc, const float* x, const float* sigma, int sigma_stride,
+                            float sigma_data, const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks,
+                            int B, cudaStream_t st) {
+    dim3 grid((g.rows_per_sample + 255) / 256, B);
+    prep_input_geom_kernel<<<grid, 256, 0, st>>>(g, enc, x, sigma, sigma_stride, sigma_data, r_vals, rz_input, phi_input, dst,
+                                                 out_chunks);
+}
+
 // =================================================================================================
 // Generic direct convolution (SIMT, fp32 accumulate).  Handles every CylindricalConv /
 // CylindricalConvTrans variant of models/models.py:25-96 by explicit coordinate arithmetic (circular
@@ -412,6 +451,27 @@ __device__ __forceinline__ float philox_normal(uint64_t seed, uint32_t shower, u
     return sqrtf(-2.0f * __logf(u1)) * __cosf(6.283185307179586f * u2);
 }
 
+// shared tail of the final kernels: EDM pre-conditioning output + sampler update for caller-facing voxel v = b*vps + rem
+__device__ __forceinline__ void final_tail(const FinalParams& p, long long v, int b, int rem, float pred) {
+    float s = p.sigma[(long long)b * p.sigma_stride];
+    float sd = p.sigma_data;
+    float den = s * s + sd * sd;
+    float xin = p.x ? p.x[v] : 0.f;
+    float x0 = sd > 0.f ? (sd * sd / den) * xin + (s * sd * rsqrtf(den)) * pred : pred;
+    if (p.pred_out) p.pred_out[v] = pred;
+    if (p.x0_out) p.x0_out[v] = x0;
+    if (p.x_out) {
+        const float* k = p.coef;
+        float o = k[0] * x0 + k[1] * xin;
+        if (p.a1) o += k[2] * p.a1[v];
+        else if (p.rng_enabled && k[2] != 0.f)
+            o += k[2] * philox_normal(p.seed, (uint32_t)(p.shower_offset + b), (uint32_t)p.step, (uint32_t)rem);
+        if (p.a2) o += k[3] * p.a2[v];
+        if (p.a3) o += k[4] * p.a3[v];
+        p.x_out[v] = o;
+    }
+}
+
 // =================================================================================================
 // Final 1x1x1 conv (C->1, models.py:696) fused with the EDM pre-conditioning output
 //   x0 = c_skip*x + c_out*pred          (calodiffusion.py:166-167, loss.py:33-37)
@@ -440,28 +500,49 @@ __global__ void final_kernel(FinalParams p, long long nvox) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) pred += f[j] * p.w[k * 8 + j];
     }
-    float s = p.sigma[(long long)b * p.sigma_stride];
-    float sd = p.sigma_data;
-    float den = s * s + sd * sd;
-    float xin = p.x[v];
-    float x0 = sd > 0.f ? (sd * sd / den) * xin + (s * sd * rsqrtf(den)) * pred : pred;
-    if (p.pred_out) p.pred_out[v] = pred;
-    if (p.x0_out) p.x0_out[v] = x0;
-    if (p.x_out) {
-        const float* k = p.coef;
-        float o = k[0] * x0 + k[1] * xin;
-        if (p.a1) o += k[2] * p.a1[v];
-        else if (p.rng_enabled && k[2] != 0.f)
-            o += k[2] * philox_normal(p.seed, (uint32_t)(p.shower_offset + b), (uint32_t)p.step, (uint32_t)rem);
-        if (p.a2) o += k[3] * p.a2[v];
-        if (p.a3) o += k[4] * p.a3[v];
-        p.x_out[v] = o;
-    }
+    final_tail(p, v, b, rem, pred);
 }
 
 void launch_final(const FinalParams& p, int B, cudaStream_t st) {
     long long nvox = (long long)B * p.g.Z * p.g.P * p.g.R;
     final_kernel<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(p, nvox);
+}
+
+// Geometry decoding fused with the pre-conditioning output and the sampler update: thread = flat voxel j of shower b,
+//   pred[b,j] = sum_k val[k] * grid_pred[b, col[k]]      (NNConverter.dec utils/utils.py:636-653; HGCal Decoder.forward
+//   HGCal_utils.py:340-349 without sparse decoding), then the same tail as final_kernel on the (B, n_flat) tensors.
+__global__ void __launch_bounds__(256) geom_decode_kernel(FinalParams p, GeomMap dec, const float* __restrict__ grid_pred,
+                                                          long long nvox) {
+    long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nvox) return;
+    const int b = (int)(v / dec.n_rows);
+    const int j = (int)(v - (long long)b * dec.n_rows);
+    const float* gb = grid_pred + (long long)b * dec.n_cols;
+    float pred = 0.f;
+    for (int k = dec.rowptr[j], ke = dec.rowptr[j + 1]; k < ke; ++k) pred = fmaf(dec.val[k], gb[dec.col[k]], pred);
+    final_tail(p, v, b, j, pred);
+}
+
+// stand-alone application of one geometry map: y[b, i] = sum_k val[k] * x[b, col[k]]  (the converters' enc / dec outside the loop)
+__global__ void __launch_bounds__(256) geom_apply_kernel(GeomMap m, const float* __restrict__ x, float* __restrict__ y, long long n) {
+    long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const int b = (int)(v / m.n_rows);
+    const int i = (int)(v - (long long)b * m.n_rows);
+    const float* xb = x + (long long)b * m.n_cols;
+    float acc = 0.f;
+    for (int k = m.rowptr[i], ke = m.rowptr[i + 1]; k < ke; ++k) acc = fmaf(m.val[k], xb[m.col[k]], acc);
+    y[v] = acc;
+}
+
+void launch_geom_apply(const GeomMap& m, const float* x, float* y, int B, cudaStream_t st) {
+    long long n = (long long)B * m.n_rows;
+    geom_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m, x, y, n);
+}
+
+void launch_geom_decode(const FinalParams& p, const GeomMap& dec, const float* grid_pred, int B, cudaStream_t st) {
+    long long nvox = (long long)B * dec.n_rows;
+    geom_decode_kernel<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(p, dec, grid_pred, nvox);
 }
 
 // x_out = a*x + b*noise (start scaling  x = start*sigma_0, and the EDM churn pre-noise, sample.py:633,651)

@@ -27,6 +27,9 @@ struct FinalParams {
     int rng_enabled; unsigned long long seed; int shower_offset; int step;
 };
 
+// CSR linear map between the caller's flat voxel vector and the regular grid (device pointers)
+struct GeomMap { const int* rowptr; const int* col; const float* val; int n_rows, n_cols; };
+
 struct RevNormParams {
     const float* vox; const float* e; const float* layerE;   // (B,Z,PR), (B), (B,Z+1) or nullptr
     float* out; float* energy_out;                          // (B,Z*PR), (B) or nullptr
@@ -38,6 +41,11 @@ void launch_reverse_norm(const RevNormParams& p, int B, cudaStream_t st);
 
 void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,
                        const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks, int B, cudaStream_t st);
+void launch_prep_input_geom(const Geom& g, const GeomMap& enc, const float* x, const float* sigma, int sigma_stride,
+                            float sigma_data, const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks,
+                            int B, cudaStream_t st);
+void launch_geom_apply(const GeomMap& m, const float* x, float* y, int B, cudaStream_t st);
+void launch_geom_decode(const FinalParams& p, const GeomMap& dec, const float* grid_pred, int B, cudaStream_t st);
 void launch_conv_generic(const ConvParams& p, cudaStream_t st);
 void launch_gn_apply(const Geom& g, const __half* src, const double* stats, const float* gamma, const float* beta, int groups,
                      double count_per_channel, const float* addvec, int addvec_stride, const __half* residual,

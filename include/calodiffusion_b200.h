@@ -82,6 +82,21 @@ cd_unet* cd_unet_create(const cd_unet_desc* desc);
 void cd_unet_destroy(cd_unet* h);
 /* fp32 host tensor under its reference state-dict name (e.g. "model.downs.0.0.block1.proj.conv.weight") */
 int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, const int64_t* shape, int ndim);
+/* In-loop geometry embedding: the two linear maps between the caller's flat voxel vector (B, n_flat) and the regular
+ * (Z,P,R) grid the U-Net works on, applied inside EVERY denoiser evaluation.  Replaces NNConverter.enc/dec
+ * (utils/utils.py:610-653; Dataset 1, called from CaloDiffusion.forward models/calodiffusion.py:86-98) and
+ * HGCalConverter.enc/dec = Embeder/Decoder.forward (utils/HGCal_utils.py:315-320, 340-349, 636-663; non-sparse decoding).
+ * Each map is a host CSR matrix: which = 0 "enc" (n_rows = Z*P*R grid cells, n_cols = n_flat),
+ * which = 1 "dec" (n_rows = n_flat, n_cols = Z*P*R).  Both must be set, before cd_unet_finalize; afterwards every x / pred /
+ * x0 / state / noise tensor of cd_unet_forward, cd_denoise and cd_sample_run is (B, n_flat) instead of (B, Z*P*R). */
+int cd_unet_set_geom_map(cd_unet* h, int which, int n_rows, int n_cols, const int32_t* rowptr, const int32_t* col,
+                         const float* val);
+/* One geometry map applied on its own, y (B, n_rows) = M x (B, n_cols), M a CSR matrix in DEVICE memory: the converters'
+ * enc / dec outside the sampling loop (utils/utils.py:610-653, HGCal_utils.py:636-663 enc/dec, enc_batches/dec_batches). */
+int cd_geom_apply(const int32_t* rowptr_dev, const int32_t* col_dev, const float* val_dev, int n_rows, int n_cols,
+                  const float* x_dev, float* y_dev, int B, void* stream);
+/* voxels per shower in the caller-facing tensors: n_flat when geometry maps are set, else Z*P*R */
+int cd_unet_voxels(const cd_unet* h);
 /* validates that every tensor of the topology was supplied, packs weights, allocates workspaces */
 int cd_unet_finalize(cd_unet* h);
 /* options: "conv_backend" 0 = tcgen05 implicit GEMM where supported (default), 1 = generic SIMT everywhere;

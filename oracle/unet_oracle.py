@@ -168,8 +168,9 @@ def cond_unet_forward(sd, x, cond, time, groups=8, pre="model."):
 class DenoiserOracle:
     """State-dict + config → `denoise(x, E, sigma, layers)`; mirrors CaloDiffusion.denoise."""
 
-    def __init__(self, config, state_dict, dtype=torch.float32, device="cpu"):
+    def __init__(self, config, state_dict, dtype=torch.float32, device="cpu", geom=None):
         self.config = config
+        self.geom = geom   # oracle.geom_embed.GeomEmbedOracle: in-loop enc/dec (calodiffusion.py:87-88, 95-96), else None
         self.dtype = dtype
         self.device = torch.device(device)   # "cuda": the same torch ops on cuDNN/cuBLAS (scripts/torch_gpu_baseline.py only)
         self.sd = {k: v.detach().to(self.device, dtype) for k, v in state_dict.items()}
@@ -199,6 +200,8 @@ class DenoiserOracle:
         cond = E
         if self.layer_cond and layers is not None:
             cond = torch.cat([E, layers], dim=1)
+        if self.geom is not None:
+            x = self.geom.enc(x.to(torch.float32)).to(self.dtype)
         B = x.shape[0]
         cats = [x]
         if self.config.get("R_Z_INPUT", False):
@@ -206,12 +209,13 @@ class DenoiserOracle:
         if self.config.get("PHI_INPUT", False):
             cats += [self.phi_img.expand(B, -1, -1, -1, -1)]
         inp = torch.cat(cats, dim=1)
-        return cond_unet_forward(self.sd, inp, cond.to(self.dtype), t_emb, self.groups)
+        out = cond_unet_forward(self.sd, inp, cond.to(self.dtype), t_emb, self.groups)
+        return out if self.geom is None else self.geom.dec(out)
 
     def denoise(self, x, E, sigma, layers=None):
         """calodiffusion.py:154-169 with loss.py:29-41 scalings ('hybrid' branch)."""
         x = x.to(self.dtype)
-        sigma = sigma.to(self.dtype).reshape(-1, 1, 1, 1, 1)
+        sigma = sigma.to(self.dtype).reshape([-1] + [1] * (x.dim() - 1))
         sd2 = self.sigma_data ** 2
         c_skip = sd2 / (sigma ** 2 + sd2)
         c_out = sigma * self.sigma_data / (sigma ** 2 + sd2) ** 0.5

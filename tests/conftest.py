@@ -30,7 +30,7 @@ def load_case(case):
     gold = dict(np.load(os.path.join(GOLDEN, f"{case}.npz")))
     cfg = meta["config"]
     sd = synth_state_dict(meta["shapes"], seed=meta["weight_seed"])
-    shape = cfg["SHAPE_PAD"][1:]
+    shape = cfg["SHAPE_ORIG"][1:] if "orig" in cfg.get("SHOWER_EMBED", "") else cfg["SHAPE_PAD"][1:]  # diffusion.py:40-43
     B = meta["B"]
     g = torch.Generator().manual_seed(meta["input_seed"])
     E = torch.rand(B, meta["cond_e"], generator=g)
@@ -47,3 +47,22 @@ def noise_bank(shape, B, n, seed=3):
 @pytest.fixture(scope="session", params=["ds2", "ds3", "hgcal"])
 def case(request):
     return request.param, load_case(request.param)
+
+
+def write_binning_xml(path, meta, particle="photon"):
+    """Re-emit the CaloChallenge binning file (as the reference's XMLHandler parsed it when the golden was made)."""
+    rows = "".join('      <Layer id="%d" r_edges="%s" n_bin_alpha="%d" />\n' % (i, ",".join(repr(float(v)) for v in e), a)
+                   for i, (e, a) in enumerate(zip(meta["xml_r_edges"], meta["xml_a_bins"])))
+    with open(path, "w") as f:
+        f.write('<Bins>\n   <Bin pid="22" etaMin="0" etaMax="130" name="%s">\n%s   </Bin>\n</Bins>\n' % (particle, rows))
+    return str(path)
+
+
+def ds1_geom_oracle(c):
+    """The oracle's NNConverter enc/dec with the reference's stored converter weights."""
+    from oracle.geom_embed import GeomEmbedOracle
+    g = c["gold"]
+    n = len(g["lay_alphas"])
+    enc_w = [torch.from_numpy(g[f"enc_w_{i}"]) for i in range(n)]
+    dec_w = [torch.from_numpy(g[f"dec_w_{i}"]) for i in range(n)]
+    return GeomEmbedOracle.nn_converter(enc_w, dec_w, g["layer_boundaries"], g["lay_alphas"], int(g["lay_alphas"].max()))
