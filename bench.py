@@ -47,6 +47,13 @@ WORKLOADS = {
                  MAX_CELLS=1988),
         name="HGCal test-fixture shape (28x12x21, pre-embedded), cylindrical U-Net, DDIM 200 steps", sampler="DDim", steps=200,
         evals_per_shower=200, batch=128, n_layers=29, gflop_per_eval=6.4713, cond_e=3),
+    # BASELINE config 1: Dataset-1 photons, 368 irregular voxels embedded to a (5,10,30) grid inside every evaluation
+    "ds1": dict(
+        cfg=dict(_COMMON, DATASET_NUM=1, PART_TYPE="photon", SHAPE_ORIG=[-1, 368], SHAPE_PAD=[-1, 1, 368],
+                 SHAPE_FINAL=[-1, 1, 5, 10, 30], LAYER_SIZE_UNET=[32, 32, 64, 96], SHOWERMAP="layer-logit-norm",
+                 SHOWER_EMBED="orig-NN", PHI_INPUT=True, NOISE_SCHED="log", TIME_EMBED="log", SAMPLER="DDim", BATCH=128),
+        name="CaloChallenge Dataset-1 photons (368 voxels, in-loop GeoEmbed to 5x10x30), cylindrical U-Net, DDIM 50 steps",
+        sampler="DDim", steps=50, evals_per_shower=50, batch=1000, n_layers=6, gflop_per_eval=1.4708, binning="ds1_meta.json"),
 }
 
 
@@ -93,6 +100,23 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
+def _data_shape(cfg):
+    """models/diffusion.py:40-43: the caller-facing shower shape."""
+    return list(cfg["SHAPE_ORIG"][1:] if "orig" in cfg.get("SHOWER_EMBED", "") else cfg["SHAPE_PAD"][1:])
+
+
+def _binning(wl, cfg):
+    """Dataset-1 binning table (tests/golden/ds1_meta.json, written from the reference's parsed XML) -> temp BIN_FILE."""
+    import json
+    import tempfile
+    from calodiffusion_b200.geometry import write_binning_xml
+    with open(os.path.join(ROOT, "tests", "golden", wl["binning"])) as f:
+        meta = json.load(f)
+    path = os.path.join(tempfile.mkdtemp(prefix="cd_bins_"), "binning.xml")
+    cfg["BIN_FILE"] = write_binning_xml(path, meta["xml_r_edges"], meta["xml_a_bins"])
+    return meta
+
+
 def cpu_reference_leg(wl, budget_s=12.0, batch=16):
     """The reference's CPU algorithm for the path (oracle port: plain torch CPU fp32 ops, all host threads) on a
     bounded sample of the same workload.  Returns (showers_per_s, cores, sample description, seconds)."""
@@ -107,11 +131,24 @@ def cpu_reference_leg(wl, budget_s=12.0, batch=16):
     in_ch = 1 + (2 if cfg.get("R_Z_INPUT") else 0) + (1 if cfg.get("PHI_INPUT") else 0)
     shapes = {"model." + k: v for k, v in unet_param_shapes(cfg["LAYER_SIZE_UNET"], in_ch, cond_size, cfg["COND_SIZE_UNET"], zpr).items()}
     sd = synth_state_dict(shapes, seed=0)
-    o = DenoiserOracle(cfg, sd)
+    geom = None
+    if wl.get("binning"):   # in-loop NNConverter with the area-weighted maps and their pseudo-inverses (utils/utils.py:588-603)
+        import json
+        from oracle.geom_embed import GeomEmbedOracle, geom_weight_mats
+        with open(os.path.join(ROOT, "tests", "golden", wl["binning"])) as f:
+            meta = json.load(f)
+        mats, _ = geom_weight_mats(meta["lay_r_edges"])
+        rel = [i for i, e in enumerate(meta["xml_r_edges"]) if len(e) > 1]
+        alphas = [meta["xml_a_bins"][i] for i in rel]
+        bounds = [0]
+        for i, w in enumerate(mats):
+            bounds.append(bounds[-1] + alphas[i] * w.shape[1])
+        geom = GeomEmbedOracle.nn_converter(mats, [torch.linalg.pinv(w) for w in mats], bounds, alphas, max(alphas))
+    o = DenoiserOracle(cfg, sd, geom=geom)
     g = torch.Generator().manual_seed(1)
     E = torch.rand(batch, wl.get("cond_e", 1), generator=g)
     layers = torch.randn(batch, wl["n_layers"], generator=g) if wl["n_layers"] else None
-    start = torch.randn([batch] + cfg["SHAPE_PAD"][1:], generator=torch.Generator().manual_seed(2))
+    start = torch.randn([batch] + _data_shape(cfg), generator=torch.Generator().manual_seed(2))
     evals_done, t_total, n = 0, 0.0, 1
     with torch.no_grad():
         o.denoise(start, E, torch.ones(batch), layers)   # warm-up (thread pool, allocator)
@@ -174,7 +211,7 @@ def _op_profile(model, x, E, layers, sigma, reps=3):
     return rep
 
 
-def _roofline(rep, peaks, B):
+def _roofline(rep, peaks, B, workload):
     """Roofline entries of the dominant kernel launch shape (largest share of the evaluation time) and of the dominant
     HBM-bound one; the per-class table goes to the op-profile file."""
     total_ms = sum(v["ms"] for v in rep.values())
@@ -209,7 +246,7 @@ def _roofline(rep, peaks, B):
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 t = json.load(f).get(name)
-            if t and t.get("batch") == B:
+            if t and t.get("batch") == B and t.get("workload") == workload:
                 roof["traffic"] = t["dram_bytes_per_launch"]
                 roof["traffic_source"] = t["source"]
         except Exception:
@@ -242,6 +279,8 @@ def run_gpu_arm(args, wl):
         dist.init_process_group("nccl", device_id=dev)
 
     cfg, B, steps = dict(wl["cfg"]), int(args.batch or wl["batch"]), int(args.sampling_steps or wl["steps"])
+    if wl.get("binning"):
+        _binning(wl, cfg)
     torch.manual_seed(0)                                   # identical random-init weights on every rank
     model = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=B)
     if os.environ.get("CD_NO_GRAPH"):
@@ -250,13 +289,13 @@ def run_gpu_arm(args, wl):
     sampler.shower_offset = rank * B                       # global shower index keys the Philox stream
     if wl["sampler"] == "Heun":
         sampler.last_step_euler = True                     # finite showers; 2 evals on all other steps
-    vox = int(np.prod(cfg["SHAPE_PAD"][1:]))
+    vox = int(np.prod(_data_shape(cfg)))
     g = torch.Generator().manual_seed(1 + rank)
     E_host = torch.rand(B, wl.get("cond_e", 1), generator=g).pin_memory()
     L_host = torch.randn(B, wl["n_layers"], generator=g).pin_memory() if wl["n_layers"] else None
     E_dev = E_host.to(dev)
     L_dev = L_host.to(dev) if L_host is not None else None
-    start_dev = torch.randn([B] + cfg["SHAPE_PAD"][1:], device=dev, generator=torch.Generator(device=dev).manual_seed(2 + rank))
+    start_dev = torch.randn([B] + _data_shape(cfg), device=dev, generator=torch.Generator(device=dev).manual_seed(2 + rank))
     gathered = torch.empty(world * B, vox, device=dev) if world > 1 else None
 
     def barrier():
@@ -317,7 +356,7 @@ def run_gpu_arm(args, wl):
         peaks = _peaks()
         sig = torch.full((B,), 1.5, device=dev)
         rep = _op_profile(model, start_dev, E_dev, L_dev, sig)
-        roof, roof_hbm, table, eval_ms = _roofline(rep, peaks, B)
+        roof, roof_hbm, table, eval_ms = _roofline(rep, peaks, B, args.workload)
         reps = 3
         cpu = None
         if world == 1 and not args.no_cpu_baseline:

@@ -50,6 +50,15 @@ class BinningXML:
         return self.relevantlayers
 
 
+def write_binning_xml(path, r_edges, a_bins, particle="photon"):
+    """Emit a CaloChallenge-style binning file (one <Layer r_edges=... n_bin_alpha=...> per calorimeter layer)."""
+    rows = "".join('      <Layer id="%d" r_edges="%s" n_bin_alpha="%d" />\n' % (i, ",".join(repr(float(v)) for v in e), int(a))
+                   for i, (e, a) in enumerate(zip(r_edges, a_bins)))
+    with open(path, "w") as f:
+        f.write('<Bins>\n   <Bin pid="22" etaMin="0" etaMax="130" name="%s">\n%s   </Bin>\n</Bins>\n' % (particle, rows))
+    return str(path)
+
+
 def _csr_from_coo(n_rows, n_cols, rows, cols, vals):
     """Sorted CSR (int32 rowptr/col, fp32 val) from COO triplets."""
     rows = np.asarray(rows, np.int64)

@@ -51,11 +51,8 @@ def case(request):
 
 def write_binning_xml(path, meta, particle="photon"):
     """Re-emit the CaloChallenge binning file (as the reference's XMLHandler parsed it when the golden was made)."""
-    rows = "".join('      <Layer id="%d" r_edges="%s" n_bin_alpha="%d" />\n' % (i, ",".join(repr(float(v)) for v in e), a)
-                   for i, (e, a) in enumerate(zip(meta["xml_r_edges"], meta["xml_a_bins"])))
-    with open(path, "w") as f:
-        f.write('<Bins>\n   <Bin pid="22" etaMin="0" etaMax="130" name="%s">\n%s   </Bin>\n</Bins>\n' % (particle, rows))
-    return str(path)
+    from calodiffusion_b200.geometry import write_binning_xml as emit
+    return emit(path, meta["xml_r_edges"], meta["xml_a_bins"], particle)
 
 
 def ds1_geom_oracle(c):
