@@ -79,6 +79,7 @@ struct cd_unet {
     std::map<std::string, cd::ProfAcc> prof;
     int profile = 0;
     int debug_sync = 0;
+    int no_fused_attention = 0;   // option "fused_attention" 0: materialise qkv (1x1x1 conv) and run the three-pass attention on it
     std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
     int conv_backend = 0;
@@ -367,6 +368,7 @@ struct Builder {
         if (!wout || !bout) { ok = false; return -1; }
         size_t s1 = slot((size_t)C * 16);
         size_t skm = slot(32 * 4), sctx = slot(33 * 32 * 4);
+        size_t sfold = slot((size_t)C * 32 * 2);     // fused attention: per-sample folded (Ctx/S, to_out) matrix, fp16
         int xn = acquire(h, level, C);
         int qkv = acquire(h, level, 96);
         // PreNorm (GroupNorm(1,C), models.py:321-329) folded into the to_qkv 1x1x1 conv on the tcgen05 path:
@@ -374,6 +376,7 @@ struct Builder {
         // so the conv reads x directly (no normalised copy) and its epilogue applies the per-sample scalars.
         ConvW cqf;
         float *pn_wsum = nullptr, *pn_wb = nullptr;
+        __half* wf_h = nullptr;
         {
             const HostTensor* wq = find_w(h, pre + "fn.fn.to_qkv.conv.weight");
             const HostTensor* gm = find_w(h, pre + "fn.norm.weight");
@@ -394,6 +397,13 @@ struct Builder {
             if (!okp) { ok = false; return -1; }
             pn_wsum = h->upload(wsum);
             pn_wb = h->upload(wb);
+            if (attention_fused_supported(C)) {     // row-major fp16 [96][C] for the fused attention kernels
+                std::vector<__half> wh((size_t)96 * C);
+                for (size_t i = 0; i < wh.size(); ++i) wh[i] = __float2half_rn(folded.data[i]);
+                wf_h = h->dalloc<__half>(wh.size(), false);
+                if (!wf_h) { ok = false; return -1; }
+                cudaMemcpy(wf_h, wh.data(), wh.size() * sizeof(__half), cudaMemcpyHostToDevice);
+            }
         }
         float* pn_gamma = upload_vec(h, pre + "fn.norm.weight", C);
         float* pn_beta = upload_vec(h, pre + "fn.norm.bias", C);
@@ -405,7 +415,10 @@ struct Builder {
             snprintf(nm, sizeof(nm), "conv_k1_prenorm_c%d_96_L%d_mma", C, level);
             hh->op_info.push_back({nm, 2.0 * m * C * 96, 2.0 * m * (C + 96)});
         }
+        // fused form (cd_attention_fused.cu): q/k/v are recomputed from x inside the attention passes, no qkv tensor
+        const bool can_fuse = wf_h != nullptr;
         hh->ops.push_back([=](Run& r) {
+            if (can_fuse && hh->conv_backend == 0 && !hh->no_fused_attention) return;
             const Geom& g = hh->geom[level];
             ConvParams p;
             p.gin = g; p.gout = g; p.nsrc = 1; p.Cin_total = C;
@@ -440,6 +453,15 @@ struct Builder {
         }
         // attention + to_out conv -> xn reused as the raw output (+ its GroupNorm(1,C) statistics), then GN(1) + residual x
         hh->ops.push_back([=](Run& r) {
+            if (can_fuse && hh->conv_backend == 0 && !hh->no_fused_attention) {
+                const Geom& g = hh->geom[level];
+                launch_attention_fused(g, hh->bufs[x].ptr, wf_h, pn_wsum, pn_wb, (const double*)(hh->scratch + s0 * r.B),
+                                       (double)C * g.Z * g.P * g.R, (unsigned*)(hh->scratch + skm * r.B),
+                                       (float*)(hh->scratch + sctx * r.B), (__half*)(hh->scratch + sfold * r.B), wout, bout,
+                                       hh->bufs[xn].ptr, C, (double*)(hh->scratch + s1 * r.B), r.B, r.st);
+                hh->launches += 4;
+                return;
+            }
             launch_attention(hh->geom[level], hh->bufs[qkv].ptr, (unsigned*)(hh->scratch + skm * r.B),
                              (float*)(hh->scratch + sctx * r.B), wout, bout, hh->bufs[xn].ptr, C,
                              (double*)(hh->scratch + s1 * r.B), r.B, r.st);
@@ -790,6 +812,11 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
         return 0;
     }
     if (!strcmp(key, "debug_sync")) { h->debug_sync = value; return 0; }
+    if (!strcmp(key, "fused_attention")) {
+        h->no_fused_attention = value ? 0 : 1;
+        if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
+        return 0;
+    }
     if (!strcmp(key, "profile")) {
         h->profile = value;
         if (value == 2) { h->prof.clear(); h->profile = 1; }   // 2 = enable and reset

@@ -371,3 +371,23 @@ def test_shower_feature_histograms_match_oracle(models):
     assert worst_sep < 2e-2, worst_sep
     # independent noise: no feature rejects "same distribution" (13 features, N = 96: p > 1e-3 each)
     assert worst_p > 1e-3, worst_p
+
+
+@pytest.mark.parametrize("case", ["ds2", "ds3"])
+def test_fused_attention_matches_unfused(models, case):
+    """The fused PreNorm + to_qkv + attention kernels (no qkv tensor) against the three-pass form on the materialised
+    qkv tensor (option fused_attention = 0), and both against the reference golden."""
+    m, c = models(case)
+    sig = torch.from_numpy(c["gold"]["denoise_a_sigma"])
+    x = (c["x"] * (1 + sig.view(-1, 1, 1, 1, 1) ** 2).sqrt()).cuda()
+    args = dict(E=c["E"].cuda(), sigma=sig.cuda().view(-1, 1, 1, 1, 1), layers=None if c["layers"] is None else c["layers"].cuda())
+    y1 = m.denoise(x, **args).cpu().numpy()
+    h = m._engine(c["B"])
+    try:
+        assert m._lib.cd_unet_set_option(h, b"fused_attention", 0) == 0
+        y0 = m.denoise(x, **args).cpu().numpy()
+    finally:
+        m._lib.cd_unet_set_option(h, b"fused_attention", 1)
+    e1, e0, d = rel_l2(y1, c["gold"]["denoise_a"]), rel_l2(y0, c["gold"]["denoise_a"]), rel_l2(y1, y0)
+    print(case, f"fused vs ref {e1:.2e}, unfused vs ref {e0:.2e}, fused vs unfused {d:.2e}")
+    assert max(e1, e0) < TOL and d < TOL
