@@ -131,6 +131,9 @@ struct ConvParams {
     const float* pn_wb;       // [Cout] sum_c W[o][c]*beta[c]
     int pn_C;                 // channels of the normalised tensor
     double pn_count;          // elements per sample (C * voxels)
+    // Optional C_out-channel PLCP tensor added to the result before rounding / statistics (3x3x3 tcgen05 form only): lets a
+    // convolution over a wide concatenated input run as two resident-weight convolutions, the second accumulating onto the first.
+    const __half* addsrc = nullptr;
     int B;
 };
 

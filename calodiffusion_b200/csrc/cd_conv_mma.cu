@@ -92,6 +92,7 @@ struct MmaParams {
     int tiles_per_cta;
     uint32_t idesc;
     int write_halo;         // 1: interior rows with pp == 1 / pp == P are also stored to their phi halo copies
+    const __half* addsrc;   // 3x3x3 form: tensor added to the result (interior rows) before rounding and statistics, or nullptr
     const double* pn_stats; const float* pn_wsum; const float* pn_wb; int pn_C; float pn_inv_count;   // folded PreNorm (1x1x1)
     int dbg_mode;           // CD_MMA_DEBUG builds only: 1 = epilogue does nothing but release slots, 2 = load A only once
 };
@@ -531,6 +532,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             }
                         }
                     }
+                    if (p.addsrc && valid) {
+#pragma unroll
+                        for (int k = 0; k < W; k += 8) {
+                            if (k < w) {
+                                float f[8];
+                                unpack8(*reinterpret_cast<const Half8*>(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) acc[k + e] += f[e];
+                            }
+                        }
+                    }
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
 #pragma unroll
                     for (int k = 0; k < W; k += 8) {
@@ -697,6 +709,8 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.w = packed_w; p.bias = cp.bias; p.dst = cp.dst; p.stats = cp.stats;
     p.write_halo = cp.write_halo;
     if (cp.pn_stats && k3) return 1;        // the folded PreNorm exists in the 1x1x1 epilogue only
+    if (cp.addsrc && !k3) return 1;         // accumulation onto a tensor exists in the 3x3x3 epilogue only
+    p.addsrc = cp.addsrc;
     p.pn_stats = cp.pn_stats; p.pn_wsum = cp.pn_wsum; p.pn_wb = cp.pn_wb; p.pn_C = cp.pn_C;
     p.pn_inv_count = cp.pn_stats ? (float)(1.0 / cp.pn_count) : 0.f;
     p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout, taps); p.ncb = cp.Cout / p.CB;

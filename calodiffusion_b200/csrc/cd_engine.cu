@@ -277,6 +277,44 @@ struct Builder {
         });
     }
 
+    // stride-1 3x3x3 conv over two concatenated sources as two tcgen05 convs (see resblock); falls back to the single conv
+    void conv_split(const ConvW& full, const ConvW& wa, const ConvW& wb, int level, std::vector<int> srcs, int dst, long long stats_off) {
+        cd_unet* hh = h;
+        {
+            const Geom& g = hh->geom[level];
+            double m = (double)g.Z * g.P * g.R;
+            char nm[96];
+            snprintf(nm, sizeof(nm), "conv_k27_c%d+%d_%d_L%d_mma", wa.Cin, wb.Cin, full.Cout, level);
+            hh->op_info.push_back({nm, 2.0 * m * full.Cin * full.Cout * 27, 2.0 * m * (full.Cin + full.Cout)});
+        }
+        hh->ops.push_back([=](Run& r) {
+            ConvParams p;
+            p.gin = hh->geom[level]; p.gout = hh->geom[level];
+            p.dst = hh->bufs[dst].ptr; p.Cout = full.Cout;
+            p.kz = p.kp = p.kr = 3; p.sz = p.sp = p.sr = 1; p.pz = p.cp = p.pr = 1;
+            p.transposed = 0; p.write_halo = 0;
+            p.stats_cpg = full.Cout / (hh->d.groups > 0 ? hh->d.groups : 1);
+            p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
+            p.B = r.B;
+            double* stats = stats_off >= 0 ? (double*)(hh->scratch + (size_t)stats_off * r.B) : nullptr;
+            if (hh->conv_backend == 0) {
+                ConvParams pa = p;
+                pa.nsrc = 1; pa.Cin_total = wa.Cin; pa.src[0].base = hh->bufs[srcs[0]].ptr; pa.src[0].C = wa.Cin;
+                pa.src[1].base = nullptr; pa.src[1].C = 0; pa.w = wa.w; pa.bias = wa.bias; pa.stats = nullptr; pa.addsrc = nullptr;
+                ConvParams pb = pa;
+                pb.Cin_total = wb.Cin; pb.src[0].base = hh->bufs[srcs[1]].ptr; pb.src[0].C = wb.Cin; pb.w = wb.w; pb.bias = nullptr;
+                pb.stats = stats; pb.addsrc = p.dst;
+                if (launch_conv_mma(pa, wa.wmma, r.st) == 0 && launch_conv_mma(pb, wb.wmma, r.st) == 0) { hh->launches += 2; return; }
+            }
+            p.nsrc = 2; p.Cin_total = full.Cin;
+            for (int i = 0; i < 2; ++i) { p.src[i].base = hh->bufs[srcs[i]].ptr; p.src[i].C = hh->bufs[srcs[i]].C; }
+            p.w = full.w; p.bias = full.bias; p.stats = stats; p.addsrc = nullptr;
+            hh->launches += 1;
+            if (hh->conv_backend == 0 && full.wmma && launch_conv_mma(p, full.wmma, r.st) == 0) return;
+            launch_conv_generic(p, r.st);
+        });
+    }
+
     // GroupNorm finalize + apply:  dst = act(GN(src)) + addvec + residual   (all rows incl. halos)
     // out_stats_off >= 0: also accumulate the per-sample sum / sum of squares of dst (GroupNorm(1,C) of a following PreNorm)
     void gn(const std::string& gname, const std::string& bname, int level, int src, int dst, int C, int groups, long long stats_off,
@@ -333,6 +371,29 @@ struct Builder {
         }
         size_t s1 = slot((size_t)Cout * 16), s2 = slot((size_t)Cout * 16);
         int t1 = acquire(h, level, Cout);
+        // A 3x3x3 conv over a concatenated input whose weights cannot stay resident in shared memory (27*Cin*Cout fp16)
+        // runs as two resident-weight convs, one per source, the second accumulating onto the first (conv is linear in Cin).
+        ConvW ca, cb2;
+        bool split = false;
+        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 > (size_t)160 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT")) {
+            const int Ca = h->bufs[srcs[0]].C, Cb = h->bufs[srcs[1]].C;
+            const HostTensor* wfull = find_w(h, pre + "block1.proj.conv.weight");
+            if (wfull && Ca + Cb == Cin && mma_conv_supported(Ca, Cout, 27) && mma_conv_supported(Cb, Cout, 27)) {
+                HostTensor wa, wb;
+                wa.shape = {Cout, Ca, 3, 3, 3}; wb.shape = {Cout, Cb, 3, 3, 3};
+                wa.data.resize((size_t)Cout * Ca * 27); wb.data.resize((size_t)Cout * Cb * 27);
+                for (int co = 0; co < Cout; ++co) {
+                    std::copy_n(&wfull->data[((size_t)co * Cin) * 27], (size_t)Ca * 27, &wa.data[(size_t)co * Ca * 27]);
+                    std::copy_n(&wfull->data[((size_t)co * Cin + Ca) * 27], (size_t)Cb * 27, &wb.data[(size_t)co * Cb * 27]);
+                }
+                h->weights["__split_a"] = wa; h->weights["__split_b"] = wb;
+                split = pack_conv(h, "__split_a", pre + "block1.proj.conv.bias", Ca, Ca, Cout, 3, 3, 3, 0, true, &ca) &&
+                        pack_conv(h, "__split_b", "", Cb, Cb, Cout, 3, 3, 3, 0, true, &cb2) && ca.wmma && cb2.wmma;
+                h->weights.erase("__split_a"); h->weights.erase("__split_b");
+            }
+        }
+        if (split) conv_split(c1, ca, cb2, level, srcs, t1, (long long)s1);
+        else
         conv(c1, level, level, srcs, t1, 1, 1, 1, 1, 0, (long long)s1);
         int hbuf = acquire(h, level, Cout);
         gn(pre + "block1.norm.weight", pre + "block1.norm.bias", level, t1, hbuf, Cout, groups, (long long)s1, 1, addvec_off, -1);
