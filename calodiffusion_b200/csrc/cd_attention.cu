@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(256) attn_kmax_kernel(Geom g, const __half* __
         for (int u = 0; u < 4; ++u) {
             const uint32_t rem = base + u * 64 + lane;
             ok[u] = rem < r1;
-            if (ok[u]) v[u] = *reinterpret_cast<const Half8*>(plane + (long long)rem * 8);
+            if (ok[u]) v[u] = load8(plane + (long long)rem * 8);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -131,8 +131,8 @@ __global__ void __launch_bounds__(256, 2) attn_context_kernel(Geom g, const __ha
         if (inb) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                kv[c] = *reinterpret_cast<const Half8*>(base_k + c * cs + (long long)rem * 8);
-                vv[c] = *reinterpret_cast<const Half8*>(base_v + c * cs + (long long)rem * 8);
+                kv[c] = load8(base_k + c * cs + (long long)rem * 8);
+                vv[c] = load8(base_v + c * cs + (long long)rem * 8);
             }
         }
         const bool interior = inb && decode_subrow(g, rem).kind == 0;
@@ -150,8 +150,8 @@ __global__ void __launch_bounds__(256, 2) attn_context_kernel(Geom g, const __ha
                 for (int j = 0; j < 8; ++j) f[j] = 0.f;
                 vv[c] = pack8(f);
             }
-            *reinterpret_cast<Half8*>(sk + lane * kRowStrideB + c * 16) = pack8(f);
-            *reinterpret_cast<Half8*>(sv + lane * kRowStrideB + c * 16) = vv[c];
+            store8(sk + lane * kRowStrideB + c * 16, pack8(f));
+            store8(sv + lane * kRowStrideB + c * 16, vv[c]);
         }
         __syncwarp();
 #pragma unroll
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(256, NT <= 4 ? 3 : 2) attn_out_kernel(Geom g, 
         if (inb) {
             Half8 qv[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) qv[c] = *reinterpret_cast<const Half8*>(base_q + c * cs + (long long)rem * 8);
+            for (int c = 0; c < 4; ++c) qv[c] = load8(base_q + c * cs + (long long)rem * 8);
 #pragma unroll
             for (int c = 0; c < 4; ++c) unpack8(qv[c], q + 8 * c);
         } else {
@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(256, NT <= 4 ? 3 : 2) attn_out_kernel(Geom g, 
         for (int c = 0; c < 4; ++c) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) q[8 * c + j] *= inv;
-            *reinterpret_cast<Half8*>(sqw + lane * kRowStrideB + c * 16) = pack8(q + 8 * c);
+            store8(sqw + lane * kRowStrideB + c * 16, pack8(q + 8 * c));
         }
         __syncwarp();
 #pragma unroll

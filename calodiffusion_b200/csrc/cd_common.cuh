@@ -143,6 +143,21 @@ __device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.0f + e
 
 struct alignas(16) Half8 { __half2 h[4]; };
 
+// explicit 128-bit accesses: a struct copy through a Half8* may be split into four 32-bit accesses by the compiler
+__device__ __forceinline__ void store8(void* p, const Half8& v) {
+    uint4 u;
+    u.x = *reinterpret_cast<const uint32_t*>(&v.h[0]); u.y = *reinterpret_cast<const uint32_t*>(&v.h[1]);
+    u.z = *reinterpret_cast<const uint32_t*>(&v.h[2]); u.w = *reinterpret_cast<const uint32_t*>(&v.h[3]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ Half8 load8(const void* p) {
+    const uint4 u = *reinterpret_cast<const uint4*>(p);
+    Half8 v;
+    v.h[0] = *reinterpret_cast<const __half2*>(&u.x); v.h[1] = *reinterpret_cast<const __half2*>(&u.y);
+    v.h[2] = *reinterpret_cast<const __half2*>(&u.z); v.h[3] = *reinterpret_cast<const __half2*>(&u.w);
+    return v;
+}
+
 __device__ __forceinline__ void unpack8(const Half8& v, float* f) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) { float2 t = __half22float2(v.h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }

@@ -24,7 +24,7 @@ namespace {
 constexpr int kGThreads = 14 * 32;  // warp 0: weights, warp 1: MMA + TMEM alloc, warps 2-5: epilogue, warps 6-13: gather
 constexpr int kGMaxStages = 6;
 
-struct GTap { signed char dz, dq, dr, pad; int widx; };
+struct GTap { signed char dz, dq, dr, pad; int widx; int delta; };   // delta: input row offset (dz*Pp + dq)*Rp + dr of the tap
 struct GClass {
     int Zc, Pc, Rc;       // class-local output extents
     int ez, ep, er;       // output coordinate = local * om + e
@@ -41,6 +41,8 @@ struct GatherParams {
     const float* bias;
     __half* dst;
     int Cout;
+    int N;                // MMA width: Cout, or 2*Cout when a tile row produces the output pair (r, r+1) (transposed form)
+    int pair_r;           // 1: columns [Cout, 2*Cout) are the output voxel r+1 (stored to the next PLCP row if r+1 < R)
     int mz, mp, mr;       // input index = local * m + tap offset
     int oz, op, orr;      // output index = local * o + class offset
     int nclass;
@@ -81,6 +83,14 @@ __device__ __forceinline__ void g_mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void g_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// 16-byte asynchronous copy global -> shared; src_bytes = 0 writes zeros.  Completion is signalled on an mbarrier by
+// cp.async.mbarrier.arrive.noinc (counts as one of the barrier's expected arrivals once this thread's copies have landed).
+__device__ __forceinline__ void g_cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void g_cp_async_arrive(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ uint64_t g_make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     uint64_t d = 0;
@@ -151,7 +161,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
     unsigned char* wbuf = abuf + (size_t)p.nstages * p.a_stage_bytes;
     const uint32_t abuf_s = g_smem_u32(abuf), wbuf_s = g_smem_u32(wbuf);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int N = p.Cout;
+    const int N = p.N;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kGMaxStages; ++s) { g_mbar_init(g_smem_u32(&ctl->full[s]), 129); g_mbar_init(g_smem_u32(&ctl->empty[s]), 1); }
@@ -207,6 +217,8 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                     const int t0 = st * G;
                     const int nt = c.ntaps - t0 < G ? c.ntaps - t0 : G;
                     g_mbar_wait(g_smem_u32(&ctl->full[slot]), ph);
+                    // the tile was written through the generic proxy (cp.async); the MMA reads it through the async proxy
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint32_t al = (abuf_s + slot * p.a_stage_bytes) >> 4, bl = (wbuf_s + slot * p.w_stage_bytes) >> 4;
                     for (int e = 0; e < nt * (NCH / 2); ++e, al += 256u, bl += bstep) {   // stage layouts are contiguous in (tap, k16)
@@ -239,20 +251,24 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
             g_mbar_wait(g_smem_u32(&ctl->t_full[acc]), aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * 256;
+            const bool ok2 = rc.ok && p.pair_r && (ro + 1 < p.gout.R);     // second voxel of the pair exists (odd R: last one does not)
             for (int c0 = 0; c0 < N; c0 += 16) {
                 float v[16];
                 g_tmem_ld16(taddr + c0, v);
+                const int half = c0 >= p.Cout ? 1 : 0;              // which voxel of the pair these columns belong to
+                const int cc = c0 - half * p.Cout;
                 if (p.bias) {
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) v[k] += __ldg(p.bias + c0 + k);
+                    for (int k = 0; k < 16; ++k) v[k] += __ldg(p.bias + cc + k);
                 }
-                if (rc.ok) {
+                if (half ? ok2 : rc.ok) {
 #pragma unroll
                     for (int k = 0; k < 2; ++k) {
                         const Half8 h = pack8(v + 8 * k);
-                        *reinterpret_cast<Half8*>(p.dst + plcp_offset(p.gout, (c0 >> 3) + k, row)) = h;
-                        if (mirror >= 0) *reinterpret_cast<Half8*>(p.dst + plcp_offset(p.gout, (c0 >> 3) + k, mirror)) = h;
-                        if (mirror2 >= 0) *reinterpret_cast<Half8*>(p.dst + plcp_offset(p.gout, (c0 >> 3) + k, mirror2)) = h;
+                        __half* o = p.dst + plcp_offset(p.gout, (cc >> 3) + k, row + half);
+                        store8(o, h);
+                        if (mirror >= 0) store8(o + (mirror - row) * 8, h);
+                        if (mirror2 >= 0) store8(o + (mirror2 - row) * 8, h);
                     }
                 }
             }
@@ -270,34 +286,37 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
             const int nst = (c.ntaps + G - 1) / G;
             const RowCoord rc = class_coord(c, tile, i);
             const int zb = rc.z * p.mz, qb = rc.p * p.mp, rb = rc.r * p.mr;
-            const long long sample_row0 = (long long)rc.b * p.gin.rows_per_sample;
+            // 16-byte piece of chunk plane 0 at the tile row's base input voxel (padded phi index qb); taps add a row delta
+            const uint4* bp = reinterpret_cast<const uint4*>(
+                p.src + plcp_offset(p.gin, 0, (long long)rc.b * p.gin.rows_per_sample + ((long long)zb * p.gin.Pp + qb) * p.gin.Rp + rb));
+            const uint4* bp0 = reinterpret_cast<const uint4*>(p.src + plcp_offset(p.gin, 0, 0));   // always-valid address for zero fills
+            const int wrap = p.gin.P * p.gin.Rp;
+            const long long cs = p.gin.chunk_stride;     // uint4 units between chunk planes
             for (int st = 0; st < nst; ++st, ++n) {
                 if ((int)(n & 1) != pg) continue;
                 const uint32_t slot = n % p.nstages, ph = (n / p.nstages) & 1;
                 const int t0 = st * G;
-                uint4 v[16];
+                // asynchronous 16-byte gathers straight into the operand tile (zero-filled when the tap falls in the zero
+                // padding): nothing is staged in registers, so a thread keeps as many stages in flight as the ring is deep
+                g_mbar_wait(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
+                const uint32_t dst_s = abuf_s + slot * p.a_stage_bytes + (uint32_t)i * 16u;
 #pragma unroll
                 for (int gi = 0; gi < G; ++gi) {
-                    bool ok = rc.ok && (t0 + gi) < c.ntaps;
-                    const GTap tp = p.taps[c.tap0 + (ok ? t0 + gi : 0)];
-                    const int zi = zb + tp.dz, qq = qb + tp.dq, ri = rb + tp.dr;
-                    ok = ok && zi >= 0 && zi < p.gin.Z && qq >= 0 && qq < p.gin.P + 2 && ri >= 0 && ri < p.gin.R;
-                    int pi = qq - 1;
-                    if (pi < 0) pi += p.gin.P;
-                    if (pi >= p.gin.P) pi -= p.gin.P;
-                    const long long srow = sample_row0 + ((long long)zi * p.gin.Pp + (pi + 1)) * p.gin.Rp + ri;
+                    const bool tv = (t0 + gi) < c.ntaps;
+                    const GTap tp = p.taps[c.tap0 + (tv ? t0 + gi : 0)];
+                    const int qq = qb + tp.dq;
+                    const bool ok = rc.ok && tv && (unsigned)(zb + tp.dz) < (unsigned)p.gin.Z && (unsigned)qq < (unsigned)(p.gin.P + 2) &&
+                                    (unsigned)(rb + tp.dr) < (unsigned)p.gin.R;
+                    // circular phi: the halo positions 0 and P+1 read the interior copies P and 1
+                    const int delta = tp.delta + (qq == 0 ? wrap : 0) - (qq == p.gin.P + 1 ? wrap : 0);
+                    const uint4* q = ok ? bp + delta : bp0;
 #pragma unroll
                     for (int k = 0; k < NCH; ++k) {
-                        if (ok && k < p.src_chunks) v[gi * NCH + k] = __ldg(reinterpret_cast<const uint4*>(p.src + plcp_offset(p.gin, k, srow)));
-                        else v[gi * NCH + k] = make_uint4(0u, 0u, 0u, 0u);
+                        const bool ld = ok && k < p.src_chunks;
+                        g_cp_async16(dst_s + (uint32_t)(gi * NCH + k) * 2048u, ld ? q + k * cs : bp0, ld ? 16u : 0u);
                     }
                 }
-                g_mbar_wait(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
-                unsigned char* dstp = abuf + (size_t)slot * p.a_stage_bytes + (size_t)i * 16;
-#pragma unroll
-                for (int e = 0; e < 16; ++e) *reinterpret_cast<uint4*>(dstp + (size_t)e * 2048) = v[e];
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                g_mbar_arrive(g_smem_u32(&ctl->full[slot]));
+                g_cp_async_arrive(g_smem_u32(&ctl->full[slot]));
             }
         }
     }
@@ -331,6 +350,33 @@ void gather_pack_weights(const float* w, int Cin, int Cout, int taps, __half* ou
                     out[(((size_t)t * nkc + kc) * Cout + n) * 8 + j] =
                         __float2half_rn(ci < Cin ? w[((size_t)t * Cin + ci) * Cout + n] : 0.f);
                 }
+}
+
+// Transposed stride-2 conv with k_r = 4, R padding 1 (CylindricalConvTrans, models.py:25-62): one tile row produces the
+// output pair r = 2r', 2r'+1 from the input offsets dr = -1, 0, +1; merged tap (a, b, dr) has the [ci][2*Cout] matrix
+//   columns [0,Cout):      original tap c = 1 - 2dr  (output r = 2r',   dr in {-1, 0})
+//   columns [Cout,2Cout):  original tap c = 2 - 2dr  (output r = 2r'+1, dr in { 0, 1})
+// packed as [(a*kp + b)*3 + dr+1][kc][n2][8] fp16.
+size_t gather_packed_elems_pairT(int Cin, int Cout, int kz, int kp) { return (size_t)kz * kp * 3 * ((Cin + 15) / 16 * 16) * 2 * Cout; }
+void gather_pack_weights_pairT(const float* w, int Cin, int Cout, int kz, int kp, int kr, __half* out) {
+    const int Cp = (Cin + 15) / 16 * 16, nkc = Cp / 8, N2 = 2 * Cout;
+    for (int a = 0; a < kz; ++a)
+        for (int b = 0; b < kp; ++b)
+            for (int di = 0; di < 3; ++di) {
+                const int dr = di - 1;
+                const size_t t = ((size_t)a * kp + b) * 3 + di;
+                for (int kc = 0; kc < nkc; ++kc)
+                    for (int n2 = 0; n2 < N2; ++n2) {
+                        const int er = n2 / Cout, co = n2 - er * Cout;
+                        const int c = er + 1 - 2 * dr;
+                        for (int j = 0; j < 8; ++j) {
+                            const int ci = kc * 8 + j;
+                            float v = 0.f;
+                            if (c >= 0 && c < kr && ci < Cin) v = w[((size_t)((a * kp + b) * kr + c) * Cin + ci) * Cout + co];
+                            out[((t * nkc + kc) * N2 + n2) * 8 + j] = __float2half_rn(v);
+                        }
+                    }
+            }
 }
 
 template <int NCH>
@@ -389,49 +435,52 @@ int launch_conv_gather(const ConvParams& cp, const __half* packed_w, cudaStream_
     } else {
         // stride-2 transposed conv: output parity classes; zi = z' + (ez + pz - a)/2, q = p' + (ep + kp-1 - b)/2 (padded
         // axis, must stay inside [0, Pin+2)), ri = r' + (er + pr - c)/2, taps restricted to matching parity
+        if (cp.kr != 4 || cp.pr != 1 || 2 * cp.Cout > 256) return 1;
         p.mz = p.mp = p.mr = 1; p.oz = p.op = p.orr = 2;
         p.nclass = 0;
+        p.pair_r = 1;
         for (int ez = 0; ez < 2; ++ez)
-            for (int ep = 0; ep < 2; ++ep)
-                for (int er = 0; er < 2; ++er) {
-                    GClass c;
-                    c.Zc = (cp.gout.Z - ez + 1) / 2; c.Pc = (cp.gout.P - ep + 1) / 2; c.Rc = (cp.gout.R - er + 1) / 2;
-                    c.ez = ez; c.ep = ep; c.er = er; c.tap0 = ntap; c.ntaps = 0; c.tile0 = tile0;
-                    c.rows = (long long)cp.B * c.Zc * c.Pc * c.Rc;
-                    if (c.rows <= 0) continue;
-                    for (int a = 0; a < cp.kz; ++a) {
-                        if ((ez + cp.pz - a) & 1) continue;
-                        for (int b = 0; b < cp.kp; ++b) {
-                            if ((ep + cp.kp - 1 - b) & 1) continue;
-                            for (int cc = 0; cc < cp.kr; ++cc) {
-                                if ((er + cp.pr - cc) & 1) continue;
-                                if (ntap >= 64) return 1;
-                                GTap& t = p.taps[ntap];
-                                // arithmetic shift keeps floor semantics for the (even) negative numerators
-                                t.dz = (signed char)((ez + cp.pz - a) / 2); t.dq = (signed char)((ep + cp.kp - 1 - b) / 2);
-                                t.dr = (signed char)((er + cp.pr - cc) / 2); t.pad = 0;
-                                t.widx = (a * cp.kp + b) * cp.kr + cc;
-                                ++ntap; ++c.ntaps;
-                            }
+            for (int ep = 0; ep < 2; ++ep) {
+                GClass c;
+                c.Zc = (cp.gout.Z - ez + 1) / 2; c.Pc = (cp.gout.P - ep + 1) / 2; c.Rc = (cp.gout.R + 1) / 2;
+                c.ez = ez; c.ep = ep; c.er = 0; c.tap0 = ntap; c.ntaps = 0; c.tile0 = tile0;
+                c.rows = (long long)cp.B * c.Zc * c.Pc * c.Rc;
+                if (c.rows <= 0) continue;
+                for (int a = 0; a < cp.kz; ++a) {
+                    if ((ez + cp.pz - a) & 1) continue;
+                    for (int b = 0; b < cp.kp; ++b) {
+                        if ((ep + cp.kp - 1 - b) & 1) continue;
+                        for (int di = 0; di < 3; ++di) {
+                            if (ntap >= 64) return 1;
+                            GTap& t = p.taps[ntap];
+                            // arithmetic shift keeps floor semantics for the (even) negative numerators
+                            t.dz = (signed char)((ez + cp.pz - a) / 2); t.dq = (signed char)((ep + cp.kp - 1 - b) / 2);
+                            t.dr = (signed char)(di - 1); t.pad = 0;
+                            t.widx = (a * cp.kp + b) * 3 + di;
+                            ++ntap; ++c.ntaps;
                         }
                     }
-                    if (c.ntaps == 0) return 1;   // an output class without taps would need a bias-only path
-                    tile0 += (int)((c.rows + 127) / 128);
-                    p.cls[p.nclass++] = c;
                 }
+                if (c.ntaps == 0) return 1;   // an output class without taps would need a bias-only path
+                tile0 += (int)((c.rows + 127) / 128);
+                p.cls[p.nclass++] = c;
+            }
     }
+    for (int t = 0; t < ntap; ++t)
+        p.taps[t].delta = ((int)p.taps[t].dz * cp.gin.Pp + (int)p.taps[t].dq) * cp.gin.Rp + (int)p.taps[t].dr;
     p.ntiles = tile0;
     if (p.ntiles < 1) return 1;
+    p.N = p.pair_r ? 2 * cp.Cout : cp.Cout;
     p.G = 16 / nch;
     p.a_stage_bytes = 16 * 2048;
-    p.w_tap_bytes = nch * 8 * cp.Cout * 2;
+    p.w_tap_bytes = nch * 8 * p.N * 2;
     p.w_stage_bytes = p.G * p.w_tap_bytes;
     int stages = (max_smem - kGCtlBytes - 256) / (p.a_stage_bytes + p.w_stage_bytes);
     if (stages > kGMaxStages) stages = kGMaxStages;
     if (stages < 2) return 1;
     p.nstages = stages;
     const size_t smem = kGCtlBytes + (size_t)stages * (p.a_stage_bytes + p.w_stage_bytes) + 128;
-    p.idesc = (1u << 4) | ((uint32_t)(cp.Cout >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    p.idesc = (1u << 4) | ((uint32_t)(p.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     int grid = num_sms < p.ntiles ? num_sms : p.ntiles;
     cudaError_t e;
     switch (nch) {

@@ -537,7 +537,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         for (int k = 0; k < W; k += 8) {
                             if (k < w) {
                                 float f[8];
-                                unpack8(*reinterpret_cast<const Half8*>(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
+                                unpack8(load8(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
 #pragma unroll
                                 for (int e = 0; e < 8; ++e) acc[k + e] += f[e];
                             }
@@ -550,9 +550,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             Half8 h = pack8(acc + k);
                             if (!keep) h = Half8{};
                             __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
-                            if (do_store) *reinterpret_cast<Half8*>(o) = h;
-                            if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
-                            if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
+                            if (do_store) store8(o, h);
+                            if (halo_up) store8(o + (long long)halo_delta * 8, h);
+                            if (halo_dn) store8(o - (long long)halo_delta * 8, h);
                         }
                     }
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(12, DBG_T() - tE1);
@@ -617,9 +617,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         Half8 h = pack8(acc);
                         if (!keep) h = Half8{};
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
-                        if (do_store) *reinterpret_cast<Half8*>(o) = h;
-                        if (halo_up) *reinterpret_cast<Half8*>(o + (long long)halo_delta * 8) = h;
-                        if (halo_dn) *reinterpret_cast<Half8*>(o - (long long)halo_delta * 8) = h;
+                        if (do_store) store8(o, h);
+                        if (halo_up) store8(o + (long long)halo_delta * 8, h);
+                        if (halo_dn) store8(o - (long long)halo_delta * 8, h);
                     }
                 }
             }

@@ -197,8 +197,10 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
     if (want_gather && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {
-        std::vector<__half> hp(gather_packed_elems(Cin_pad, Cout, taps));
-        gather_pack_weights(pk.data(), Cin_pad, Cout, taps, hp.data());
+        const bool pairT = transposed && kr == 4;     // transposed convs use the merged output-pair taps
+        std::vector<__half> hp(pairT ? gather_packed_elems_pairT(Cin_pad, Cout, kz, kp) : gather_packed_elems(Cin_pad, Cout, taps));
+        if (pairT) gather_pack_weights_pairT(pk.data(), Cin_pad, Cout, kz, kp, kr, hp.data());
+        else gather_pack_weights(pk.data(), Cin_pad, Cout, taps, hp.data());
         out->wgat = h->dalloc<__half>(hp.size(), false);
         if (out->wgat) cudaMemcpy(out->wgat, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
@@ -755,7 +757,7 @@ __global__ void dense_to_plcp_kernel(Geom g, const float* __restrict__ x, __half
         if (ri.kind != 2)
             for (int j = 0; j < 8; ++j)
                 f[j] = x[((long long)ri.b * C + k * 8 + j) * sp + ((long long)ri.z * g.P + p) * g.R + ri.rr];
-        *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = pack8(f);
+        store8(dst + plcp_offset(g, k, row), pack8(f));
     }
 }
 __global__ void plcp_to_dense_kernel(Geom g, const __half* __restrict__ src, float* __restrict__ y, int C, long long nvox) {
@@ -769,7 +771,7 @@ __global__ void plcp_to_dense_kernel(Geom g, const __half* __restrict__ src, flo
     int p = rem2 / g.R, r = rem2 - p * g.R;
     long long row = interior_row(g, b, z, p, r);
     for (int k = 0; k < C / 8; ++k) {
-        Half8 hv = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k, row));
+        Half8 hv = load8(src + plcp_offset(g, k, row));
         float f[8];
         unpack8(hv, f);
         for (int j = 0; j < 8; ++j) y[((long long)b * C + k * 8 + j) * sp + rem] = f[j];

@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(256) prep_input_kernel(Geom g, const float* __
         if (rz_input) { f[c++] = r_vals[sr.rr]; f[c++] = (float)sr.z / (float)g.Z; }
         if (phi_input) { f[c++] = (g.P > 1) ? (float)p / (float)(g.P - 1) : 0.f; }
     }
-    *reinterpret_cast<Half8*>(dst + plcp_offset(g, 0, row)) = pack8(f);
+    store8(dst + plcp_offset(g, 0, row), pack8(f));
     // channel padding up to the tensor-core K granularity (the buffer may have been used by another layer)
     for (int k = 1; k < out_chunks; ++k) *reinterpret_cast<uint4*>(dst + plcp_offset(g, k, row)) = make_uint4(0u, 0u, 0u, 0u);
 }
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(256) prep_input_geom_kernel(Geom g, GeomMap en
         if (rz_input) { f[c++] = r_vals[sr.rr]; f[c++] = (float)sr.z / (float)g.Z; }
         if (phi_input) { f[c++] = (g.P > 1) ? (float)p / (float)(g.P - 1) : 0.f; }
     }
-    *reinterpret_cast<Half8*>(dst + plcp_offset(g, 0, row)) = pack8(f);
+    store8(dst + plcp_offset(g, 0, row), pack8(f));
     for (int k = 1; k < out_chunks; ++k) *reinterpret_cast<uint4*>(dst + plcp_offset(g, k, row)) = make_uint4(0u, 0u, 0u, 0u);
 }
 
@@ -146,7 +146,7 @@ __global__ void conv_generic_kernel(ConvParams p, long long nrows) {
                         const __half* sb = p.src[s].base;
                         int nch = p.src[s].C >> 3;
                         for (int k = 0; k < nch; ++k) {
-                            Half8 v = *reinterpret_cast<const Half8*>(sb + plcp_offset(gi, k, irow));
+                            Half8 v = load8(sb + plcp_offset(gi, k, irow));
                             float f[8];
                             unpack8(v, f);
 #pragma unroll
@@ -169,7 +169,7 @@ __global__ void conv_generic_kernel(ConvParams p, long long nrows) {
     }
     if (active && (compute || p.write_halo)) {
         // zero rows are written as zeros only in write_halo mode; raw mode leaves halos untouched
-        *reinterpret_cast<Half8*>(p.dst + plcp_offset(p.gout, cog, row)) = pack8(acc);
+        store8(p.dst + plcp_offset(p.gout, cog, row), pack8(acc));
     }
     if (p.stats) {
         // per-(sample, channel) sum / sum of squares over interior rows, of the fp16-rounded values
@@ -291,14 +291,14 @@ __global__ void __launch_bounds__(kGnThreads, 4) gn_apply_kernel(
             Half8 v[4], rv[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                if (k0 + i < nch) v[i] = *reinterpret_cast<const Half8*>(src + plcp_offset(g, k0 + i, srow));
+                if (k0 + i < nch) v[i] = load8(src + plcp_offset(g, k0 + i, srow));
             if (residual) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
                     if (k0 + i < nch) {
                         const int k = k0 + i;
                         const __half* rb = (k < res_split) ? residual + plcp_offset(g, k, srow) : residual2 + plcp_offset(g, k - res_split, srow);
-                        rv[i] = *reinterpret_cast<const Half8*>(rb);
+                        rv[i] = load8(rb);
                     }
             }
 #pragma unroll
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(kGnThreads, 4) gn_apply_kernel(
                     for (int j = 0; j < 8; ++j) f[j] += r[j];
                 }
                 const Half8 o = pack8(f);
-                *reinterpret_cast<Half8*>(dst + plcp_offset(g, k, row)) = o;
+                store8(dst + plcp_offset(g, k, row), o);
                 if (out_stats && sr.kind == 0) {
                     unpack8(o, f);
 #pragma unroll
@@ -494,7 +494,7 @@ __global__ void final_kernel(FinalParams p, long long nvox) {
     float pred = p.bias;
     int nch = p.C >> 3;
     for (int k = 0; k < nch; ++k) {
-        Half8 hv = *reinterpret_cast<const Half8*>(p.h + plcp_offset(g, k, row));
+        Half8 hv = load8(p.h + plcp_offset(g, k, row));
         float f[8];
         unpack8(hv, f);
 #pragma unroll

@@ -76,6 +76,9 @@ int launch_conv_gather(const ConvParams& p, const __half* packed_w, cudaStream_t
 bool gather_conv_supported(int Cin, int Cout);
 size_t gather_packed_elems(int Cin, int Cout, int taps);
 void gather_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out);
+// transposed stride-2 convs (k_r = 4): merged (r, r+1) output-pair taps, see cd_conv_gather.cu
+size_t gather_packed_elems_pairT(int Cin, int Cout, int kz, int kp);
+void gather_pack_weights_pairT(const float* w, int Cin, int Cout, int kz, int kp, int kr, __half* out);
 bool mma_conv_supported(int Cin, int Cout, int taps);
 size_t mma_packed_elems(int Cin, int Cout, int taps);
 // w: fp32 [tap][ci][co]; out: fp16 blocks in the layout the tcgen05 kernel streams (see cd_conv_mma.cu)
