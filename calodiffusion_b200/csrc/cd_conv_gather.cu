@@ -87,7 +87,7 @@ __device__ __forceinline__ void g_bulk_g2s(uint32_t dst, const void* src, uint32
 // 16-byte asynchronous copy global -> shared; src_bytes = 0 writes zeros.  Completion is signalled on an mbarrier by
 // cp.async.mbarrier.arrive.noinc (counts as one of the barrier's expected arrivals once this thread's copies have landed).
 __device__ __forceinline__ void g_cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void g_cp_async_arrive(uint32_t bar) {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
