@@ -377,7 +377,11 @@ struct Builder {
         // runs as two resident-weight convs, one per source, the second accumulating onto the first (conv is linear in Cin).
         ConvW ca, cb2;
         bool split = false;
-        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 > (size_t)160 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT")) {
+        // (criterion: resident weights + two activation windows of the full input width exceed what one CTA can hold, so the
+        //  single conv would stream its weights or stage K in many small groups; measured on DS2 L1 128->32 and DS3 L0 64->32)
+        const Geom& gl = h->geom[level];
+        const size_t win_bytes = (size_t)(128 + 2 * (gl.Pp * gl.Rp + gl.Rp + 1)) * Cin * 2;
+        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 + 2 * win_bytes > (size_t)300 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT")) {
             const int Ca = h->bufs[srcs[0]].C, Cb = h->bufs[srcs[1]].C;
             const HostTensor* wfull = find_w(h, pre + "block1.proj.conv.weight");
             if (wfull && Ca + Cb == Cin && mma_conv_supported(Ca, Cout, 27) && mma_conv_supported(Cb, Cout, 27)) {
