@@ -12,8 +12,13 @@ EXPORTS = [
     "cd_last_error", "cd_version", "cd_device_check", "cd_unet_create", "cd_unet_destroy", "cd_unet_set_weight",
     "cd_unet_finalize", "cd_unet_set_option", "cd_unet_workspace_bytes", "cd_unet_launch_count", "cd_unet_forward",
     "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_reverse_norm", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
-    "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply",
+    "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply", "cd_layer_model_create",
 ]
+
+
+class LayerDesc(C.Structure):
+    _fields_ = [("dim_in", C.c_int), ("hidden", C.c_int), ("num_layers", C.c_int), ("cond_size", C.c_int), ("cond_dim", C.c_int),
+                ("time_embed", C.c_int), ("sigma_data", C.c_float), ("max_batch", C.c_int)]
 
 
 class UnetDesc(C.Structure):
@@ -70,6 +75,8 @@ def load():
     lib.cd_device_check.restype = i32
     lib.cd_unet_create.restype = vp
     lib.cd_unet_create.argtypes = [C.POINTER(UnetDesc)]
+    lib.cd_layer_model_create.restype = vp
+    lib.cd_layer_model_create.argtypes = [C.POINTER(LayerDesc)]
     lib.cd_unet_destroy.argtypes = [vp]
     lib.cd_unet_destroy.restype = None
     lib.cd_unet_set_weight.argtypes = [vp, C.c_char_p, vp, C.POINTER(i64), i32]

@@ -257,10 +257,7 @@ class CaloDiffusion(Diffusion):
             self._max_batch = int(batch)
         self._destroy_handle()
         lib = self._lib
-        desc = self._desc(self._max_batch)
-        h = lib.cd_unet_create(C.byref(desc))
-        if not h:
-            raise RuntimeError("cd_unet_create failed: " + lib.cd_last_error().decode())
+        h = self._create_handle(lib, self._max_batch)
         try:
             for name, p in self.model.named_parameters():
                 t = p.detach().to("cpu", torch.float32).contiguous()
@@ -278,6 +275,13 @@ class CaloDiffusion(Diffusion):
             lib.cd_unet_destroy(h)
             raise
         self._handle, self._handle_versions = h, versions
+        return h
+
+    def _create_handle(self, lib, max_batch):
+        desc = self._desc(max_batch)
+        h = lib.cd_unet_create(C.byref(desc))
+        if not h:
+            raise RuntimeError("cd_unet_create failed: " + lib.cd_last_error().decode())
         return h
 
     def set_conv_backend(self, backend):

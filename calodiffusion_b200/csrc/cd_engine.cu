@@ -79,6 +79,9 @@ struct cd_unet {
     std::map<std::string, cd::ProfAcc> prof;
     int profile = 0;
     int debug_sync = 0;
+    bool dense = false;           // layer-energy ResNet (cd_layer_model_create) instead of the U-Net
+    cd_layer_desc ld = {};
+    LayerMlpParams lm = {};
     int no_fused_attention = 0;   // option "fused_attention" 0: materialise qkv (1x1x1 conv) and run the three-pass attention on it
     std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
@@ -541,7 +544,64 @@ struct Builder {
     }
 };
 
+// [out][in] row-major fp32 -> device [in][out]
+static const float* upload_transposed(cd_unet* h, const std::string& name, int n_out, int n_in) {
+    const HostTensor* t = find_w(h, name);
+    if (!t) { fail("missing weight %s", name.c_str()); return nullptr; }
+    if ((int)t->data.size() != n_out * n_in) { fail("weight %s has unexpected size %zu (want %dx%d)", name.c_str(), t->data.size(), n_out, n_in); return nullptr; }
+    std::vector<float> w((size_t)n_in * n_out);
+    for (int o = 0; o < n_out; ++o)
+        for (int i = 0; i < n_in; ++i) w[(size_t)i * n_out + o] = t->data[(size_t)o * n_in + i];
+    return h->upload(w);
+}
+
+// dense ResNet of the layer-energy model (models/models.py:390-457): one kernel per evaluation
+static int build_dense_plan(cd_unet* h) {
+    const cd_layer_desc& d = h->ld;
+    const std::string M = "model.";
+    LayerMlpParams& m = h->lm;
+    const int half = d.cond_dim / 2;
+    m.dim_in = d.dim_in; m.hidden = d.hidden; m.n_hidden = d.num_layers - 1; m.cond_size = d.cond_size; m.cond_dim = d.cond_dim;
+    m.time_mode = d.time_embed;
+    const int tidx[3] = {1, 3, 5}, cidx[3] = {0, 2, 4};
+    const int tin[3] = {1, half / 2, half}, cin[3] = {d.cond_size, half / 2, half}, outs[3] = {half / 2, half, half};
+    for (int i = 0; i < 3; ++i) {
+        m.tw[i] = upload_transposed(h, M + "time_mlp." + std::to_string(tidx[i]) + ".weight", outs[i], tin[i]);
+        m.tb[i] = upload_vec(h, M + "time_mlp." + std::to_string(tidx[i]) + ".bias", outs[i]);
+        m.cw[i] = upload_transposed(h, M + "cond_mlp." + std::to_string(cidx[i]) + ".weight", outs[i], cin[i]);
+        m.cb[i] = upload_vec(h, M + "cond_mlp." + std::to_string(cidx[i]) + ".bias", outs[i]);
+        if (!m.tw[i] || !m.tb[i] || !m.cw[i] || !m.cb[i]) return 1;
+    }
+    m.in_w = upload_transposed(h, M + "in_lay.weight", d.hidden, d.dim_in);
+    m.in_b = upload_vec(h, M + "in_lay.bias", d.hidden);
+    m.out_w = upload_transposed(h, M + "out_lay.weight", d.dim_in, d.hidden);
+    m.out_b = upload_vec(h, M + "out_lay.bias", d.dim_in);
+    if (!m.in_w || !m.in_b || !m.out_w || !m.out_b) return 1;
+    for (int l = 0; l < m.n_hidden; ++l) {
+        const std::string L = M + "hidden_layers." + std::to_string(l) + ".";
+        m.ew[l] = upload_transposed(h, L + "embeder.1.weight", d.hidden, d.cond_dim);
+        m.eb[l] = upload_vec(h, L + "embeder.1.bias", d.hidden);
+        m.w1[l] = upload_transposed(h, L + "dense1.0.weight", d.hidden, d.hidden);
+        m.b1[l] = upload_vec(h, L + "dense1.0.bias", d.hidden);
+        m.w2[l] = upload_transposed(h, L + "dense2.0.weight", d.hidden, d.hidden);
+        m.b2[l] = upload_vec(h, L + "dense2.0.bias", d.hidden);
+        if (!m.ew[l] || !m.eb[l] || !m.w1[l] || !m.b1[l] || !m.w2[l] || !m.b2[l]) return 1;
+    }
+    const double mac = (double)d.dim_in * d.hidden * 2 + (double)m.n_hidden * ((double)d.cond_dim * d.hidden + 2.0 * d.hidden * d.hidden);
+    h->op_info.push_back({"layer_mlp", 2.0 * mac, 8.0 * d.dim_in});
+    h->ops.push_back([h](Run& r) {
+        FinalParams f = r.fin;
+        f.x = r.x; f.sigma = r.sigma; f.sigma_stride = r.sigma_stride;
+        f.sigma_data = r.scale_input ? h->ld.sigma_data : -1.f;
+        launch_layer_mlp(h->lm, f, r.cond, r.B, r.time_is_raw, r.st);
+        h->launches += 1;
+    });
+    h->scratch_per_sample = 0;
+    return 0;
+}
+
 static int build_plan(cd_unet* h) {
+    if (h->dense) return build_dense_plan(h);
     const cd_unet_desc& d = h->d;
     Builder b;
     b.h = h;
@@ -822,6 +882,27 @@ cd_unet* cd_unet_create(const cd_unet_desc* desc) {
         h->geom[l] = make_geom(Z, P, R, desc->max_batch);
         Z = (Z + 1) / 2; P = P / 2; R = R / 2;  // models.py:629-634
     }
+    return h;
+}
+
+cd_unet* cd_layer_model_create(const cd_layer_desc* desc) {
+    if (!desc) { fail("null desc"); return nullptr; }
+    if (cd_device_check()) return nullptr;
+    if (desc->dim_in < 1 || desc->dim_in > 64 || desc->hidden < 8 || desc->hidden > 256 || desc->num_layers < 2 || desc->num_layers > 9 ||
+        desc->cond_size < 1 || desc->cond_size > 64 || desc->cond_dim < 8 || desc->cond_dim > 128 || desc->cond_dim % 4 || desc->max_batch < 1) {
+        fail("unsupported layer-model shape (dim_in %d, hidden %d, layers %d, cond %d/%d)", desc->dim_in, desc->hidden, desc->num_layers,
+             desc->cond_size, desc->cond_dim);
+        return nullptr;
+    }
+    cd_unet* h = new cd_unet();
+    memset(&h->d, 0, sizeof(h->d));
+    h->dense = true;
+    h->ld = *desc;
+    // the shared machinery (state buffers, sampling loop, Philox keys) sees a (dim_in, 1, 1) "grid"
+    h->d.Z = desc->dim_in; h->d.P = 1; h->d.R = 1; h->d.n_sizes = 2; h->d.max_batch = desc->max_batch;
+    h->d.cond_size = desc->cond_size; h->d.cond_dim = desc->cond_dim; h->d.sigma_data = desc->sigma_data; h->d.time_embed = desc->time_embed;
+    h->n_levels = 1;
+    h->geom[0] = make_geom(desc->dim_in, 1, 1, desc->max_batch);
     return h;
 }
 

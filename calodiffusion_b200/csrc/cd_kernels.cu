@@ -545,6 +545,102 @@ void launch_geom_decode(const FinalParams& p, const GeomMap& dec, const float* g
     geom_decode_kernel<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(p, dec, grid_pred, nvox);
 }
 
+// =================================================================================================
+// Dense ResNet denoiser of the layer-energy model (LayerDiffusion.layer_model: models/layerdiffusion.py:34-37, 111-114;
+// ResNet / ResDense models/models.py:372-457), fp32 throughout, fused with the pre-conditioning output and the sampler
+// update (same tail as final_kernel).  One block carries kLmS showers through the whole network: every weight matrix is
+// read once per block ([in][out] layout, thread = output column, coalesced) and applied to all kLmS showers held in
+// shared memory.  dim_in <= 64 values per shower, hidden <= 256.
+// =================================================================================================
+constexpr int kLmS = 8;
+__device__ __forceinline__ void lm_dense(const float* __restrict__ Wt, const float* __restrict__ bias, const float* in, int in_stride,
+                                         float* out, int out_stride, int n_in, int n_out, int act, const float* add, int add_stride,
+                                         const float* res, int res_stride) {
+    // out[s][o] = act(bias[o] + sum_i in[s][i] * Wt[i][o]) (+ add[s][o]) (+ res[s][o]);  act: 0 none, 1 GELU
+    for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
+        float acc[kLmS];
+        const float bo = bias ? __ldg(bias + o) : 0.f;
+#pragma unroll
+        for (int s = 0; s < kLmS; ++s) acc[s] = bo;
+        for (int i = 0; i < n_in; ++i) {
+            const float w = __ldg(Wt + (long long)i * n_out + o);
+#pragma unroll
+            for (int s = 0; s < kLmS; ++s) acc[s] = fmaf(in[s * in_stride + i], w, acc[s]);
+        }
+#pragma unroll
+        for (int s = 0; s < kLmS; ++s) {
+            float v = act ? gelu_erf(acc[s]) : acc[s];
+            if (add) v += add[s * add_stride + o];
+            if (res) v += res[s * res_stride + o];
+            out[s * out_stride + o] = v;
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) layer_mlp_kernel(LayerMlpParams m, FinalParams p, const float* __restrict__ cond, int B,
+                                                        int time_is_raw) {
+    __shared__ float xin[kLmS][64];
+    __shared__ float cvec[kLmS][128];      // [cond_mlp output | time_mlp output] (models.py:443-445), then GELU of it
+    __shared__ float t0[kLmS][64], t1[kLmS][64];
+    __shared__ float h[kLmS][256], a[kLmS][256], e[kLmS][256];
+    const int b0 = blockIdx.x * kLmS;
+    const int D = m.dim_in, H = m.hidden, half = m.cond_dim / 2;
+    for (int i = threadIdx.x; i < kLmS * 64; i += blockDim.x) {
+        const int s = i >> 6, j = i & 63, b = b0 + s;
+        float v = 0.f;
+        if (b < B && j < D) {
+            const float sg = p.sigma[(long long)b * p.sigma_stride];
+            const float c_in = p.sigma_data > 0.f ? rsqrtf(sg * sg + p.sigma_data * p.sigma_data) : 1.f;
+            v = p.x[(long long)b * D + j] * c_in;
+        }
+        xin[s][j] = v;
+    }
+    if (threadIdx.x < kLmS) {
+        const int b = b0 + threadIdx.x;
+        float tv = 0.f;
+        if (b < B) {
+            const float sg = p.sigma[(long long)b * p.sigma_stride];
+            tv = time_is_raw ? sg : (m.time_mode == 0 ? sg / sqrtf(1.f + sg * sg) : 0.5f * logf(sg));
+        }
+        t0[threadIdx.x][0] = tv;
+    }
+    __syncthreads();
+    // time_mlp: Linear(1,h/2) GELU Linear(h/2,h) GELU Linear(h,h) -> cvec[:, half:]
+    lm_dense(m.tw[0], m.tb[0], &t0[0][0], 64, &t1[0][0], 64, 1, half / 2, 1, nullptr, 0, nullptr, 0);
+    lm_dense(m.tw[1], m.tb[1], &t1[0][0], 64, &t0[0][0], 64, half / 2, half, 1, nullptr, 0, nullptr, 0);
+    lm_dense(m.tw[2], m.tb[2], &t0[0][0], 64, &cvec[0][half], 128, half, half, 0, nullptr, 0, nullptr, 0);
+    // cond_mlp: Linear(cs,h/2) GELU Linear(h/2,h) GELU Linear(h,h) -> cvec[:, :half]
+    for (int i = threadIdx.x; i < kLmS * m.cond_size; i += blockDim.x) {
+        const int s = i / m.cond_size, j = i - s * m.cond_size, b = b0 + s;
+        t0[s][j] = b < B ? cond[(long long)b * m.cond_size + j] : 0.f;
+    }
+    __syncthreads();
+    lm_dense(m.cw[0], m.cb[0], &t0[0][0], 64, &t1[0][0], 64, m.cond_size, half / 2, 1, nullptr, 0, nullptr, 0);
+    lm_dense(m.cw[1], m.cb[1], &t1[0][0], 64, &t0[0][0], 64, half / 2, half, 1, nullptr, 0, nullptr, 0);
+    lm_dense(m.cw[2], m.cb[2], &t0[0][0], 64, &cvec[0][0], 128, half, half, 0, nullptr, 0, nullptr, 0);
+    // every ResDense embeder starts with GELU(cond) (models.py:377): apply it once
+    for (int i = threadIdx.x; i < kLmS * 128; i += blockDim.x) cvec[i >> 7][i & 127] = gelu_erf(cvec[i >> 7][i & 127]);
+    __syncthreads();
+    lm_dense(m.in_w, m.in_b, &xin[0][0], 64, &h[0][0], 256, D, H, 0, nullptr, 0, nullptr, 0);
+    for (int l = 0; l < m.n_hidden; ++l) {
+        lm_dense(m.ew[l], m.eb[l], &cvec[0][0], 128, &e[0][0], 256, m.cond_dim, H, 0, nullptr, 0, nullptr, 0);       // embed
+        lm_dense(m.w1[l], m.b1[l], &h[0][0], 256, &a[0][0], 256, H, H, 1, &e[0][0], 256, nullptr, 0);                // GELU(dense1) + embed
+        lm_dense(m.w2[l], m.b2[l], &a[0][0], 256, &e[0][0], 256, H, H, 1, nullptr, 0, &h[0][0], 256);                // GELU(dense2) + x
+        for (int i = threadIdx.x; i < kLmS * H; i += blockDim.x) h[i / H][i % H] = e[i / H][i % H];
+        __syncthreads();
+    }
+    lm_dense(m.out_w, m.out_b, &h[0][0], 256, &a[0][0], 256, H, D, 0, nullptr, 0, nullptr, 0);
+    for (int i = threadIdx.x; i < kLmS * D; i += blockDim.x) {
+        const int s = i / D, j = i - s * D, b = b0 + s;
+        if (b < B) final_tail(p, (long long)b * D + j, b, j, a[s][j]);
+    }
+}
+
+void launch_layer_mlp(const LayerMlpParams& m, const FinalParams& p, const float* cond, int B, int time_is_raw, cudaStream_t st) {
+    layer_mlp_kernel<<<(B + kLmS - 1) / kLmS, 256, 0, st>>>(m, p, cond, B, time_is_raw);
+}
+
 // x_out = a*x + b*noise (start scaling  x = start*sigma_0, and the EDM churn pre-noise, sample.py:633,651)
 __global__ void axpby_kernel(const float* __restrict__ x, const float* __restrict__ noise, float* __restrict__ out,
                              const float* __restrict__ coef, long long n, int vps, uint64_t seed, int shower_offset,
@@ -577,8 +673,21 @@ __global__ void copy16_kernel(const uint4* __restrict__ src, uint4* __restrict__
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) dst[i] = src ? src[i] : make_uint4(0u, 0u, 0u, 0u);
     if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail ? src_tail[threadIdx.x] : 0;
 }
+__global__ void copy4_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, long long n4) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) dst[i] = src ? src[i] : 0u;
+}
 void launch_copy_bytes(const void* src, void* dst, size_t bytes, cudaStream_t st) {
-    // src == nullptr clears dst.  Both pointers must be 16-byte aligned (all library and torch allocations are).
+    // src == nullptr clears dst.  16-byte vectors when both pointers allow it; record slots of odd-sized tensors
+    // (e.g. B x 46 layer-energy vectors) are only 4-byte aligned and take the word form.
+    if ((((uintptr_t)src | (uintptr_t)dst) & 15u) != 0 && (((uintptr_t)src | (uintptr_t)dst | bytes) & 3u) == 0) {
+        const long long n4 = (long long)(bytes / 4);
+        long long blocks = (n4 + 255) / 256;
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        if (blocks < 1) blocks = 1;
+        copy4_kernel<<<(unsigned)blocks, 256, 0, st>>>((const uint32_t*)src, (uint32_t*)dst, n4);
+        return;
+    }
     const long long n16 = (long long)(bytes / 16);
     const int tail = (int)(bytes % 16);
     long long blocks = (n16 + 255) / 256;

@@ -30,6 +30,18 @@ struct FinalParams {
 // CSR linear map between the caller's flat voxel vector and the regular grid (device pointers)
 struct GeomMap { const int* rowptr; const int* col; const float* val; int n_rows, n_cols; };
 
+// dense ResNet of the layer-energy model; all matrices transposed to [in][out] fp32 (device pointers)
+struct LayerMlpParams {
+    int dim_in, hidden, n_hidden, cond_size, cond_dim, time_mode;
+    const float* tw[3]; const float* tb[3];
+    const float* cw[3]; const float* cb[3];
+    const float* in_w; const float* in_b;
+    const float* ew[8]; const float* eb[8];
+    const float* w1[8]; const float* b1[8];
+    const float* w2[8]; const float* b2[8];
+    const float* out_w; const float* out_b;
+};
+
 struct RevNormParams {
     const float* vox; const float* e; const float* layerE;   // (B,Z,PR), (B), (B,Z+1) or nullptr
     float* out; float* energy_out;                          // (B,Z*PR), (B) or nullptr
@@ -44,6 +56,7 @@ void launch_prep_input(const Geom& g, const float* x, const float* sigma, int si
 void launch_prep_input_geom(const Geom& g, const GeomMap& enc, const float* x, const float* sigma, int sigma_stride,
                             float sigma_data, const float* r_vals, int rz_input, int phi_input, __half* dst, int out_chunks,
                             int B, cudaStream_t st);
+void launch_layer_mlp(const LayerMlpParams& m, const FinalParams& p, const float* cond, int B, int time_is_raw, cudaStream_t st);
 void launch_geom_apply(const GeomMap& m, const float* x, float* y, int B, cudaStream_t st);
 void launch_geom_decode(const FinalParams& p, const GeomMap& dec, const float* grid_pred, int B, cudaStream_t st);
 void launch_conv_generic(const ConvParams& p, cudaStream_t st);

@@ -79,6 +79,23 @@ int cd_version(void);
 int cd_device_check(void);
 
 cd_unet* cd_unet_create(const cd_unet_desc* desc);
+
+/* Layer-energy denoiser of LayerDiffusion (models/layerdiffusion.py:34-37 `layer_model = ResNet(dim_in = Z+1, num_layers = 5,
+ * cond_size)`, 111-114 `layer_forward`; ResNet / ResDense models/models.py:372-457): a dense residual MLP over (B, dim_in)
+ * vectors.  Returns the same handle type: cd_unet_set_weight (names "model.time_mlp.1.weight", "model.in_lay.weight",
+ * "model.hidden_layers.0.dense1.0.weight", ...), cd_unet_finalize, cd_unet_forward, cd_denoise, cd_sample_run and
+ * cd_unet_destroy apply unchanged, with voxels = dim_in and cond = E only (layerdiffusion.py:111-114). */
+typedef struct cd_layer_desc {
+    int dim_in;                  /* SHAPE_FINAL[2] + 1 (total energy + one value per layer), <= 64 */
+    int hidden;                  /* ResNet hidden_dim (256), <= 256 */
+    int num_layers;              /* ResNet num_layers (5): num_layers - 1 ResDense blocks, <= 9 */
+    int cond_size;               /* 1 (3 for HGCal) */
+    int cond_dim;                /* cond_emb_dim (128) */
+    int time_embed;              /* 0 = 'sigma', 1 = 'log' */
+    float sigma_data;
+    int max_batch;
+} cd_layer_desc;
+cd_unet* cd_layer_model_create(const cd_layer_desc* desc);
 void cd_unet_destroy(cd_unet* h);
 /* fp32 host tensor under its reference state-dict name (e.g. "model.downs.0.0.block1.proj.conv.weight") */
 int cd_unet_set_weight(cd_unet* h, const char* name, const float* host_data, const int64_t* shape, int ndim);
