@@ -298,6 +298,212 @@ __global__ void __launch_bounds__(256, 2) fa_ctx_kernel(Geom g, const __half* __
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// pass 1+2 in one ("online" softmax over the voxels): every warp keeps a running raw maximum per channel and rescales its
+// Ctx / S accumulators when it grows, so the separate max pass (one more read of x) disappears.  Each block writes its
+// partial (Ctx, S) together with the maximum they are relative to: part[b][blk] = {33 x 32 floats, 32 maxima};
+// fa_fold_online merges the blocks.  No atomics on global memory: the result is independent of block scheduling.
+constexpr int kPartFloats = 33 * 32 + 32;
+template <int KS>
+__global__ void __launch_bounds__(256, 2) fa_ctx_online_kernel(Geom g, const __half* __restrict__ x, const __half* __restrict__ wf,
+                                                               const float* __restrict__ wsum, const float* __restrict__ wb,
+                                                               const double* __restrict__ pn_stats, float pn_inv_count,
+                                                               float* __restrict__ part, int rows_per_block) {
+    constexpr int C = 16 * KS, STR = C * 2 + 16;
+    __shared__ __align__(16) unsigned char sw[64 * STR];     // rows 0..31 Wk', 32..63 Wv'
+    __shared__ float red[33 * 32];
+    __shared__ float wmax[kWarps][32];
+    const int b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int gq = lane >> 2, tq = lane & 3;
+    stage_w<KS>(wf + 32 * C, sw, 64);
+    for (int i = threadIdx.x; i < 33 * 32; i += 256) red[i] = 0.f;
+    __syncthreads();
+    const PnScal ps = pn_scalars(pn_stats, b, C, pn_inv_count);
+    const float a2 = ps.a * kLog2e;
+    float cv[2][2], mr[2][2], nk[2][2];     // this lane's channels: d (and e) = 16i + 8h + g
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int d = 16 * i + 8 * h + gq;
+            cv[i][h] = fmaf(ps.m, __ldg(wsum + 64 + d), __ldg(wb + 64 + d));
+            mr[i][h] = -INFINITY;
+            nk[i][h] = 0.f;
+        }
+    const uint32_t r0 = blockIdx.x * rows_per_block;
+    uint32_t r1 = r0 + rows_per_block;
+    if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const __half* xb = x + plcp_offset(g, 0, (long long)b * g.rows_per_sample);
+    const long long cs = g.chunk_stride * 8;
+    float acc[2][4][4], sacc[2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int f = 0; f < 4; ++f) acc[i][j][f] = 0.f;
+#pragma unroll
+        for (int f = 0; f < 4; ++f) sacc[i][f] = 0.f;
+    }
+    const uint32_t ones = gq == 0 ? 0x3C003C00u : 0u;
+    uint32_t xf[4][KS][2];
+    uint32_t base = r0 + warp * 32;
+    unsigned vmask = 0;
+    if (base < r1) {
+        vmask = group_mask(g, base, r1, lane);
+        if (vmask) load_x32<KS>(xb, cs, base, r1, lane, xf);
+    }
+    while (base < r1) {
+        const unsigned cm = vmask;
+        uint32_t ek[2][4][2], vt[2][4][2];
+        if (cm) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                uint32_t a[KS][4];
+#pragma unroll
+                for (int s = 0; s < KS; ++s) ldsm_a<KS>(sw, 16 * i, s, lane, a[s]);
+                float kr[4][4];
+                float gm0 = -INFINITY, gm1 = -INFINITY;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    kr[j][0] = kr[j][1] = kr[j][2] = kr[j][3] = 0.f;
+#pragma unroll
+                    for (int s = 0; s < KS; ++s) mma16816(kr[j], a[s], xf[j][s][0], xf[j][s][1]);
+                    const bool v0 = (cm >> (8 * j + 2 * tq)) & 1u, v1 = (cm >> (8 * j + 2 * tq + 1)) & 1u;
+                    if (v0) { gm0 = fmaxf(gm0, kr[j][0]); gm1 = fmaxf(gm1, kr[j][2]); }
+                    if (v1) { gm0 = fmaxf(gm0, kr[j][1]); gm1 = fmaxf(gm1, kr[j][3]); }
+                }
+                gm0 = fmaxf(gm0, __shfl_xor_sync(0xffffffffu, gm0, 1)); gm0 = fmaxf(gm0, __shfl_xor_sync(0xffffffffu, gm0, 2));
+                gm1 = fmaxf(gm1, __shfl_xor_sync(0xffffffffu, gm1, 1)); gm1 = fmaxf(gm1, __shfl_xor_sync(0xffffffffu, gm1, 2));
+                if (__any_sync(0xffffffffu, gm0 > mr[i][0] || gm1 > mr[i][1])) {
+                    // the maximum grew for some channel: bring this m tile's accumulators to the new reference
+                    const float n0 = fmaxf(mr[i][0], gm0), n1 = fmaxf(mr[i][1], gm1);
+                    const float f0 = mr[i][0] == -INFINITY ? 0.f : ex2f(a2 * (mr[i][0] - n0));
+                    const float f1 = mr[i][1] == -INFINITY ? 0.f : ex2f(a2 * (mr[i][1] - n1));
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) { acc[i][jj][0] *= f0; acc[i][jj][1] *= f0; acc[i][jj][2] *= f1; acc[i][jj][3] *= f1; }
+                    sacc[i][0] *= f0; sacc[i][1] *= f0; sacc[i][2] *= f1; sacc[i][3] *= f1;
+                    mr[i][0] = n0; mr[i][1] = n1;
+                    nk[i][0] = -a2 * n0; nk[i][1] = -a2 * n1;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t pm = pair_mask(cm, j, tq);
+                    ek[i][j][0] = pack_h2(ex2f(fmaf(a2, kr[j][0], nk[i][0])), ex2f(fmaf(a2, kr[j][1], nk[i][0]))) & pm;
+                    ek[i][j][1] = pack_h2(ex2f(fmaf(a2, kr[j][2], nk[i][1])), ex2f(fmaf(a2, kr[j][3], nk[i][1]))) & pm;
+                }
+#pragma unroll
+                for (int s = 0; s < KS; ++s) ldsm_a<KS>(sw, 32 + 16 * i, s, lane, a[s]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float c4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int s = 0; s < KS; ++s) mma16816(c4, a[s], xf[j][s][0], xf[j][s][1]);
+                    vt[i][j][0] = pack_h2(fmaf(ps.a, c4[0], cv[i][0]), fmaf(ps.a, c4[1], cv[i][0]));
+                    vt[i][j][1] = pack_h2(fmaf(ps.a, c4[2], cv[i][1]), fmaf(ps.a, c4[3], cv[i][1]));
+                }
+            }
+        }
+        base += kWarps * 32;
+        if (base < r1) {
+            vmask = group_mask(g, base, r1, lane);
+            if (vmask) load_x32<KS>(xb, cs, base, r1, lane, xf);
+        }
+        if (cm) {
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const uint32_t a[4] = {ek[i][2 * ks][0], ek[i][2 * ks][1], ek[i][2 * ks + 1][0], ek[i][2 * ks + 1][1]};
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj)
+                        mma16816(acc[i][jj], a, vt[jj >> 1][2 * ks][jj & 1], vt[jj >> 1][2 * ks + 1][jj & 1]);
+                    mma16816(sacc[i], a, ones, ones);
+                }
+        }
+    }
+    // block maximum per channel, then every warp rescales to it and adds into the block partial
+    if (tq == 0) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { wmax[warp][16 * i + gq] = mr[i][0]; wmax[warp][16 * i + 8 + gq] = mr[i][1]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        float f[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int d = 16 * i + 8 * h + gq;
+            float bm = wmax[0][d];
+#pragma unroll
+            for (int w = 1; w < kWarps; ++w) bm = fmaxf(bm, wmax[w][d]);
+            f[h] = mr[i][h] == -INFINITY ? 0.f : ex2f(a2 * (mr[i][h] - bm));
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int d0 = i * 16 + gq, e0 = j * 8 + 2 * tq;
+            atomicAdd(&red[d0 * 32 + e0], acc[i][j][0] * f[0]);
+            atomicAdd(&red[d0 * 32 + e0 + 1], acc[i][j][1] * f[0]);
+            atomicAdd(&red[(d0 + 8) * 32 + e0], acc[i][j][2] * f[1]);
+            atomicAdd(&red[(d0 + 8) * 32 + e0 + 1], acc[i][j][3] * f[1]);
+        }
+        if (tq == 0) {
+            atomicAdd(&red[32 * 32 + i * 16 + gq], sacc[i][0] * f[0]);
+            atomicAdd(&red[32 * 32 + i * 16 + gq + 8], sacc[i][2] * f[1]);
+        }
+    }
+    __syncthreads();
+    float* o = part + ((long long)b * gridDim.x + blockIdx.x) * kPartFloats;
+    for (int i = threadIdx.x; i < 33 * 32; i += 256) o[i] = red[i];
+    if (threadIdx.x < 32) {
+        float bm = wmax[0][threadIdx.x];
+#pragma unroll
+        for (int w = 1; w < kWarps; ++w) bm = fmaxf(bm, wmax[w][threadIdx.x]);
+        o[33 * 32 + threadIdx.x] = bm;
+    }
+}
+
+// merge the block partials of one sample and fold:  fold[c][d] = sum_e Wout[c][e] * Ctx[d][e] / S[d] * 32^-1/2
+__global__ void __launch_bounds__(256) fa_fold_online_kernel(const float* __restrict__ part, int nblk, const double* __restrict__ pn_stats,
+                                                             float pn_inv_count, int C, const float* __restrict__ wout /* [Cout][32] */,
+                                                             __half* __restrict__ fold, int CO) {
+    __shared__ float M[32][33];
+    __shared__ float wgt[32][32];      // [blk][d] weight of block blk for channel d (nblk <= 32)
+    __shared__ float S[32];
+    const int b = blockIdx.x;
+    const float a2 = pn_scalars(pn_stats, b, C, pn_inv_count).a * kLog2e;
+    const float* pb = part + (long long)b * nblk * kPartFloats;
+    if (threadIdx.x < 32) {
+        const int d = threadIdx.x;
+        float gm = -INFINITY;
+        for (int k = 0; k < nblk; ++k) gm = fmaxf(gm, pb[(long long)k * kPartFloats + 33 * 32 + d]);
+        float s = 0.f;
+        for (int k = 0; k < nblk; ++k) {
+            const float mk = pb[(long long)k * kPartFloats + 33 * 32 + d];
+            const float w = mk == -INFINITY ? 0.f : ex2f(a2 * (mk - gm));
+            wgt[k][d] = w;
+            s = fmaf(w, pb[(long long)k * kPartFloats + 32 * 32 + d], s);
+        }
+        S[d] = s;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 1024; i += 256) {
+        const int d = i >> 5, e = i & 31;
+        float c = 0.f;
+        for (int k = 0; k < nblk; ++k) c = fmaf(wgt[k][d], pb[(long long)k * kPartFloats + i], c);
+        M[d][e] = c / S[d] * 0.17677669529663687f;  // 32^-0.5
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < CO * 32; i += 256) {
+        const int co = i >> 5, d = i & 31;
+        float a = 0.f;
+#pragma unroll 8
+        for (int e = 0; e < 32; ++e) a = fmaf(__ldg(wout + co * 32 + e), M[d][e], a);
+        fold[(long long)b * CO * 32 + i] = __float2half_rn(a);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // once per sample: fold[c][d] = sum_e Wout[c][e] * Ctx[d][e] / S[d] * 32^-1/2   (second einsum + to_out conv as one 32 x Cout matrix)
 __global__ void __launch_bounds__(256) fa_fold_kernel(const float* __restrict__ ctx, const float* __restrict__ wout /* [Cout][32] */,
                                                       __half* __restrict__ fold, int CO) {
@@ -461,33 +667,42 @@ __global__ void __launch_bounds__(256, 2) fa_out_kernel(Geom g, const __half* __
 
 template <int KS>
 void launch_fused_t(const Geom& g, const __half* x, const __half* wf, const float* wsum, const float* wb, const double* pn_stats,
-                    float inv_count, unsigned* kmax, float* ctx, __half* fold, const float* wout, const float* bout, __half* dst,
-                    double* stats, int B, cudaStream_t st) {
+                    float inv_count, unsigned* kmax, float* ctx, float* part, __half* fold, const float* wout, const float* bout,
+                    __half* dst, double* stats, int B, cudaStream_t st) {
     int rows = 2048;
     while (rows > 512 && (long long)B * ((g.rows_per_sample + rows - 1) / rows) < 592) rows >>= 1;
+    // the online form merges at most kAttnMaxBlocks partials per sample
+    while ((g.rows_per_sample + rows - 1) / rows > kAttnMaxBlocks) rows += 32 * kWarps;
     const int nblk = (g.rows_per_sample + rows - 1) / rows;
     dim3 grid(nblk, B);
-    fa_kmax_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, kmax, rows);
-    fa_ctx_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, kmax, ctx, rows, nblk > 1 ? 1 : 0);
+    if (part) {
+        fa_ctx_online_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, part, rows);
+        fa_fold_online_kernel<<<B, 256, 0, st>>>(part, nblk, pn_stats, inv_count, 16 * KS, wout, fold, 16 * KS);
+    } else {
+        fa_kmax_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, kmax, rows);
+        fa_ctx_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, kmax, ctx, rows, nblk > 1 ? 1 : 0);
+        fa_fold_kernel<<<B, 256, 0, st>>>(ctx, wout, fold, 16 * KS);
+    }
     const int orows = 1024;
     dim3 ogrid((g.rows_per_sample + orows - 1) / orows, B);
-    fa_fold_kernel<<<B, 256, 0, st>>>(ctx, wout, fold, 16 * KS);
     fa_out_kernel<KS, 2 * KS><<<ogrid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, fold, bout, dst, stats, orows);
 }
 
 }  // namespace
 
 bool attention_fused_supported(int C) { return C == 32 || C == 64; }
+int attn_part_floats() { return kPartFloats; }
 
 // x: raw (un-normalised) C-channel PLCP input of the attention block; wf: fp16 [96][C] = to_qkv weight * diag(gamma);
 // wsum[96] = row sums of wf as fp16, wb[96] = W beta; pn_stats: GroupNorm(1,C) sums of x (channel-0 slot per sample).
-// kmax, ctx and stats must be zero on entry; fold is [B][C][32] fp16 scratch.  Returns 0 if launched (4 launches).
+// kmax, ctx and stats must be zero on entry; fold is [B][C][32] fp16 scratch; part (optional) is
+// [B][kAttnMaxBlocks][attn_part_floats()] floats and selects the online-softmax form (no max pass).  Returns 0 if launched.
 int launch_attention_fused(const Geom& g, const __half* x, const __half* wf, const float* wsum, const float* wb,
-                           const double* pn_stats, double pn_count, unsigned* kmax, float* ctx, __half* fold, const float* wout,
-                           const float* bout, __half* dst, int C, double* stats, int B, cudaStream_t st) {
+                           const double* pn_stats, double pn_count, unsigned* kmax, float* ctx, float* part, __half* fold,
+                           const float* wout, const float* bout, __half* dst, int C, double* stats, int B, cudaStream_t st) {
     const float inv = (float)(1.0 / pn_count);
-    if (C == 32) launch_fused_t<2>(g, x, wf, wsum, wb, pn_stats, inv, kmax, ctx, fold, wout, bout, dst, stats, B, st);
-    else if (C == 64) launch_fused_t<4>(g, x, wf, wsum, wb, pn_stats, inv, kmax, ctx, fold, wout, bout, dst, stats, B, st);
+    if (C == 32) launch_fused_t<2>(g, x, wf, wsum, wb, pn_stats, inv, kmax, ctx, part, fold, wout, bout, dst, stats, B, st);
+    else if (C == 64) launch_fused_t<4>(g, x, wf, wsum, wb, pn_stats, inv, kmax, ctx, part, fold, wout, bout, dst, stats, B, st);
     else return 1;
     return 0;
 }

@@ -82,6 +82,8 @@ struct cd_unet {
     bool dense = false;           // layer-energy ResNet (cd_layer_model_create) instead of the U-Net
     cd_layer_desc ld = {};
     LayerMlpParams lm = {};
+    int online_attention = 1;     // option "online_attention" 0: separate max pass + atomically merged context
+    float* attn_part = nullptr;   // [max_batch][kAttnMaxBlocks][attn_part_floats()] block partials of the online form (not zeroed)
     int no_fused_attention = 0;   // option "fused_attention" 0: materialise qkv (1x1x1 conv) and run the three-pass attention on it
     std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
@@ -527,7 +529,8 @@ struct Builder {
                 const Geom& g = hh->geom[level];
                 launch_attention_fused(g, hh->bufs[x].ptr, wf_h, pn_wsum, pn_wb, (const double*)(hh->scratch + s0 * r.B),
                                        (double)C * g.Z * g.P * g.R, (unsigned*)(hh->scratch + skm * r.B),
-                                       (float*)(hh->scratch + sctx * r.B), (__half*)(hh->scratch + sfold * r.B), wout, bout,
+                                       (float*)(hh->scratch + sctx * r.B), hh->online_attention ? hh->attn_part : nullptr,
+                                       (__half*)(hh->scratch + sfold * r.B), wout, bout,
                                        hh->bufs[xn].ptr, C, (double*)(hh->scratch + s1 * r.B), r.B, r.st);
                 hh->launches += 4;
                 return;
@@ -960,6 +963,11 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
         return 0;
     }
     if (!strcmp(key, "debug_sync")) { h->debug_sync = value; return 0; }
+    if (!strcmp(key, "online_attention")) {
+        h->online_attention = value ? 1 : 0;
+        if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
+        return 0;
+    }
     if (!strcmp(key, "fused_attention")) {
         h->no_fused_attention = value ? 0 : 1;
         if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
@@ -1004,6 +1012,10 @@ int cd_unet_finalize(cd_unet* h) {
         h->has_geom = true;
     }
     if (build_plan(h)) return 1;
+    if (!h->dense) {
+        h->attn_part = h->dalloc<float>((size_t)h->d.max_batch * kAttnMaxBlocks * attn_part_floats(), false);
+        if (!h->attn_part) return fail("out of device memory for the attention partials");
+    }
     size_t nv = (size_t)h->d.max_batch * h->voxels();
     for (int i = 0; i < CD_NUM_STATE_BUFS; ++i) {
         h->state[i] = h->dalloc<float>(nv, true);

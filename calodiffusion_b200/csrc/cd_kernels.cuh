@@ -71,8 +71,10 @@ bool attention_out_supported(int C);
 // PreNorm + to_qkv + attention + to_out without the qkv tensor (cd_attention_fused.cu); 4 launches; returns 0 if launched
 bool attention_fused_supported(int C);
 int launch_attention_fused(const Geom& g, const __half* x, const __half* wf, const float* wsum, const float* wb,
-                           const double* pn_stats, double pn_count, unsigned* kmax, float* ctx, __half* fold, const float* wout,
-                           const float* bout, __half* dst, int C, double* stats, int B, cudaStream_t st);
+                           const double* pn_stats, double pn_count, unsigned* kmax, float* ctx, float* part, __half* fold,
+                           const float* wout, const float* bout, __half* dst, int C, double* stats, int B, cudaStream_t st);
+constexpr int kAttnMaxBlocks = 32;   // block partials per sample merged by the online-softmax form
+int attn_part_floats();
 void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, const float* cond, float* addvec, int B,
                   cudaStream_t st);
 void launch_final(const FinalParams& p, int B, cudaStream_t st);

@@ -391,3 +391,23 @@ def test_fused_attention_matches_unfused(models, case):
     e1, e0, d = rel_l2(y1, c["gold"]["denoise_a"]), rel_l2(y0, c["gold"]["denoise_a"]), rel_l2(y1, y0)
     print(case, f"fused vs ref {e1:.2e}, unfused vs ref {e0:.2e}, fused vs unfused {d:.2e}")
     assert max(e1, e0) < TOL and d < TOL
+
+
+@pytest.mark.parametrize("case", ["ds2", "ds3"])
+def test_online_attention_matches_two_pass(models, case):
+    """Online-softmax context pass (running maximum, block partials merged per sample, no atomics) against the two-pass
+    form (separate max pass, option online_attention = 0); the online form must also be bit-reproducible run to run."""
+    m, c = models(case)
+    sig = torch.from_numpy(c["gold"]["denoise_b_sigma"])
+    x = (c["x"] * (1 + sig.view(-1, 1, 1, 1, 1) ** 2).sqrt()).cuda()
+    args = dict(E=c["E"].cuda(), sigma=sig.cuda().view(-1, 1, 1, 1, 1), layers=None if c["layers"] is None else c["layers"].cuda())
+    y1 = m.denoise(x, **args).cpu().numpy()
+    h = m._engine(c["B"])
+    try:
+        assert m._lib.cd_unet_set_option(h, b"online_attention", 0) == 0
+        y0 = m.denoise(x, **args).cpu().numpy()
+    finally:
+        m._lib.cd_unet_set_option(h, b"online_attention", 1)
+    e1, e0, d = rel_l2(y1, c["gold"]["denoise_b"]), rel_l2(y0, c["gold"]["denoise_b"]), rel_l2(y1, y0)
+    print(case, f"online vs ref {e1:.2e}, two-pass vs ref {e0:.2e}, online vs two-pass {d:.2e}")
+    assert max(e1, e0) < TOL and d < TOL
