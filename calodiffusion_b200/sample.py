@@ -173,3 +173,51 @@ class Euler(EDMAbstract):
 class Heun(EDMAbstract):
     """models/sample.py:792-821 — including its use of x_cur in d' (:820) and the unguarded last step."""
     order = 2
+
+
+def linear_multistep_coeff(order, t, i, j):
+    """utils/sampling.py:77-89: integral over [t_i, t_{i+1}] of the Lagrange basis polynomial of node t_{i-j} among
+    t_i .. t_{i-order+1}.  The reference calls scipy quad on this degree-(order-1) polynomial; an `order`-point
+    Gauss-Legendre rule integrates it exactly."""
+    if order - 1 > i:
+        raise ValueError(f"Order {order} too high for step {i}")
+    t = np.asarray(t, dtype=np.float64)
+    nodes, weights = np.polynomial.legendre.leggauss(max(int(order), 1))
+    half, mid = 0.5 * (t[i + 1] - t[i]), 0.5 * (t[i + 1] + t[i])
+    tau = half * nodes + mid
+    prod = np.ones_like(tau)
+    for k in range(order):
+        if k != j:
+            prod *= (tau - t[i - k]) / (t[i - j] - t[i - k])
+    return float(half * np.dot(weights, prod))
+
+
+class LMS(EDMAbstract):
+    """models/sample.py:729-768: linear multistep (SAMPLER_OPTIONS ORDER, default 4) over the Karras schedule; one
+    denoiser evaluation per step, no noise, returns empty xs / x0s like the reference.
+
+    The update needs up to ORDER stored derivatives, more operands than a `cd_eval` record carries, so the loop runs
+    on the host: each step is one `cd_denoise` call (the CUDA denoiser) plus the axpy on the device tensors."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        self.order = self.sample_config.get("ORDER", 4)
+
+    @torch.no_grad()
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        t_steps = self.setup(num_steps, sample_offset)
+        t64 = t_steps.double().numpy()
+        x_next = start.to(torch.float32) * float(t_steps[0])
+        B = start.shape[0]
+        ds = []
+        for i in range(len(t_steps) - 1):
+            t_hat = float(t_steps[i])
+            sigma = torch.full((B,), t_hat, dtype=torch.float32, device=x_next.device)
+            denoised = model.denoise(x_next, sigma=sigma, E=energy, layers=layers)
+            ds.append((x_next - denoised) / t_hat)
+            if len(ds) > self.order:
+                ds.pop(0)
+            cur_order = min(i + 1, self.order)
+            for j, d in enumerate(reversed(ds)):
+                x_next = x_next + linear_multistep_coeff(cur_order, t64, i, j) * d
+        return x_next, [], []

@@ -315,6 +315,44 @@ def sample_edm(model, start, E, layers, num_steps, order=1, noise_bank=None, las
     return x_next, xs, x0s
 
 
+def lms_coeff(order, t, i, j):
+    """utils/sampling.py:77-89 `linear_multistep_coeff`: integral over [t_i, t_{i+1}] of the Lagrange basis polynomial
+    of node t_{i-j} among t_i .. t_{i-order+1}.  The reference integrates with scipy quad (epsrel 1e-4); the integrand is
+    a polynomial of degree order-1, so an `order`-point Gauss-Legendre rule is exact."""
+    if order - 1 > i:
+        raise ValueError(f"Order {order} too high for step {i}")
+    t = np.asarray(t, dtype=np.float64)
+    nodes, weights = np.polynomial.legendre.leggauss(max(order, 1))
+    a, b = t[i], t[i + 1]
+    tau = 0.5 * (b - a) * nodes + 0.5 * (b + a)
+    prod = np.ones_like(tau)
+    for k in range(order):
+        if k == j:
+            continue
+        prod = prod * (tau - t[i - k]) / (t[i - j] - t[i - k])
+    return float(0.5 * (b - a) * np.dot(weights, prod))
+
+
+def sample_lms(model, start, E, layers, num_steps, order=4, sigma_min=0.002, sigma_max=80.0, rho=7):
+    """sample.py:729-768 `LMS.sampler`: linear multistep over the Karras schedule, one evaluation per step, no noise,
+    up to `order` stored derivatives d = (x - D)/t."""
+    t_steps = karras_steps(num_steps, sigma_min, sigma_max, rho)
+    dt = model.dtype
+    B = start.shape[0]
+    x_next = start.to(dt) * t_steps[0].to(dt)
+    ds = []
+    for i, t_cur in enumerate(t_steps[:-1]):
+        x_hat = x_next
+        denoised = model(x_hat, E, torch.full((B,), float(t_cur), dtype=dt), layers)
+        ds.append((x_hat - denoised) / t_cur.to(dt))
+        if len(ds) > order:
+            ds.pop(0)
+        cur_order = min(i + 1, order)
+        coeffs = [lms_coeff(cur_order, t_steps.numpy(), i, j) for j in range(cur_order)]
+        x_next = x_hat + sum(c * d for c, d in zip(coeffs, reversed(ds)))
+    return x_next, [], []
+
+
 # --------------------------------------------------------------------------------------------
 # deterministic synthetic weights (shared recipe; the product never calls this)
 # --------------------------------------------------------------------------------------------

@@ -252,6 +252,22 @@ def test_edm_sampling(models, name):
         assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL
 
 
+@pytest.mark.parametrize("order", [4, 2])
+def test_lms_sampling(models, order):
+    """LMS (models/sample.py:729-768) against the live reference's final showers (tests/golden/lms.npz)."""
+    import os
+    from conftest import GOLDEN
+    from calodiffusion_b200 import sample as S
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    m, c = models("ds2")
+    s = S.LMS(dict(c["cfg"], SAMPLER_OPTIONS={"ORDER": order}))
+    x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 6, 0, True)
+    assert xs == [] and x0s == []
+    e = rel_l2(x.cpu().numpy(), gold[f"LMS_order{order}_x"])
+    print(f"LMS order {order} final {e:.2e}")
+    assert e < TOL
+
+
 def test_hgcal_ddim(models):
     from calodiffusion_b200 import sample as S
     m, c = models("hgcal")

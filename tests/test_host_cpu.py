@@ -73,6 +73,9 @@ class _InterpretedModel:
     def __init__(self, oracle):
         self.o = oracle
 
+    def denoise(self, x, E=None, sigma=None, layers=None):
+        return self.o.denoise(x, E, sigma, layers)
+
     def run_program(self, start, E, layers, evals, start_scale, final_buf, noise_bank=None, seed=0, shower_offset=0,
                     n_rec_x=0, n_rec_x0=0):
         buf = [None] * 4
@@ -131,6 +134,24 @@ def test_edm_program_reproduces_reference(name):
         assert rel_l2(x.numpy(), c["gold"]["Euler_x"]) < 1e-4
     else:
         assert not np.isfinite(x.numpy()).all()  # reference defect reproduced
+
+
+@pytest.mark.parametrize("order", [4, 2])
+def test_lms_host_loop_reproduces_reference(order):
+    """The LMS class (host loop over model.denoise) with the oracle denoiser vs the live reference's LMS."""
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    model = _InterpretedModel(DenoiserOracle(c["cfg"], c["sd"]))
+    sampler = b200_utils.load_attr("sampler", "LMS")(dict(c["cfg"], SAMPLER_OPTIONS={"ORDER": order}))
+    assert sampler.order == order
+    with torch.no_grad():
+        x, xs, x0s = sampler(model, c["x"], c["E"], c["layers"], 6, 0, True)
+    assert xs == [] and x0s == []
+    assert rel_l2(x.numpy(), gold[f"LMS_order{order}_x"]) < 5e-5
+    with pytest.raises(ValueError):
+        b200_sample.linear_multistep_coeff(3, [3.0, 2.0, 1.0, 0.0], 1, 0)   # utils/sampling.py:78-79
 
 
 def test_no_cpu_fallback_without_gpu():

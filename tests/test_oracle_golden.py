@@ -3,7 +3,7 @@ import numpy as np
 import torch
 
 from conftest import load_case, noise_bank, rel_l2
-from oracle.unet_oracle import DenoiserOracle, cylindrical_conv, sample_ddim, sample_edm
+from oracle.unet_oracle import DenoiserOracle, cylindrical_conv, lms_coeff, sample_ddim, sample_edm, sample_lms
 
 TOL = 2e-5  # fp32 CPU vs fp32 CPU, different op order only
 
@@ -67,3 +67,33 @@ def test_hgcal_ddim_matches_reference():
         x, xs, x0s = sample_ddim(m, c["x"], c["E"], c["layers"], 2, 0.0, bank)
     assert rel_l2(torch.stack(x0s).numpy(), c["gold"]["DDim_x0s"]) < TOL
     assert rel_l2(x.numpy(), c["gold"]["DDim_x"]) < TOL
+
+
+def test_lms_matches_reference():
+    """tests/golden/lms.npz (oracle/make_golden_lms.py): the live reference's LMS, 6 steps, ORDER 4 (default) and 2."""
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    for order in (4, 2):
+        with torch.no_grad():
+            x, xs, x0s = sample_lms(m, c["x"], c["E"], c["layers"], 6, order)
+        assert xs == [] and x0s == []
+        assert rel_l2(x.numpy(), gold[f"LMS_order{order}_x"]) < 5e-5, order
+
+
+def test_lms_coefficients():
+    """Closed forms: order 1 is the step h; order 2 is Adams-Bashforth on a non-uniform grid; the basis sums to h."""
+    t = np.array([80.0, 30.0, 9.0, 2.0, 0.3, 0.0])
+    for i in range(1, 5):
+        h = t[i + 1] - t[i]
+        assert abs(lms_coeff(1, t, i, 0) - h) < 1e-12
+        hp = t[i] - t[i - 1]
+        assert abs(lms_coeff(2, t, i, 0) - (h + h * h / (2 * hp))) < 1e-10
+        assert abs(lms_coeff(2, t, i, 1) + h * h / (2 * hp)) < 1e-10
+    for order in (3, 4):
+        assert abs(sum(lms_coeff(order, t, 4, j) for j in range(order)) - (t[5] - t[4])) < 1e-10
+    import pytest
+    with pytest.raises(ValueError):
+        lms_coeff(3, t, 1, 0)
