@@ -132,14 +132,26 @@ class EDMAbstract(Sample):
             pre_b = float((t_hat ** 2 - t_cur ** 2).sqrt() * self.S_noise)
             h = t_next - t_hat
             ht = float(h / t_hat)
-            if pre_b != 0.0 and self.order == 2:
-                raise ValueError("Heun with NOISY_SAMPLE churn is not supported by the B200 backend yet")
+            if pre_b != 0.0 and self.order != 1:
+                raise ValueError("Heun / DPM2 with NOISY_SAMPLE churn is not supported by the B200 backend yet")
             common = dict(sigma=float(t_hat), x_in=cur, pre_a=1.0, pre_b=pre_b, pre_noise_index=i,
                           rec_x0=i if debug else -1)
             # NOTE: with churn the reference records the un-noised x_cur; records are taken only when pre_b == 0
             if self.order == 1 or (self.last_step_euler and float(t_next) == 0.0):
                 # x_next = x_hat + h*(x_hat - D)/t_hat
                 evals.append(_eval(**common, x_out=other, k=(-ht, 1.0 + ht, 0, 0, 0),
+                                   rec_x=i if debug else -1, rec_x_buf=cur))
+                cur, other = other, cur
+            elif self.order == "dpm2":
+                # sample.py:836-850: t_mid = sqrt(t_hat*t_next) (lerp in log sigma); x_2 = x_hat + d_cur*(t_mid - t_hat) -> buf3;
+                # x_next = x_hat + h*(x_2 - D_2)/t_mid.  t_next = 0: t_mid = 0, evaluation at sigma 0 and h/0 (reference)
+                t_mid = torch.as_tensor(t_hat).log().lerp(torch.as_tensor(t_next).log(), 0.5).exp()
+                r = float((t_mid - t_hat) / t_hat)
+                evals.append(_eval(**common, x_out=3, k=(-r, 1.0 + r, 0, 0, 0)))
+                with np.errstate(divide="ignore"):
+                    hm = float(np.float32(h) / np.float32(t_mid))
+                sig2 = float(t_mid) if float(t_mid) > 0.0 else 1e-30
+                evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=(-hm, hm, 1.0, 0, 0), a1=cur,
                                    rec_x=i if debug else -1, rec_x_buf=cur))
                 cur, other = other, cur
             else:
@@ -221,3 +233,33 @@ class LMS(EDMAbstract):
             for j, d in enumerate(reversed(ds)):
                 x_next = x_next + linear_multistep_coeff(cur_order, t64, i, j) * d
         return x_next, [], []
+
+
+class Restart(EDMAbstract):
+    """models/sample.py:853-955.  The restart branch is guarded by `index + 1 in self.restart_list.keys()` (:877) with an
+    int on the left; the default RESTART_LIST (and any list read from config.json) has string keys, so the reference never
+    restarts and every step is the Euler update x_hat + h*d_cur (:872-875) - that behaviour is what runs here, as the same
+    fused cd_eval program as `Euler`.  A RESTART_LIST whose int keys would fire the restart loop raises `ValueError`.
+    (The reference fills `xs` with the builtin `next` (:951); the per-step states are returned here instead.)"""
+    order = 1
+
+    def __init__(self, config):
+        super().__init__(config)
+        default_restart = {"0": [4, 1, 19.35, 40.79], "1": [4, 1, 1.09, 1.92], "2": [4, 4, 0.59, 1.09],
+                           "3": [4, 1, 0.30, 0.59], "4": [4, 4, 0.06, 0.30]}
+        self.restart_list = self.sample_config.get("RESTART_LIST", default_restart)
+        self.restart_gamma = self.sample_config.get("RESTART_GAMMA", 0.05)
+
+    @torch.no_grad()
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        n_steps = num_steps + 1 - sample_offset - 1
+        if any(isinstance(k, int) and not isinstance(k, bool) and 1 <= k <= n_steps for k in self.restart_list.keys()):
+            raise ValueError("Restart with an int-keyed RESTART_LIST (active restart loops) is not supported by the "
+                             "B200 backend")
+        return super().__call__(model, start, energy, layers, num_steps, sample_offset, debug)
+
+
+class DPM2(EDMAbstract):
+    """models/sample.py:824-850: midpoint (in log sigma) second-order step, two evaluations per step - including the
+    unguarded last step (t_mid = 0: the reference's final showers are non-finite; `last_step_euler` is the guarded form)."""
+    order = "dpm2"

@@ -304,6 +304,12 @@ def sample_edm(model, start, E, layers, num_steps, order=1, noise_bank=None, las
         h = t_next.to(dt) - t_hat
         if order == 1 or (last_step_euler and float(t_next) == 0.0):
             x_next = x_hat + h * d_cur
+        elif order == "dpm2":
+            # sample.py:836-850 DPM2: midpoint in log-sigma; t_next = 0 gives t_mid = 0 and a division by zero
+            t_mid = t_hat.log().lerp(t_next.to(dt).log(), 0.5).exp()
+            x_2 = x_hat + d_cur * (t_mid - t_hat)
+            den2 = model(x_2, E, torch.full((B,), float(t_mid), dtype=dt), layers)
+            x_next = x_hat + h * ((x_2 - den2) / t_mid)
         else:
             x_prime = x_hat + h * d_cur
             t_prime = t_hat + h

@@ -268,6 +268,50 @@ def test_lms_sampling(models, order):
     assert e < TOL
 
 
+def test_restart_sampling(models):
+    """Restart with the reference's default RESTART_LIST (never restarts, sample.py:877) vs the live reference."""
+    import os
+    from conftest import GOLDEN
+    from calodiffusion_b200 import sample as S
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    m, c = models("ds2")
+    s = S.Restart(c["cfg"])
+    s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 4)).cuda()
+    x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, True)
+    e0 = rel_l2(torch.stack(list(x0s)).cpu().numpy(), gold["Restart_x0s"])
+    e1 = rel_l2(x.cpu().numpy(), gold["Restart_x"])
+    print(f"Restart x0s {e0:.2e} final {e1:.2e}")
+    assert max(e0, e1) < TOL
+
+
+def test_dpm2_sampling(models):
+    """DPM2 (models/sample.py:824-850) vs the live reference: per-step x0 / states; the final showers are non-finite on
+    both sides (t_mid = 0 at the last step); the guarded form is finite and matches the oracle."""
+    import os
+    from conftest import GOLDEN
+    from calodiffusion_b200 import sample as S
+    from oracle.unet_oracle import DenoiserOracle, sample_edm
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    m, c = models("ds2")
+    s = S.DPM2(c["cfg"])
+    s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 4)).cuda()
+    x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, True)
+    e0 = rel_l2(torch.stack(list(x0s)).cpu().numpy(), gold["DPM2_x0s"])
+    e1 = rel_l2(torch.stack(list(xs)).cpu().numpy(), gold["DPM2_xs"])
+    print(f"DPM2 x0s {e0:.2e} xs {e1:.2e}")
+    assert max(e0, e1) < TOL
+    assert not np.isfinite(x.cpu().numpy()).all()
+    s.last_step_euler = True
+    xg, _, _ = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, False)
+    o = DenoiserOracle(c["cfg"], c["sd"])
+    with torch.no_grad():
+        xo, _, _ = sample_edm(o, c["x"], c["E"], c["layers"], 4, "dpm2", noise_bank(c["shape"], c["B"], 4),
+                              last_step_euler=True)
+    eg = rel_l2(xg.cpu().numpy(), xo.numpy())
+    print(f"DPM2 guarded final {eg:.2e}")
+    assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL
+
+
 def test_hgcal_ddim(models):
     from calodiffusion_b200 import sample as S
     m, c = models("hgcal")

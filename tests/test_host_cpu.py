@@ -154,6 +154,42 @@ def test_lms_host_loop_reproduces_reference(order):
         b200_sample.linear_multistep_coeff(3, [3.0, 2.0, 1.0, 0.0], 1, 0)   # utils/sampling.py:78-79
 
 
+def test_restart_program_reproduces_reference():
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    model = _InterpretedModel(DenoiserOracle(c["cfg"], c["sd"]))
+    sampler = b200_utils.load_attr("sampler", "Restart")(c["cfg"])
+    sampler.noise_bank = noise_bank(c["shape"], c["B"], 4)
+    with torch.no_grad():
+        x, xs, x0s = sampler(model, c["x"], c["E"], c["layers"], 4, 0, True)
+    assert rel_l2(torch.stack(x0s).numpy(), gold["Restart_x0s"]) < 1e-4
+    assert rel_l2(x.numpy(), gold["Restart_x"]) < 1e-4
+    active = b200_sample.Restart(dict(c["cfg"], SAMPLER_OPTIONS={"RESTART_LIST": {1: [4, 1, 19.35, 40.79]}}))
+    with pytest.raises(ValueError):
+        active(model, c["x"], c["E"], c["layers"], 4, 0, False)
+
+
+def test_dpm2_program_reproduces_reference():
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    model = _InterpretedModel(DenoiserOracle(c["cfg"], c["sd"]))
+    sampler = b200_utils.load_attr("sampler", "DPM2")(c["cfg"])
+    sampler.noise_bank = noise_bank(c["shape"], c["B"], 4)
+    with torch.no_grad():
+        x, xs, x0s = sampler(model, c["x"], c["E"], c["layers"], 4, 0, True)
+    assert rel_l2(torch.stack(x0s).numpy(), gold["DPM2_x0s"]) < 1e-4
+    assert rel_l2(torch.stack(xs).numpy(), gold["DPM2_xs"]) < 1e-4
+    assert not np.isfinite(x.numpy()).all()  # reference defect reproduced: last step divides by t_mid = 0
+    sampler.last_step_euler = True
+    with torch.no_grad():
+        xg, _, _ = sampler(model, c["x"], c["E"], c["layers"], 4, 0, False)
+    assert np.isfinite(xg.numpy()).all()
+
+
 def test_no_cpu_fallback_without_gpu():
     if torch.cuda.is_available():
         pytest.skip("GPU present")

@@ -97,3 +97,31 @@ def test_lms_coefficients():
     import pytest
     with pytest.raises(ValueError):
         lms_coeff(3, t, 1, 0)
+
+
+def test_restart_default_is_euler():
+    """The live reference's Restart with its default (string-keyed) RESTART_LIST never restarts (sample.py:877): its
+    showers are the Euler loop's."""
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    with torch.no_grad():
+        x, xs, x0s = sample_edm(m, c["x"], c["E"], c["layers"], 4, 1, noise_bank(c["shape"], c["B"], 4))
+    assert rel_l2(torch.stack(x0s).numpy(), gold["Restart_x0s"]) < 5e-5
+    assert rel_l2(x.numpy(), gold["Restart_x"]) < 5e-5
+
+
+def test_dpm2_matches_reference():
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    with torch.no_grad():
+        x, xs, x0s = sample_edm(m, c["x"], c["E"], c["layers"], 4, "dpm2", noise_bank(c["shape"], c["B"], 4))
+    assert rel_l2(torch.stack(x0s).numpy(), gold["DPM2_x0s"]) < 5e-5
+    assert rel_l2(torch.stack(xs).numpy(), gold["DPM2_xs"]) < 5e-5
+    # reference defect: the last step's t_mid is 0
+    assert not np.isfinite(gold["DPM2_x"]).all() and not np.isfinite(x.numpy()).all()
