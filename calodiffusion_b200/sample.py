@@ -263,3 +263,40 @@ class DPM2(EDMAbstract):
     """models/sample.py:824-850: midpoint (in log sigma) second-order step, two evaluations per step - including the
     unguarded last step (t_mid = 0: the reference's final showers are non-finite; `last_step_euler` is the guarded form)."""
     order = "dpm2"
+
+
+class Consistency(Sample):
+    """models/sample.py:957-1011 + utils/sampling.py:1143-1172 (`sample_consis`): x0 prediction at up to five hard-coded
+    levels of the CONSIS_NSTEPS cosine schedule, re-noised to the next level (x = x0 + sqrt(s_next^2 - s_min^2)*noise) in
+    between.  Returns `(x, xs, last x0)` like the reference (the third item is a tensor there, not a list)."""
+    sigma_min = 0.002
+
+    def __init__(self, config):
+        super().__init__(config)
+        self.consis_nsteps = self.config.get("CONSIS_NSTEPS", 100)
+
+    @torch.no_grad()
+    def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        n = self.consis_nsteps
+        alphas_cumprod = torch.cumprod(1.0 - cosine_beta_schedule(n), dim=0)
+        sqrt_ac, sqrt_1m = torch.sqrt(alphas_cumprod), torch.sqrt(1.0 - alphas_cumprod)
+        t_all = [sqrt_1m[n - t - 1] / sqrt_ac[n - t - 1] for t in range(n)]
+        sample_idxs = [0] + [int(round(n * f)) for f in (0.5, 0.7, 0.9, 0.95)]
+        t_steps = torch.stack([t_all[i] for i in sample_idxs[:num_steps]]) if num_steps > 1 else torch.stack([t_all[0]])
+        sigmas = torch.cat([t_steps, torch.zeros_like(t_steps[:1])])
+        evals, draws = [], 0
+        last = len(sigmas) - 2
+        for i in range(len(sigmas) - 1):
+            sigma_next = torch.clip(sigmas[i + 1], self.sigma_min, None)
+            rec = dict(rec_x0=0 if i == last else -1, rec_x=i if debug else -1, rec_x_buf=0)
+            if sigma_next > self.sigma_min:
+                ns = float(torch.sqrt(sigma_next ** 2 - self.sigma_min ** 2))
+                evals.append(_eval(sigma=float(sigmas[i]), x_in=0, x_out=0, k=(1.0, 0, ns, 0, 0), a1=-2,
+                                   noise_index=draws, **rec))
+                draws += 1
+            else:
+                evals.append(_eval(sigma=float(sigmas[i]), x_in=0, x_out=0, k=(1.0, 0, 0, 0, 0), **rec))
+        x, xs, x0s = model.run_program(start, energy, layers, evals, float(sigmas[0]), 0, noise_bank=self.noise_bank,
+                                       seed=self._seed(), shower_offset=self.shower_offset,
+                                       n_rec_x=len(evals) if debug else 0, n_rec_x0=1)
+        return x, (xs if debug else []), x0s[0]

@@ -359,6 +359,33 @@ def sample_lms(model, start, E, layers, num_steps, order=4, sigma_min=0.002, sig
     return x_next, [], []
 
 
+def sample_consistency(model, start, E, layers, num_steps, consis_nsteps=100, noise_bank=None, sigma_min=0.002):
+    """sample.py:969-1011 `Consistency.__call__` + utils/sampling.py:1143-1172 `sample_consis`: x0 prediction at up to
+    five hard-coded noise levels of the `consis_nsteps` cosine schedule, re-noised to the next level in between.
+    Returns (x, xs, last x0) like the reference."""
+    ac = cosine_alphas_cumprod(consis_nsteps)
+    s1m, sac = torch.sqrt(1.0 - ac), torch.sqrt(ac)
+    t_all = [s1m[consis_nsteps - t - 1] / sac[consis_nsteps - t - 1] for t in range(consis_nsteps)]
+    idxs = [0] + [int(round(consis_nsteps * f)) for f in (0.5, 0.7, 0.9, 0.95)]
+    t_steps = torch.stack([t_all[i] for i in idxs[:num_steps]]) if num_steps > 1 else torch.stack([t_all[0]])
+    sigmas = torch.cat([t_steps, torch.zeros_like(t_steps[:1])])
+    dt = model.dtype
+    B = start.shape[0]
+    x = start.to(dt) * sigmas[0].to(dt)
+    xs, x0, draws = [], None, 0
+    for sigma_cur, sigma_next in zip(sigmas[:-1], sigmas[1:]):
+        x0 = model(x, E, torch.full((B,), float(sigma_cur), dtype=dt), layers)
+        sigma_next = torch.clip(sigma_next, sigma_min, None)
+        if sigma_next > sigma_min:
+            noise = noise_bank[draws].to(dt) if noise_bank is not None else torch.randn(x.shape, dtype=dt)
+            draws += 1
+            x = x0 + noise * torch.sqrt(sigma_next ** 2 - sigma_min ** 2).to(dt)
+        else:
+            x = x0
+        xs.append(x)
+    return x, xs, x0
+
+
 # --------------------------------------------------------------------------------------------
 # deterministic synthetic weights (shared recipe; the product never calls this)
 # --------------------------------------------------------------------------------------------

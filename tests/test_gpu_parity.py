@@ -312,6 +312,23 @@ def test_dpm2_sampling(models):
     assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL
 
 
+def test_consistency_sampling(models):
+    """Consistency (models/sample.py:957-1011, utils/sampling.py:1143-1172) vs the live reference, 5 levels."""
+    import os
+    from conftest import GOLDEN
+    from calodiffusion_b200 import sample as S
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    m, c = models("ds2")
+    s = S.Consistency(c["cfg"])
+    s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 5)).cuda()
+    x, xs, x0 = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 5, 0, True)
+    e0 = rel_l2(torch.stack(list(xs)).cpu().numpy(), gold["Consistency_xs"])
+    e1 = rel_l2(x0.cpu().numpy(), gold["Consistency_x0_last"])
+    e2 = rel_l2(x.cpu().numpy(), gold["Consistency_x"])
+    print(f"Consistency xs {e0:.2e} x0 {e1:.2e} final {e2:.2e}")
+    assert max(e0, e1, e2) < TOL
+
+
 def test_hgcal_ddim(models):
     from calodiffusion_b200 import sample as S
     m, c = models("hgcal")

@@ -190,6 +190,29 @@ def test_dpm2_program_reproduces_reference():
     assert np.isfinite(xg.numpy()).all()
 
 
+@pytest.mark.parametrize("steps", [5, 1])
+def test_consistency_program_reproduces_reference(steps):
+    import os
+    from conftest import GOLDEN
+    from oracle.unet_oracle import sample_consistency
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    o = DenoiserOracle(c["cfg"], c["sd"])
+    sampler = b200_utils.load_attr("sampler", "Consistency")(c["cfg"])
+    sampler.noise_bank = noise_bank(c["shape"], c["B"], 5)
+    with torch.no_grad():
+        x, xs, x0 = sampler(_InterpretedModel(o), c["x"], c["E"], c["layers"], steps, 0, True)
+    assert len(xs) == steps
+    if steps == 5:
+        assert rel_l2(torch.stack(xs).numpy(), gold["Consistency_xs"]) < 1e-4
+        assert rel_l2(x0.numpy(), gold["Consistency_x0_last"]) < 1e-4
+        assert rel_l2(x.numpy(), gold["Consistency_x"]) < 1e-4
+    else:   # single step: x = x0 at the top noise level, no draw
+        with torch.no_grad():
+            xo, _, _ = sample_consistency(o, c["x"], c["E"], c["layers"], 1, 100, None)
+        assert rel_l2(x.numpy(), xo.numpy()) < 1e-4 and torch.equal(x, x0)
+
+
 def test_no_cpu_fallback_without_gpu():
     if torch.cuda.is_available():
         pytest.skip("GPU present")

@@ -3,7 +3,7 @@ import numpy as np
 import torch
 
 from conftest import load_case, noise_bank, rel_l2
-from oracle.unet_oracle import DenoiserOracle, cylindrical_conv, lms_coeff, sample_ddim, sample_edm, sample_lms
+from oracle.unet_oracle import DenoiserOracle, cylindrical_conv, lms_coeff, sample_consistency, sample_ddim, sample_edm, sample_lms
 
 TOL = 2e-5  # fp32 CPU vs fp32 CPU, different op order only
 
@@ -125,3 +125,16 @@ def test_dpm2_matches_reference():
     assert rel_l2(torch.stack(xs).numpy(), gold["DPM2_xs"]) < 5e-5
     # reference defect: the last step's t_mid is 0
     assert not np.isfinite(gold["DPM2_x"]).all() and not np.isfinite(x.numpy()).all()
+
+
+def test_consistency_matches_reference():
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "lms.npz"))
+    c = load_case("ds2")
+    m = DenoiserOracle(c["cfg"], c["sd"])
+    with torch.no_grad():
+        x, xs, x0 = sample_consistency(m, c["x"], c["E"], c["layers"], 5, 100, noise_bank(c["shape"], c["B"], 5))
+    assert rel_l2(torch.stack(xs).numpy(), gold["Consistency_xs"]) < 5e-5
+    assert rel_l2(x0.numpy(), gold["Consistency_x0_last"]) < 5e-5
+    assert rel_l2(x.numpy(), gold["Consistency_x"]) < 5e-5
