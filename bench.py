@@ -117,8 +117,89 @@ def _binning(wl, cfg):
     return meta
 
 
-def cpu_reference_leg(wl, budget_s=12.0, batch=16):
-    """The reference's CPU algorithm for the path (oracle port: plain torch CPU fp32 ops, all host threads) on a
+HGCAL_REF_OVERRIDES = {  # the reference's pytest hgcal fixture (tests/test_execution.py:178-190)
+    "HGCAL": True, "SHAPE_ORIG": [-1, 28, 1988], "DATASET_NUM": 111, "SHAPE_PAD": [-1, 1, 28, 12, 21],
+    "SHAPE_FINAL": [-1, 1, 28, 12, 21], "MAX_CELLS": 1988, "LAYER_SIZE_UNET": [32, 32, 64, 96],
+    "SHOWER_EMBED": "NN-pre-embed",
+}
+REF_CONFIGS = {"ds2": ("config_dataset2.json", None), "ds3": ("config_dataset3.json", None),
+               "hgcal": ("config_HGCal.json", HGCAL_REF_OVERRIDES),
+               "ds1": ("config_dataset1_photon.json", {"BIN_FILE": "{REF_ROOT}/CaloChallenge/code/binning_dataset_1_photons.xml"})}
+
+
+def config_block(wl, B, steps, world):
+    """The `config` object of the JSON line: identical on both arms (the driver compares them)."""
+    evals = wl["evals_per_shower"] * steps / wl["steps"]
+    return {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
+            "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
+            "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
+            "weights": "random init (seed 0)"}
+
+
+def reference_leg(key, budget_s=10.0, batch=None):
+    """The UNMODIFIED reference (`oracle/_ref`, staged by oracle/build_ref.sh) timed through its own public API,
+    `CaloDiffusion.sample` (models/diffusion.py:77-104) with its own sampler classes, on whatever device its
+    `utils.get_device()` picks (the host cores when CUDA is hidden, else the GPU with torch/cuDNN eager defaults),
+    on a bounded sample of the workload: the last n steps of the real schedule (`sample_offset`) at a reduced batch.
+    Returns dict(value showers/s, cores, kind, sample, device, ms_per_eval)."""
+    import torch
+    from oracle import ref_shim
+    wl = WORKLOADS[key]
+    if not ref_shim.available():
+        v, cores, sample, _ = port_leg(wl, budget_s=budget_s)
+        return dict(value=v, cores=cores, kind="port", sample=sample, device="cpu", ms_per_eval=None)
+    cfg_name, overrides = REF_CONFIGS[key]
+    overrides = {k: (v.format(REF_ROOT=ref_shim.REF_ROOT) if isinstance(v, str) else v) for k, v in (overrides or {}).items()}
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model, cfg = ref_shim.load_reference_model(cfg_name, wl["sampler"], overrides)
+    on_gpu = model.device.type == "cuda"
+    B = int(batch or (wl["batch"] if on_gpu else 16))
+    g = torch.Generator().manual_seed(1)
+    E = torch.rand(B, wl.get("cond_e", 1), generator=g).to(model.device)
+    layers = torch.randn(B, wl["n_layers"], generator=g).to(model.device) if wl["n_layers"] else None
+    per_step = 2 if wl["sampler"] == "Heun" else 1      # denoiser evaluations per sampler step
+
+    def run(n):   # n sampler steps at the tail of the real schedule
+        t0 = time.perf_counter()
+        out = model.sample(E, layers, num_steps=wl["steps"], sample_offset=wl["steps"] - n)
+        if on_gpu:
+            torch.cuda.synchronize()
+        assert out.shape[0] == B
+        return time.perf_counter() - t0
+
+    run(1)                                                # warm-up (thread pool / cuDNN autotune / allocator)
+    evals_done, t_total, n = 0, 0.0, 1
+    while t_total < budget_s and evals_done < 4096:
+        t_total += run(n)
+        evals_done += n * per_step
+        n = min(n * 2, 16 if on_gpu else 8)
+    value = B * evals_done / t_total / wl["evals_per_shower"]
+    sample = (f"unmodified reference CaloDiffusion.sample + {wl['sampler']} on {model.device.type}: {evals_done} denoiser "
+              f"evaluations (tail of the {wl['steps']}-step schedule via sample_offset) at batch {B} in {t_total:.1f} s, "
+              f"scaled to {wl['evals_per_shower']} evaluations per shower")
+    return dict(value=value, cores=cores, kind="reference", sample=sample, device=model.device.type,
+                ms_per_eval=1e3 * t_total / evals_done, batch=B)
+
+
+def reference_leg_subprocess(key, device, budget_s=10.0, timeout=900):
+    """Run `reference_leg` in a fresh interpreter (CUDA hidden for the CPU leg) and parse its JSON line."""
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE"):
+        env.pop(k, None)
+    if device == "cpu":
+        env["CUDA_VISIBLE_DEVICES"] = ""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference-leg", "--workload", key, "--budget", str(budget_s)]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=ROOT)
+    for ln in reversed(out.stdout.strip().splitlines()):
+        if ln.startswith("{"):
+            return json.loads(ln)
+    raise RuntimeError("reference leg failed: " + out.stderr[-2000:])
+
+
+def port_leg(wl, budget_s=12.0, batch=16):
+    """Fallback when oracle/_ref is absent: the oracle port (plain torch CPU fp32 ops, all host threads) on a
     bounded sample of the same workload.  Returns (showers_per_s, cores, sample description, seconds)."""
     import torch
     from oracle.unet_oracle import DenoiserOracle, sample_ddim, sample_edm, synth_state_dict
@@ -171,28 +252,30 @@ def cpu_reference_leg(wl, budget_s=12.0, batch=16):
 
 
 def run_reference_arm(args, wl):
-    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    """--impl reference: the reference's own implementation of the path on the host cores (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    vals, sample, cores = [], "", 1
+    B, steps = int(args.batch or wl["batch"]), int(args.sampling_steps or wl["steps"])
+    vals, last = [], None
     for _ in range(max(args.warmup, 0)):
-        cpu_reference_leg(wl, budget_s=2.0)
+        reference_leg(args.workload, budget_s=2.0)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        v, cores, sample, _ = cpu_reference_leg(wl, budget_s=10.0)
-        vals.append(v)
+        last = reference_leg(args.workload, budget_s=args.budget)
+        vals.append(last["value"])
     dt = time.perf_counter() - t0
     v = sum(vals) / len(vals)
     line = {
         "impl": "reference", "metric": "showers/sec sampled", "value": v, "unit": "showers/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "batch_per_gpu": wl["batch"], "sampler": wl["sampler"],
-                   "sampling_steps": wl["steps"], "note": "each step = a bounded sample of the workload on the host CPU"},
-        "cpu_baseline": {"value": v, "unit": "showers/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": config_block(wl, B, steps, args.gpus),
+        "cpu_baseline": {"value": v, "unit": "showers/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"],
+                         "device": last["device"]},
         "e2e": {"value": v, "unit": "showers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "note": "each step = a bounded sample of the workload (see cpu_baseline.sample) on the host CPU, CUDA hidden",
     }
     print(json.dumps(line), flush=True)
 
@@ -358,25 +441,31 @@ def run_gpu_arm(args, wl):
         rep = _op_profile(model, start_dev, E_dev, L_dev, sig)
         roof, roof_hbm, table, eval_ms = _roofline(rep, peaks, B, args.workload)
         reps = 3
-        cpu = None
+        cpu = gpu_ref = None
         if world == 1 and not args.no_cpu_baseline:
-            v, cores, sample, _ = cpu_reference_leg(wl, budget_s=12.0)
-            cpu = {"value": v, "unit": "showers/s", "cores": cores, "kind": "port", "sample": sample}
+            # the unmodified reference (oracle/_ref) in fresh interpreters: on the host cores (CUDA hidden), and eager on
+            # this same B200 with torch/cuDNN defaults (TF32 convolutions) - SURVEY 8(d) "GPU reference baseline"
+            r = reference_leg_subprocess(args.workload, "cpu", budget_s=12.0)
+            cpu = {"value": r["value"], "unit": "showers/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+            try:
+                r = reference_leg_subprocess(args.workload, "cuda", budget_s=6.0)
+                gpu_ref = {"value": r["value"], "unit": "showers/s", "ms_per_eval": r["ms_per_eval"], "batch": r.get("batch"),
+                           "kind": r["kind"], "device": r["device"], "sample": r["sample"]}
+            except Exception as exc:   # reported, never fatal: this leg is context for the headline, not the headline
+                gpu_ref = {"unavailable": str(exc)[-300:]}
         evals = wl["evals_per_shower"] * steps / wl["steps"]
         line = {
             "metric": "showers/sec sampled", "value": value, "unit": "showers/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
-                       "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
-                       "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
-                       "weights": "random init (seed 0)"},
+            "config": config_block(wl, B, steps, world),
             "e2e": {"value": e2e, "unit": "showers/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
             "roofline_hbm": roof_hbm,
             "cpu_baseline": cpu,
+            "gpu_reference": gpu_ref,
             "shower_evals_per_s": value * evals,
             "model_tflops": value * evals * wl["gflop_per_eval"] / 1e3,
             "eval_ms_profiled": eval_ms / reps,
@@ -394,14 +483,19 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-leg"])
+    ap.add_argument("--budget", type=float, default=10.0, help="seconds of reference work per step (--impl reference)")
     ap.add_argument("--workload", default="ds2", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="override showers per GPU (diagnostics only)")
     ap.add_argument("--sampling-steps", type=int, default=0, help="override sampler steps (diagnostics only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
     if args.impl == "reference":
+        os.environ["CUDA_VISIBLE_DEVICES"] = ""      # the reference picks cuda when it sees one (utils.get_device)
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference-leg":      # internal: one bounded reference measurement on the visible device
+        print(json.dumps(reference_leg(args.workload, budget_s=args.budget)), flush=True)
+    elif args.impl == "reference":
         run_reference_arm(args, wl)
     else:
         run_gpu_arm(args, wl)

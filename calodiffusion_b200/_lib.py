@@ -41,6 +41,7 @@ class Eval(C.Structure):
         ("noise_index", C.c_int),
         ("pre_a", C.c_float), ("pre_b", C.c_float), ("pre_noise_index", C.c_int),
         ("rec_x0", C.c_int), ("rec_x", C.c_int), ("rec_x_buf", C.c_int),
+        ("pre_src", C.c_int), ("d_out", C.c_int), ("d_scale", C.c_float),
     ]
 
 

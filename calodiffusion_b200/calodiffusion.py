@@ -172,6 +172,7 @@ class CaloDiffusion(Diffusion):
             self._voxels = int(np.prod(self._data_shape))
         self.use_graph = True
         self.conv_backend = 0
+        self.check_finite = True
 
     # ------------------------------------------------------------------ contract
     def init_model(self):
@@ -268,6 +269,7 @@ class CaloDiffusion(Diffusion):
                     _lib.check(lib.cd_unet_set_geom_map(h, which, m["n_rows"], m["n_cols"], m["rowptr"].ctypes.data,
                                                         m["col"].ctypes.data, m["val"].ctypes.data), "set_geom_map")
             _lib.check(lib.cd_unet_set_option(h, b"conv_backend", int(self.conv_backend)), "set_option")
+            _lib.check(lib.cd_unet_set_option(h, b"check_finite", int(self.check_finite)), "set_option")
             _lib.check(lib.cd_unet_finalize(h), "finalize")
             if int(lib.cd_unet_voxels(h)) != self._voxels:
                 raise RuntimeError(f"engine works on {int(lib.cd_unet_voxels(h))} voxels per shower, host expects {self._voxels}")
@@ -289,6 +291,13 @@ class CaloDiffusion(Diffusion):
         self.conv_backend = int(backend)
         if self._handle is not None:
             _lib.check(self._lib.cd_unet_set_option(self._handle, b"conv_backend", self.conv_backend), "set_option")
+
+    def set_check_finite(self, on=True):
+        """True (default): `run_program` raises RuntimeError when a denoiser evaluation produced non-finite output (activations
+        left the fp16 range, |c_in*x| >= 65504); False: the non-finite showers are returned, as the reference would."""
+        self.check_finite = bool(on)
+        if self._handle is not None:
+            _lib.check(self._lib.cd_unet_set_option(self._handle, b"check_finite", int(self.check_finite)), "set_option")
 
     def launch_count(self):
         return int(self._lib.cd_unet_launch_count(self._handle)) if self._handle else 0

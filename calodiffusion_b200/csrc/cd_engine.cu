@@ -60,6 +60,8 @@ struct Run {  // per-call state
 
 struct Buf { int level, C; __half* ptr; bool busy; };
 
+constexpr int kRow = 12;   // floats per sampler coefficient-table row: sigma, k0..k4, pre_a, pre_b, d_scale, 3 spare
+
 struct OpInfo { std::string name; double flops, bytes; };          // per shower
 struct ProfAcc { long long count = 0; double ms = 0, flops = 0, bytes = 0; };
 
@@ -110,9 +112,12 @@ struct cd_unet {
     float* grid_pred = nullptr;   // (max_batch, Z*P*R) raw network output before decoding
     int voxels() const { return has_geom ? geom_map[1].n_rows : d.Z * d.P * d.R; }
     // sampling state
-    float* state[CD_NUM_STATE_BUFS] = {nullptr, nullptr, nullptr, nullptr};
-    float* coef_tab = nullptr;  // [max_evals][8]
+    float* state[CD_NUM_STATE_BUFS] = {};
+    float* coef_tab = nullptr;  // [max_evals][kRow]; row n_evals: {start_scale, 0, seed lo, seed hi, shower_offset, ...} (raw bits)
     int coef_cap = 0;
+    int* fault = nullptr;       // device word: first evaluation whose raw network output was non-finite (INT_MAX: none)
+    int* fault_host = nullptr;  // pinned mirror
+    int check_finite = 1;       // option "check_finite": cd_sample_run reads the fault word back and fails on a fault
     float* unit_sigma = nullptr;
     // graph cache
     cudaGraphExec_t graph_exec = nullptr;
@@ -914,6 +919,7 @@ void cd_unet_destroy(cd_unet* h) {
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->capture_stream) cudaStreamDestroy(h->capture_stream);
     for (cudaEvent_t ev : h->prof_evs) cudaEventDestroy(ev);
+    if (h->fault_host) cudaFreeHost(h->fault_host);
     for (void* p : h->dev_allocs) cudaFree(p);
     delete h;
 }
@@ -963,6 +969,7 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
         return 0;
     }
     if (!strcmp(key, "debug_sync")) { h->debug_sync = value; return 0; }
+    if (!strcmp(key, "check_finite")) { h->check_finite = value ? 1 : 0; return 0; }
     if (!strcmp(key, "online_attention")) {
         h->online_attention = value ? 1 : 0;
         if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_key.clear(); }
@@ -1022,7 +1029,10 @@ int cd_unet_finalize(cd_unet* h) {
         if (!h->state[i]) return fail("out of device memory for sampler state");
     }
     h->coef_cap = 4096;
-    h->coef_tab = h->dalloc<float>((size_t)h->coef_cap * 8, true);
+    h->coef_tab = h->dalloc<float>((size_t)h->coef_cap * kRow, true);
+    h->fault = h->dalloc<int>(1, true);
+    if (!h->coef_tab || !h->fault || cudaMallocHost((void**)&h->fault_host, sizeof(int)) != cudaSuccess)
+        return fail("out of memory for the sampler tables");
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return fail("finalize: %s", cudaGetErrorString(e));
     for (auto& b : h->bufs) if (!b.ptr) return fail("out of device memory for activations");
@@ -1136,15 +1146,25 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
     const long long n = (long long)a.B * V;
     const size_t bytes = (size_t)n * sizeof(float);
     float* tab = h->coef_tab;
+    // Philox key {seed lo, seed hi, shower_offset}: device-resident (row n_evals, slots 2..4) so the graph does not bake it
+    const uint32_t* rng_key = reinterpret_cast<const uint32_t*>(tab + (size_t)a.n_evals * kRow + 2);
     // buf[0] = start * start_scale  (row n_evals of the table holds [start_scale, 0])
-    launch_axpby(a.start, nullptr, h->state[0], tab + (size_t)a.n_evals * 8, n, V, a.seed, a.shower_offset, 0, 0, st);
+    launch_axpby(a.start, nullptr, h->state[0], tab + (size_t)a.n_evals * kRow, n, V, a.seed, a.shower_offset, 0, 0, st);
     h->launches += 1;
     for (int i = 0; i < a.n_evals; ++i) {
         const cd_eval& e = a.evals[i];
-        float* row = tab + (size_t)i * 8;
-        if (e.pre_b != 0.f) {
+        float* row = tab + (size_t)i * kRow;
+        bool recorded_x = false;
+        if (e.pre_b != 0.f || e.pre_src >= 0) {
+            const int src = e.pre_src >= 0 ? e.pre_src : e.x_in;
+            if (e.rec_x >= 0 && a.xs && e.rec_x_buf == e.x_in && src == e.x_in) {
+                // the reference records the state before the churn noise is added (models/sample.py:660)
+                launch_copy_bytes(h->state[e.rec_x_buf], a.xs + (size_t)e.rec_x * n, bytes, st); h->launches += 1;
+                recorded_x = true;
+            }
             const float* nz = a.bank ? a.bank + (size_t)e.pre_noise_index * n : nullptr;
-            launch_axpby(h->state[e.x_in], nz, h->state[e.x_in], row + 6, n, V, a.seed, a.shower_offset, e.pre_noise_index, 1, st);
+            launch_axpby(h->state[src], nz, h->state[e.x_in], row + 6, n, V, a.seed, a.shower_offset, e.pre_noise_index, 1, st,
+                         rng_key);
             h->launches += 1;
         }
         Run r;
@@ -1154,6 +1174,10 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
         if (e.x0_buf >= 0) x0_dst = h->state[e.x0_buf];
         else if (e.rec_x0 >= 0 && a.x0s) x0_dst = a.x0s + (size_t)e.rec_x0 * n;
         r.fin.x0_out = x0_dst;
+        r.fin.fault = h->fault; r.fin.eval_index = i;
+        r.fin.coef = row + 1;
+        if (e.d_out >= 0) r.fin.d_out = h->state[e.d_out];
+        r.fin.rng_key = rng_key;
         if (e.x_out >= 0) {
             r.fin.x_out = h->state[e.x_out];
             r.fin.coef = row + 1;
@@ -1168,7 +1192,7 @@ static int enqueue_sample(cd_unet* h, const SampleArgs& a, cudaStream_t st) {
         if (run_forward(h, r)) return 1;
         if (e.x0_buf >= 0 && e.rec_x0 >= 0 && a.x0s)
             { launch_copy_bytes(h->state[e.x0_buf], a.x0s + (size_t)e.rec_x0 * n, bytes, st); h->launches += 1; }
-        if (e.rec_x >= 0 && a.xs)
+        if (e.rec_x >= 0 && a.xs && !recorded_x)
             { launch_copy_bytes(h->state[e.rec_x_buf], a.xs + (size_t)e.rec_x * n, bytes, st); h->launches += 1; }
     }
     launch_copy_bytes(h->state[a.final_buf], a.x_final, bytes, st);
@@ -1201,34 +1225,53 @@ extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_sca
         const cd_eval& e = evals[i];
         auto okb = [](int b, int lo) { return b >= lo && b < CD_NUM_STATE_BUFS; };
         if (!okb(e.x_in, 0) || !okb(e.x_out, -1) || !okb(e.x0_buf, -1) || !okb(e.a1, -2) || !okb(e.a2, -1) || !okb(e.a3, -1) ||
+            !okb(e.pre_src, -1) || !okb(e.d_out, -1) ||
             (e.rec_x >= 0 && !okb(e.rec_x_buf, 0)))
             return fail("eval %d references a state buffer outside [0,%d)", i, CD_NUM_STATE_BUFS);
         if (!(e.sigma > 0.f)) return fail("eval %d: sigma must be > 0 (got %g)", i, (double)e.sigma);  // sample.py:166-167
     }
     cudaStream_t st = (cudaStream_t)stream;
-    std::vector<float> tab((size_t)(n_evals + 1) * 8, 0.f);
+    std::vector<float> tab((size_t)(n_evals + 1) * kRow, 0.f);
     for (int i = 0; i < n_evals; ++i) {
-        float* row = &tab[(size_t)i * 8];
+        float* row = &tab[(size_t)i * kRow];
         row[0] = evals[i].sigma;
         for (int j = 0; j < 5; ++j) row[1 + j] = evals[i].k[j];
-        row[6] = evals[i].pre_a; row[7] = evals[i].pre_b;
+        row[6] = evals[i].pre_a; row[7] = evals[i].pre_b; row[8] = evals[i].d_scale;
     }
-    tab[(size_t)n_evals * 8] = start_scale;
+    tab[(size_t)n_evals * kRow] = start_scale;
+    {
+        const uint32_t key[3] = {(uint32_t)seed, (uint32_t)(seed >> 32), (uint32_t)shower_offset};
+        memcpy(&tab[(size_t)n_evals * kRow + 2], key, sizeof(key));
+    }
     CD_CUDA(cudaMemcpyAsync(h->coef_tab, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+    *h->fault_host = 0x7fffffff;
+    CD_CUDA(cudaMemcpyAsync(h->fault, h->fault_host, sizeof(int), cudaMemcpyHostToDevice, st));
+    // after the loop: one 4-byte readback (the only synchronisation; nothing inside the graph waits on the host)
+    auto check_fault = [&]() -> int {
+        if (!h->check_finite) return 0;
+        CD_CUDA(cudaMemcpyAsync(h->fault_host, h->fault, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CD_CUDA(cudaStreamSynchronize(st));
+        if (*h->fault_host != 0x7fffffff)
+            return fail("non-finite network output at evaluation %d of %d (sigma %g): activations left the fp16 range "
+                        "(supported domain |c_in*x| < 65504); set option check_finite=0 to get the non-finite showers instead",
+                        *h->fault_host, n_evals, (double)evals[*h->fault_host].sigma);
+        return 0;
+    };
     SampleArgs a{start_dev, start_scale, cond_dev, evals, n_evals, noise_bank_dev, seed, shower_offset, final_buf,
                  x_final_dev, xs_dev, x0s_dev, B};
-    if (!use_graph || h->profile) return enqueue_sample(h, a, st);
+    if (!use_graph || h->profile) { if (enqueue_sample(h, a, st)) return 1; return check_fault(); }
 
     // key: everything baked into the graph (structure + pointers); numeric schedule values live in coef_tab
     std::vector<unsigned char> key;
     auto put = [&key](const void* p, size_t n) { const unsigned char* c = (const unsigned char*)p; key.insert(key.end(), c, c + n); };
     put(&start_dev, sizeof(void*)); put(&cond_dev, sizeof(void*)); put(&noise_bank_dev, sizeof(void*));
     put(&x_final_dev, sizeof(void*)); put(&xs_dev, sizeof(void*)); put(&x0s_dev, sizeof(void*));
-    put(&seed, sizeof(seed)); put(&shower_offset, sizeof(int)); put(&final_buf, sizeof(int)); put(&B, sizeof(int));
-    put(&h->conv_backend, sizeof(int));
+    put(&final_buf, sizeof(int)); put(&B, sizeof(int));     // seed / shower_offset are device-resident (coef_tab), not baked
+    put(&h->conv_backend, sizeof(int)); put(&n_evals, sizeof(int));
     for (int i = 0; i < n_evals; ++i) {
         const cd_eval& e = evals[i];
-        int s[12] = {e.x_in, e.x_out, e.x0_buf, e.a1, e.a2, e.a3, e.noise_index, e.pre_b != 0.f, e.pre_noise_index, e.rec_x0, e.rec_x, e.rec_x_buf};
+        int s[14] = {e.x_in, e.x_out, e.x0_buf, e.a1, e.a2, e.a3, e.noise_index, e.pre_b != 0.f, e.pre_noise_index, e.rec_x0, e.rec_x,
+                     e.rec_x_buf, e.pre_src, e.d_out};
         put(s, sizeof(s));
     }
     if (!h->graph_exec || key != h->graph_key) {
@@ -1252,7 +1295,7 @@ extern "C" int cd_sample_run(cd_unet* h, const float* start_dev, float start_sca
     }
     CD_CUDA(cudaGraphLaunch(h->graph_exec, st));
     h->launches += h->graph_nodes;
-    return 0;
+    return check_fault();
 }
 
 // -------------------------------------------------------------------------------------------------

@@ -460,12 +460,17 @@ __device__ __forceinline__ void final_tail(const FinalParams& p, long long v, in
     float x0 = sd > 0.f ? (sd * sd / den) * xin + (s * sd * rsqrtf(den)) * pred : pred;
     if (p.pred_out) p.pred_out[v] = pred;
     if (p.x0_out) p.x0_out[v] = x0;
+    if (p.d_out) p.d_out[v] = p.coef[7] * (xin - x0);
+    if (p.fault && !isfinite(pred)) atomicMin(p.fault, p.eval_index);   // activations left the fp16 range somewhere upstream
     if (p.x_out) {
         const float* k = p.coef;
         float o = k[0] * x0 + k[1] * xin;
         if (p.a1) o += k[2] * p.a1[v];
-        else if (p.rng_enabled && k[2] != 0.f)
-            o += k[2] * philox_normal(p.seed, (uint32_t)(p.shower_offset + b), (uint32_t)p.step, (uint32_t)rem);
+        else if (p.rng_enabled && k[2] != 0.f) {
+            const uint64_t seed = p.rng_key ? (((uint64_t)p.rng_key[1] << 32) | p.rng_key[0]) : p.seed;
+            const int so = p.rng_key ? (int)p.rng_key[2] : p.shower_offset;
+            o += k[2] * philox_normal(seed, (uint32_t)(so + b), (uint32_t)p.step, (uint32_t)rem);
+        }
         if (p.a2) o += k[3] * p.a2[v];
         if (p.a3) o += k[4] * p.a3[v];
         p.x_out[v] = o;
@@ -644,9 +649,10 @@ void launch_layer_mlp(const LayerMlpParams& m, const FinalParams& p, const float
 // x_out = a*x + b*noise (start scaling  x = start*sigma_0, and the EDM churn pre-noise, sample.py:633,651)
 __global__ void axpby_kernel(const float* __restrict__ x, const float* __restrict__ noise, float* __restrict__ out,
                              const float* __restrict__ coef, long long n, int vps, uint64_t seed, int shower_offset,
-                             int step, int rng_enabled) {
+                             int step, int rng_enabled, const uint32_t* __restrict__ rng_key) {
     long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
+    if (rng_key) { seed = ((uint64_t)rng_key[1] << 32) | rng_key[0]; shower_offset = (int)rng_key[2]; }
     float o = coef[0] * x[v];
     float kb = coef[1];
     if (kb != 0.f) {
@@ -660,9 +666,9 @@ __global__ void axpby_kernel(const float* __restrict__ x, const float* __restric
 }
 
 void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps, unsigned long long seed,
-                  int shower_offset, int step, int rng_enabled, cudaStream_t st) {
+                  int shower_offset, int step, int rng_enabled, cudaStream_t st, const uint32_t* rng_key) {
     axpby_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, noise, out, coef, n, vps, seed, shower_offset, step,
-                                                              rng_enabled);
+                                                              rng_enabled, rng_key);
 }
 
 // plain device copy / clear as kernels: inside the captured sampling graph these replace cudaMemcpyAsync / cudaMemsetAsync

@@ -22,9 +22,15 @@ struct FinalParams {
     float* pred_out;                    // optional raw network output
     float* x0_out;                      // optional denoised output
     float* x_out;                       // optional sampler-updated state
-    const float* coef;                  // k0..k4 (device)
+    const float* coef;                  // k0..k4, [7] = d_scale (device)
+    float* d_out;                       // optional: d_scale*(x - x0), the derivative multistep samplers keep
     const float* a1; const float* a2; const float* a3;
     int rng_enabled; unsigned long long seed; int shower_offset; int step;
+    // optional device-resident Philox key {seed lo, seed hi, shower_offset} (overrides seed / shower_offset): keeps a captured
+    // sampling graph independent of the per-call seed
+    const uint32_t* rng_key;
+    // optional fault word: atomicMin(eval_index) when the raw network output of a voxel is non-finite (fp16 range exceeded)
+    int* fault; int eval_index;
 };
 
 // CSR linear map between the caller's flat voxel vector and the regular grid (device pointers)
@@ -79,7 +85,8 @@ void launch_embed(const EmbedParams& p, const float* sigma, int sigma_stride, co
                   cudaStream_t st);
 void launch_final(const FinalParams& p, int B, cudaStream_t st);
 void launch_axpby(const float* x, const float* noise, float* out, const float* coef, long long n, int vps,
-                  unsigned long long seed, int shower_offset, int step, int rng_enabled, cudaStream_t st);
+                  unsigned long long seed, int shower_offset, int step, int rng_enabled, cudaStream_t st,
+                  const uint32_t* rng_key = nullptr);
 void launch_copy_bytes(const void* src /* nullptr: clear */, void* dst, size_t bytes, cudaStream_t st);
 void launch_fill_normal(float* out, long long n, int vps, unsigned long long seed, int shower_offset, int step,
                         cudaStream_t st);

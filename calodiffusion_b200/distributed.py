@@ -33,7 +33,10 @@ def gather_showers(local, n_showers):
         return local
     sizes = [shard_range(n_showers, r, ws) for r in range(ws)]
     cap = max(hi - lo for lo, hi in sizes)
-    flat = local.reshape(local.shape[0], -1)
+    width = 1
+    for d in local.shape[1:]:
+        width *= int(d)
+    flat = local.reshape(local.shape[0], width)      # explicit width: an empty slice (n < world size) reshapes too
     if len({hi - lo for lo, hi in sizes}) == 1:
         out = torch.empty((ws * cap, flat.shape[1]), dtype=flat.dtype, device=flat.device)
         dist.all_gather_into_tensor(out, flat.contiguous())
@@ -49,22 +52,28 @@ def gather_showers(local, n_showers):
 def sample_sharded(model, energy, layers, num_steps=400, sample_offset=0, start=None, seed=None):
     """`Diffusion.sample` for a batch that is split over the ranks: every rank passes the FULL conditioning
     (and optionally the full start noise), samples its own slice and receives the full set of showers.
-    With `seed` the start noise comes from the library's Philox stream keyed by global shower index, so the showers
-    are independent of the number of ranks (the per-step noise seed is drawn from torch's RNG: seed it identically
-    on every rank).  Returns a device tensor (n_showers, *data_shape)."""
+    The start noise (when not passed in) and the per-step noise both come from the library's Philox stream keyed by
+    GLOBAL shower index, so the showers do not depend on the number of ranks and no two ranks ever share a stream.
+    `seed=None` draws the key from torch's global RNG: seed that identically on every rank (the per-step noise key is
+    drawn from it as well).  Returns a device tensor (n_showers, *data_shape)."""
     rank, ws = world()
     n = energy.shape[0]
     lo, hi = shard_range(n, rank, ws)
     sampler = model.sampler_algorithm
+    if start is None and seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())       # same draw on every (identically seeded) rank
+    if hi == lo:
+        # fewer showers than ranks: this rank owns none, but still consumes the RNG draw the others make and joins the gather
+        sampler._seed()
+        x = torch.empty([0] + list(model._data_shape), device=model.device, dtype=torch.float32)
+        return gather_showers(x, n)
     prev = sampler.shower_offset
     sampler.shower_offset = lo
     try:
         e = energy[lo:hi]
         l = None if layers is None else layers[lo:hi]
-        if start is None and seed is not None:
+        if start is None:
             start_l = model.philox_normal(hi - lo, seed, shower_offset=lo, slot=0x7fffffff)
-        elif start is None:
-            start_l = model.noise_generation([hi - lo] + list(model._data_shape))
         else:
             start_l = start[lo:hi]
         x, _, _ = sampler(model, start_l, e, l, num_steps, sample_offset, False)

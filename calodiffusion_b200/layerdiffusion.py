@@ -60,7 +60,7 @@ class LayerDiffusion(CaloDiffusion):
         self._states = {
             False: None,
             True: dict(_handle=None, _handle_versions=None, _io={}, _voxels=self._layer_dim, _cond_size=3 if self.hgcal else 1,
-                       layer_cond=False, do_embed=False),
+                       layer_cond=False, do_embed=False, _max_batch=self._max_batch),
         }
 
     def init_model(self):
@@ -73,7 +73,9 @@ class LayerDiffusion(CaloDiffusion):
         return model
 
     # ------------------------------------------------------------------ state switching
-    _SWAPPED = ("_handle", "_handle_versions", "_io", "_voxels", "_cond_size", "layer_cond", "do_embed")
+    # `_max_batch` is per handle: each engine is built for its own largest batch (a larger later batch rebuilds only the
+    # active state's handle, so the other state's handle must keep the value it was built with)
+    _SWAPPED = ("_handle", "_handle_versions", "_io", "_voxels", "_cond_size", "layer_cond", "do_embed", "_max_batch")
 
     def set_layer_state(self, is_layer=False):
         """layerdiffusion.py:40-48: which of the two denoisers `forward` / `denoise` / the samplers drive."""

@@ -24,6 +24,7 @@ def _eval(**kw):
     e = _lib.Eval()
     e.x_out = e.x0_buf = e.a1 = e.a2 = e.a3 = -1
     e.rec_x0 = e.rec_x = -1
+    e.pre_src = e.d_out = -1
     e.pre_a = 1.0
     for k, v in kw.items():
         if k == "k":
@@ -108,11 +109,17 @@ class EDMAbstract(Sample):
         self.sigma_max = self.sample_config.get("SIGMA_MAX", 80.0)
         self.orig_schedule = self.sample_config.get("ORG_SCHEDULE", False)
         self.rho = self.sample_config.get("RHO", 7)
-        self.last_step_euler = False   # True: guarded final step (utils/sampling.py:232) instead of the reference's 1/0
+        # Heun / DPM2: the reference's last step divides by t_next = 0 (non-finite showers, reproduced by default).
+        # SAMPLER_OPTIONS {"LAST_STEP_EULER": true} (or the attribute) takes that step as an Euler step instead, the
+        # guard of utils/sampling.py:232 - the finite form bench.py measures and says so in its config block.
+        self.last_step_euler = bool(self.sample_config.get("LAST_STEP_EULER", False))
 
     def setup(self, num_steps, sample_offset):
         if self.orig_schedule:
-            raise ValueError("ORG_SCHEDULE is not supported by the B200 backend")
+            # models/sample.py:686-699 calls self.alpha_bar(j - 1) with one argument although alpha_bar takes (j, num_steps):
+            # the reference raises TypeError here for every sampler, so there is no behaviour to reproduce
+            raise ValueError("ORG_SCHEDULE raises inside the reference itself (alpha_bar arity, models/sample.py:691); "
+                             "not supported by the B200 backend")
         step_indices = torch.arange(num_steps, dtype=torch.float32)
         t_steps = (self.sigma_max ** (1 / self.rho) + step_indices / (num_steps - 1)
                    * (self.sigma_min ** (1 / self.rho) - self.sigma_max ** (1 / self.rho))) ** self.rho
@@ -132,11 +139,10 @@ class EDMAbstract(Sample):
             pre_b = float((t_hat ** 2 - t_cur ** 2).sqrt() * self.S_noise)
             h = t_next - t_hat
             ht = float(h / t_hat)
-            if pre_b != 0.0 and self.order != 1:
-                raise ValueError("Heun / DPM2 with NOISY_SAMPLE churn is not supported by the B200 backend yet")
             common = dict(sigma=float(t_hat), x_in=cur, pre_a=1.0, pre_b=pre_b, pre_noise_index=i,
                           rec_x0=i if debug else -1)
-            # NOTE: with churn the reference records the un-noised x_cur; records are taken only when pre_b == 0
+            # with churn (pre_b != 0) x_hat = x_cur + noise replaces x_cur in place; the engine records xs[i] before the noise
+            # is added, as the reference does (models/sample.py:660 appends x_cur)
             if self.order == 1 or (self.last_step_euler and float(t_next) == 0.0):
                 # x_next = x_hat + h*(x_hat - D)/t_hat
                 evals.append(_eval(**common, x_out=other, k=(-ht, 1.0 + ht, 0, 0, 0),
@@ -147,12 +153,12 @@ class EDMAbstract(Sample):
                 # x_next = x_hat + h*(x_2 - D_2)/t_mid.  t_next = 0: t_mid = 0, evaluation at sigma 0 and h/0 (reference)
                 t_mid = torch.as_tensor(t_hat).log().lerp(torch.as_tensor(t_next).log(), 0.5).exp()
                 r = float((t_mid - t_hat) / t_hat)
-                evals.append(_eval(**common, x_out=3, k=(-r, 1.0 + r, 0, 0, 0)))
+                # (xs[i] is recorded by the FIRST evaluation: with churn the engine takes it before the noise is added)
+                evals.append(_eval(**common, x_out=3, k=(-r, 1.0 + r, 0, 0, 0), rec_x=i if debug else -1, rec_x_buf=cur))
                 with np.errstate(divide="ignore"):
                     hm = float(np.float32(h) / np.float32(t_mid))
                 sig2 = float(t_mid) if float(t_mid) > 0.0 else 1e-30
-                evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=(-hm, hm, 1.0, 0, 0), a1=cur,
-                                   rec_x=i if debug else -1, rec_x_buf=cur))
+                evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=(-hm, hm, 1.0, 0, 0), a1=cur))
                 cur, other = other, cur
             else:
                 # first evaluation: D -> buf2, x' -> buf3
@@ -167,8 +173,17 @@ class EDMAbstract(Sample):
                     # reference evaluates the network at sigma = 0 here (log 0 / division by zero): results are
                     # non-finite there as well; evaluate at a tiny sigma and let the inf coefficients propagate
                     sig2 = 1e-30
-                evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=k, a1=cur, a2=2,
-                                   rec_x=i if debug else -1, rec_x_buf=cur))
+                if pre_b != 0.0:
+                    # churn: d' uses the UN-noised x_cur (models/sample.py:820 reads self.x_next) while everything else uses
+                    # x_hat, so x_hat goes to its own buffer (`other`) and x_cur stays in `cur`:
+                    #   x_next = x_hat + h*(0.5*(x_hat - D)/t_hat + 0.5*(x_cur - D')/t_next)
+                    evals[-1].x_in, evals[-1].pre_src = other, cur
+                    k = (-hn, 0.0, hn, -0.5 * ht, 1.0 + 0.5 * ht)
+                    evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=k, a1=cur, a2=2, a3=other,
+                                       rec_x=i if debug else -1, rec_x_buf=cur))
+                else:
+                    evals.append(_eval(sigma=sig2, x_in=3, x_out=other, k=k, a1=cur, a2=2,
+                                       rec_x=i if debug else -1, rec_x_buf=cur))
                 cur, other = other, cur
         n = n_steps
         x, xs, x0s = model.run_program(start, energy, layers, evals, float(t_steps[0]), cur, noise_bank=self.noise_bank,
@@ -208,8 +223,10 @@ class LMS(EDMAbstract):
     """models/sample.py:729-768: linear multistep (SAMPLER_OPTIONS ORDER, default 4) over the Karras schedule; one
     denoiser evaluation per step, no noise, returns empty xs / x0s like the reference.
 
-    The update needs up to ORDER stored derivatives, more operands than a `cd_eval` record carries, so the loop runs
-    on the host: each step is one `cd_denoise` call (the CUDA denoiser) plus the axpy on the device tensors."""
+    Runs as a fused `cd_eval` program like the other samplers (one CUDA graph): every evaluation also stores its ODE
+    derivative d_i = (x - D)/t_i in a ring of state buffers (cd_eval.d_out / d_scale) and the update reads the previous
+    ORDER-1 of them:  x_next = x + c_0*d_i + c_1*d_{i-1} + ...  with c_0*d_i folded into the (D, x) coefficients."""
+    MAX_ORDER = 4   # x + the current derivative + three ring reads (a1..a3) per record
 
     def __init__(self, config):
         super().__init__(config)
@@ -217,22 +234,22 @@ class LMS(EDMAbstract):
 
     @torch.no_grad()
     def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
+        if not 1 <= int(self.order) <= self.MAX_ORDER:
+            raise ValueError(f"LMS ORDER must be in [1, {self.MAX_ORDER}] on the B200 backend (got {self.order})")
         t_steps = self.setup(num_steps, sample_offset)
         t64 = t_steps.double().numpy()
-        x_next = start.to(torch.float32) * float(t_steps[0])
-        B = start.shape[0]
-        ds = []
+        ring = (1, 2, 3, 4)                     # state buffers holding d_i, slot i % 4
+        evals = []
         for i in range(len(t_steps) - 1):
             t_hat = float(t_steps[i])
-            sigma = torch.full((B,), t_hat, dtype=torch.float32, device=x_next.device)
-            denoised = model.denoise(x_next, sigma=sigma, E=energy, layers=layers)
-            ds.append((x_next - denoised) / t_hat)
-            if len(ds) > self.order:
-                ds.pop(0)
-            cur_order = min(i + 1, self.order)
-            for j, d in enumerate(reversed(ds)):
-                x_next = x_next + linear_multistep_coeff(cur_order, t64, i, j) * d
-        return x_next, [], []
+            cur_order = min(i + 1, int(self.order))
+            c = [linear_multistep_coeff(cur_order, t64, i, j) for j in range(cur_order)] + [0.0] * 4
+            prev = [ring[(i - j) % 4] if j < cur_order else -1 for j in (1, 2, 3)]
+            evals.append(_eval(sigma=t_hat, x_in=0, x_out=0, k=(-c[0] / t_hat, 1.0 + c[0] / t_hat, c[1], c[2], c[3]),
+                               a1=prev[0], a2=prev[1], a3=prev[2], d_out=ring[i % 4], d_scale=1.0 / t_hat))
+        x, _, _ = model.run_program(start, energy, layers, evals, float(t_steps[0]), 0, noise_bank=None, seed=0,
+                                    shower_offset=self.shower_offset)
+        return x, [], []
 
 
 class Restart(EDMAbstract):

@@ -51,9 +51,10 @@ typedef struct cd_unet_desc {
 } cd_unet_desc;
 
 /* One denoiser evaluation inside a sampling loop plus the fused state update that follows it:
- *   [optional]  buf[x_in] = pre_a*buf[x_in] + pre_b*noise(pre_noise_index)
+ *   [optional]  buf[x_in] = pre_a*buf[pre_src] + pre_b*noise(pre_noise_index)      (pre_src < 0: in place on buf[x_in])
  *   x0 = denoise(buf[x_in], sigma)
  *   [optional]  buf[x0_buf] = x0
+ *   [optional]  buf[d_out] = d_scale*(buf[x_in] - x0)        (the ODE derivative (x - D)/sigma kept by multistep samplers)
  *   [optional]  buf[x_out] = k0*x0 + k1*buf[x_in] + k2*A1 + k3*buf[a2] + k4*buf[a3]
  * A1 is buf[a1] if a1 >= 0, noise slot `noise_index` if a1 == -2, absent if a1 == -1.
  * Noise comes from the caller's bank (noise_bank != NULL: slot i = bank + i*B*voxels) or from the
@@ -68,10 +69,13 @@ typedef struct cd_eval {
     int pre_noise_index;
     int rec_x0;    /* >= 0: also copy x0 to x0s[rec_x0] */
     int rec_x;     /* >= 0: copy a state buffer to xs[rec_x] ... */
-    int rec_x_buf; /* ... this buffer, after the update */
+    int rec_x_buf; /* ... this buffer, after the update (a buffer that receives pre-noise is recorded before the noise) */
+    int pre_src;   /* >= 0: the pre-noise step reads this buffer and writes buf[x_in]; -1: in place */
+    int d_out;     /* >= 0: buf[d_out] = d_scale*(buf[x_in] - x0); -1: none */
+    float d_scale;
 } cd_eval;
 
-#define CD_NUM_STATE_BUFS 4
+#define CD_NUM_STATE_BUFS 8
 
 const char* cd_last_error(void);
 int cd_version(void);

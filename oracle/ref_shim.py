@@ -1,14 +1,21 @@
 """Import shim for the live reference (TEST INFRASTRUCTURE ONLY — never imported by the product).
 
-Makes `/root/reference/calodiffusion` importable on CPU in the build container by stubbing the five
-non-arithmetic modules it imports at module scope (h5py, matplotlib, mpl_toolkits, mplhep, torchsde).
-Only `oracle/make_golden.py` and `oracle/check_oracle_vs_reference.py` use this, and only in the
-container that has `/root/reference`; it cannot travel to the GPU box (no /root/reference there).
+Makes the unmodified reference package importable by stubbing the five non-arithmetic modules it imports at
+module scope (h5py, matplotlib, mpl_toolkits, mplhep, torchsde) when they are absent.  The reference is looked
+up in `oracle/_ref/` first (the verbatim copy staged by `oracle/build_ref.sh`, which travels to the GPU box with
+the gpurun snapshot) and in `/root/reference` otherwise (build container).  Users: `oracle/make_golden*.py`,
+`tests/` (drop-in checks) and `bench.py`'s reference legs.  Never imported by `calodiffusion_b200/`.
 """
+import os
 import sys
 import types
 
-REF_ROOT = "/root/reference"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_ROOT = os.path.join(_HERE, "_ref") if os.path.isdir(os.path.join(_HERE, "_ref", "calodiffusion")) else "/root/reference"
+
+
+def available():
+    return os.path.isdir(os.path.join(REF_ROOT, "calodiffusion"))
 
 
 def _make_stub(name):

@@ -26,6 +26,9 @@ class _FakeSampler:
     """Stands in for a sampler: the 'shower' of global index i is a deterministic function of i, its conditioning and start."""
     shower_offset = 0
 
+    def _seed(self):
+        return int(torch.randint(0, 2 ** 62, (1,)).item())
+
     def __call__(self, model, start, energy, layers, num_steps, sample_offset, debug):
         idx = torch.arange(start.shape[0], dtype=torch.float32) + self.shower_offset
         x = start * 0.5 + energy.view(-1, 1, 1) + idx.view(-1, 1, 1) * 10.0 + (0 if layers is None else layers.sum(1).view(-1, 1, 1))
@@ -34,9 +37,16 @@ class _FakeSampler:
 
 class _FakeModel:
     _data_shape = [3, 4]
+    device = torch.device("cpu")
 
     def __init__(self):
         self.sampler_algorithm = _FakeSampler()
+
+    def philox_normal(self, n_showers, seed, shower_offset=0, slot=0):
+        """Stand-in for the library's Philox stream: row i is a function of (seed, global shower index) only."""
+        rows = [torch.randn(3, 4, generator=torch.Generator().manual_seed((int(seed) + 7919 * (shower_offset + i)) % (2 ** 31)))
+                for i in range(int(n_showers))]
+        return torch.stack(rows) if rows else torch.empty(0, 3, 4)
 
     def noise_generation(self, shape):
         raise AssertionError("the test passes the start noise explicitly")
@@ -48,7 +58,7 @@ def _expected(E, L, start):
     return x
 
 
-def _worker(rank, ws, port, n, q):
+def _worker(rank, ws, port, n, q, own_start=True):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=ws)
@@ -56,23 +66,33 @@ def _worker(rank, ws, port, n, q):
         g = torch.Generator().manual_seed(5)
         E, L, start = torch.rand(n, 1, generator=g), torch.randn(n, 6, generator=g), torch.randn(n, 3, 4, generator=g)
         m = _FakeModel()
-        out = D.sample_sharded(m, E, L, num_steps=4, start=start)
+        if own_start:
+            out = D.sample_sharded(m, E, L, num_steps=4, start=start)
+        else:
+            # start=None, seed=None: the key is drawn from the identically seeded torch RNG and the start noise is keyed by
+            # global shower index - the gathered result must equal the single-process one (no duplicated streams)
+            torch.manual_seed(123)
+            out = D.sample_sharded(m, E, L, num_steps=4)
+            torch.manual_seed(123)
+            start = m.philox_normal(n, int(torch.randint(0, 2 ** 62, (1,)).item()))
+            rows = out - _expected(E, L, torch.zeros_like(start))     # = 0.5 * start row by row
+            assert n < 2 or not torch.equal(rows[0], rows[n - 1])     # distinct ranks do not reuse a stream
         assert m.sampler_algorithm.shower_offset == 0          # restored
-        ok = torch.equal(out, _expected(E, L, start))
+        ok = torch.allclose(out, _expected(E, L, start), atol=0, rtol=0) if own_start else torch.allclose(out, _expected(E, L, start))
         q.put((rank, bool(ok), tuple(out.shape)))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n", [8, 7])   # even and ragged split
-def test_sample_sharded_world_size_2_gloo(n):
+@pytest.mark.parametrize("n,own_start", [(8, True), (7, True), (7, False), (1, False)])   # even / ragged / fewer showers than ranks
+def test_sample_sharded_world_size_2_gloo(n, own_start):
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, q, own_start)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in procs]

@@ -2,7 +2,7 @@
 
 Dataset 1 photons: x is (B, 368); every denoiser evaluation runs NNConverter.enc -> cylindrical U-Net on (5,10,30) ->
 NNConverter.dec on the device.  Checked against the live reference's goldens (tests/golden/ds1.npz) and the oracle.
-Tolerance as in test_gpu_parity.py (fp16 activations, fp32 accumulation): rel-L2 <= 1e-2; the maps alone are fp32
+Tolerance as in test_gpu_parity.py (fp16 activations, fp32 accumulation): rel-L2 gate 2.5e-3 (3x measured); the maps alone are fp32
 (<= 1e-5)."""
 import numpy as np
 import pytest
@@ -12,7 +12,7 @@ from conftest import ds1_geom_oracle, load_case, noise_bank, rel_l2, write_binni
 
 pytestmark = pytest.mark.gpu
 
-TOL = 1e-2
+TOL = 2.5e-3   # 3x the largest error measured for these checks (8.0e-4, profiles/r01_pytest_gpu_geometry.log)
 
 
 @pytest.fixture(scope="module")

@@ -99,3 +99,13 @@ def test_two_stage_sample_matches_oracle_chain(ld):
     out = m.sample(E.cuda(), None, num_steps=2, return_layers=True)
     assert set(out) == {"x", "layers"} and out["x"].shape == (B, 1, 45, 16, 9) and np.isfinite(out["x"]).all()
     assert tuple(out["layers"].shape) == (B, 46)
+
+
+def test_growing_batch_rebuilds_each_engine(ld):
+    """a small warm-up batch followed by a larger one.  Each of the two engines (layer model, U-Net) is rebuilt for
+    the larger batch on its own (`_max_batch` is per handle), so the second call must not fail with 'batch outside max_batch'."""
+    m, c, base, cfg = ld
+    for B in (4, 12):      # the fixture was built with max_batch = 8: 12 forces a rebuild of both handles
+        E = torch.rand(B, 1, generator=torch.Generator().manual_seed(B)).cuda()
+        out = m.sample(E, None, num_steps=2, return_layers=True)
+        assert out["x"].shape[0] == B and np.isfinite(out["x"]).all() and tuple(out["layers"].shape) == (B, 46)

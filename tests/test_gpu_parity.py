@@ -1,8 +1,13 @@
 """GPU parity tests: the CUDA path (through the C ABI) against the oracle and the live-reference goldens.
 
 Tolerance: the path stores activations in fp16 and multiplies fp16 x fp16 -> fp32 on the tensor cores
-(TF32-equivalent 10-bit mantissa at BF16 speed), so north_star's 16-bit tolerance applies: relative L2
-<= 1e-2 per denoiser evaluation and on final showers.  Measured errors are ~1e-3 (printed)."""
+(TF32-equivalent 10-bit mantissa at BF16 speed); north_star's bound for a 16-bit path is relative L2 <= 1e-2.
+The gates below are NOT that blanket bound: each is 2-3x the error measured on B200 for that kind of check
+(profiles/r01_pytest_gpu_*.log, r02_*), so a regression that triples an error fails:
+  single denoiser evaluation  measured 3.4e-4 .. 8.0e-4  -> TOL_EVAL 2e-3
+  raw network output (forward, no c_skip blend) 1.6e-3   -> TOL_FWD  4e-3
+  2..8-step sampling loops    measured 2.5e-4 .. 1.9e-3  -> TOL_LOOP 4e-3
+(the BASELINE-horizon loops, 50..400 steps, live in tests/test_gpu_long.py with their own measured gates)."""
 import ctypes as C
 import os
 
@@ -15,7 +20,9 @@ from conftest import load_case, noise_bank, rel_l2
 
 pytestmark = pytest.mark.gpu
 
-TOL = 1e-2
+TOL_EVAL = 2e-3
+TOL_FWD = 4e-3
+TOL_LOOP = 4e-3
 TOL_LAYER = 2e-3   # single layer on fp16-rounded inputs/weights: only the fp16 output rounding + sum order remain
 
 
@@ -156,7 +163,7 @@ def test_denoise_generic_backend(models, case):
     finally:
         m.set_conv_backend(0)
     print(case, "generic-backend denoise rel-L2:", f"{e:.2e}")
-    assert e < TOL
+    assert e < TOL_EVAL
 
 
 def _level_z(m, lev):
@@ -176,7 +183,7 @@ def test_denoise_matches_reference_golden(models, case):
                       layers=None if c["layers"] is None else c["layers"].cuda())
         errs.append(rel_l2(y.cpu().numpy(), c["gold"][f"denoise_{tag}"]))
     print(case, "denoise rel-L2 vs reference:", [f"{e:.2e}" for e in errs])
-    assert max(errs) < TOL
+    assert max(errs) < TOL_EVAL
 
 
 def test_unet_forward_matches_oracle(models):
@@ -190,7 +197,7 @@ def test_unet_forward_matches_oracle(models):
     y = m.forward(c["x"].cuda(), c["E"].cuda(), t.cuda(), c["layers"].cuda()).cpu().numpy()
     e = rel_l2(y, ref)
     print("forward rel-L2:", f"{e:.2e}")
-    assert e < TOL
+    assert e < TOL_FWD
 
 
 @pytest.mark.parametrize("name,steps", [("DDPM", 4), ("DDim", 3)])
@@ -206,12 +213,12 @@ def test_ddpm_ddim_sampling(models, name, steps, graph):
     e1 = rel_l2(torch.stack(xs).cpu().numpy(), c["gold"][f"{name}_xs"])
     e2 = rel_l2(x.cpu().numpy(), c["gold"][f"{name}_x"])
     print(name, "graph" if graph else "eager", f"x0s {e0:.2e} xs {e1:.2e} final {e2:.2e}")
-    assert max(e0, e1, e2) < TOL
+    assert max(e0, e1, e2) < TOL_LOOP
     # replaying the cached graph must give the same answer again, up to the path's rounding noise: fp32 atomic
     # accumulation order (attention context) perturbs values by ~1e-7, and fp16 re-rounding of the activations
     # at every layer amplifies any perturbation to the fp16 noise floor (~1e-3), never beyond it
     x2, _, _ = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), steps, 0, True)
-    assert rel_l2(x2.cpu().numpy(), x.cpu().numpy()) < TOL / 2
+    assert rel_l2(x2.cpu().numpy(), x.cpu().numpy()) < TOL_LOOP / 2
 
 
 @pytest.mark.parametrize("name", ["Euler", "Heun"])
@@ -221,7 +228,15 @@ def test_edm_sampling(models, name):
     m.use_graph = True
     s = getattr(S, name)(c["cfg"])
     s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 3)).cuda()
-    x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), None, 3, 0, True)
+    if name == "Heun":
+        # the 3-step run leaves the fp16 domain at its last evaluation (below): by default that is an error, not silent NaNs
+        with pytest.raises(RuntimeError, match="fp16 range"):
+            s(m, c["x"].cuda(), c["E"].cuda(), None, 3, 0, True)
+        m.set_check_finite(False)
+    try:
+        x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), None, 3, 0, True)
+    finally:
+        m.set_check_finite(True)
     # With random weights the reference's 3-step Heun blows the state up to ~3e6 at its last step (h/t_next ~ 1e3
     # multiplies x_cur - D', sample.py:820); c_in*x then leaves the fp16 range of this path's activations
     # (|c_in*x| < 65504 is the supported domain; EDM pre-conditioning keeps it O(1) for a trained model).
@@ -231,11 +246,11 @@ def test_edm_sampling(models, name):
     e0 = rel_l2(torch.stack([x0s[i] for i in ok]).cpu().numpy(), c["gold"][f"{name}_x0s"][ok])
     e1 = rel_l2(torch.stack([xs[i] for i in ok]).cpu().numpy(), c["gold"][f"{name}_xs"][ok])
     print(name, f"steps {ok}: x0s {e0:.2e} xs {e1:.2e}")
-    assert max(e0, e1) < TOL
+    assert max(e0, e1) < TOL_LOOP
     if name == "Euler":
         e2 = rel_l2(x.cpu().numpy(), c["gold"]["Euler_x"])
         print("Euler final", f"{e2:.2e}")
-        assert e2 < TOL
+        assert e2 < TOL_LOOP
     else:
         assert not np.isfinite(x.cpu().numpy()).all()   # reference defect reproduced
         # guarded variant (last step = Euler, utils/sampling.py:232), 8 steps so the state stays in range:
@@ -249,7 +264,7 @@ def test_edm_sampling(models, name):
             xo, _, _ = sample_edm(o, c["x"], c["E"], None, 8, 2, noise_bank(c["shape"], c["B"], 8), last_step_euler=True)
         eg = rel_l2(xg.cpu().numpy(), xo.numpy())
         print("Heun guarded final", f"{eg:.2e}", "max|x|", float(xo.abs().max()))
-        assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL
+        assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL_LOOP
 
 
 @pytest.mark.parametrize("order", [4, 2])
@@ -265,7 +280,36 @@ def test_lms_sampling(models, order):
     assert xs == [] and x0s == []
     e = rel_l2(x.cpu().numpy(), gold[f"LMS_order{order}_x"])
     print(f"LMS order {order} final {e:.2e}")
-    assert e < TOL
+    assert e < TOL_LOOP
+
+
+@pytest.mark.parametrize("name", ["Euler", "Heun", "DPM2"])
+def test_churn_sampling(models, name):
+    """NOISY_SAMPLE churn (models/sample.py:639-662) for the first- and second-order samplers vs the live reference
+    (tests/golden/churn.npz): pre-noise before every evaluation with t in [S_min, S_max], xs recorded un-noised."""
+    import os
+    from conftest import GOLDEN
+    from calodiffusion_b200 import sample as S
+    gold = np.load(os.path.join(GOLDEN, "churn.npz"))
+    m, c = models("ds2")
+    s = getattr(S, name)(dict(c["cfg"], NOISY_SAMPLE=True))
+    s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 5)).cuda()
+    m.set_check_finite(False)       # Heun / DPM2: the reference's own last step is 1/0
+    try:
+        x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 5, 0, True)
+    finally:
+        m.set_check_finite(True)
+    ok = [i for i in range(5) if np.isfinite(gold[f"{name}_xs"][i]).all() and np.isfinite(gold[f"{name}_x0s"][i]).all()
+          and np.abs(gold[f"{name}_xs"][i]).max() < 3.0e4]
+    assert len(ok) >= 4
+    e0 = rel_l2(torch.stack([x0s[i] for i in ok]).cpu().numpy(), gold[f"{name}_x0s"][ok])
+    e1 = rel_l2(torch.stack([xs[i] for i in ok]).cpu().numpy(), gold[f"{name}_xs"][ok])
+    print(f"churn {name} steps {ok}: x0s {e0:.2e} xs {e1:.2e}")
+    assert max(e0, e1) < TOL_LOOP
+    if name == "Euler":
+        e2 = rel_l2(x.cpu().numpy(), gold["Euler_x"])
+        print(f"churn Euler final {e2:.2e}")
+        assert e2 < TOL_LOOP
 
 
 def test_restart_sampling(models):
@@ -281,7 +325,7 @@ def test_restart_sampling(models):
     e0 = rel_l2(torch.stack(list(x0s)).cpu().numpy(), gold["Restart_x0s"])
     e1 = rel_l2(x.cpu().numpy(), gold["Restart_x"])
     print(f"Restart x0s {e0:.2e} final {e1:.2e}")
-    assert max(e0, e1) < TOL
+    assert max(e0, e1) < TOL_LOOP
 
 
 def test_dpm2_sampling(models):
@@ -295,11 +339,15 @@ def test_dpm2_sampling(models):
     m, c = models("ds2")
     s = S.DPM2(c["cfg"])
     s.noise_bank = torch.stack(noise_bank(c["shape"], c["B"], 4)).cuda()
-    x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, True)
+    m.set_check_finite(False)       # the reference's own last step evaluates at sigma = 0 and divides by t_mid = 0
+    try:
+        x, xs, x0s = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, True)
+    finally:
+        m.set_check_finite(True)
     e0 = rel_l2(torch.stack(list(x0s)).cpu().numpy(), gold["DPM2_x0s"])
     e1 = rel_l2(torch.stack(list(xs)).cpu().numpy(), gold["DPM2_xs"])
     print(f"DPM2 x0s {e0:.2e} xs {e1:.2e}")
-    assert max(e0, e1) < TOL
+    assert max(e0, e1) < TOL_LOOP
     assert not np.isfinite(x.cpu().numpy()).all()
     s.last_step_euler = True
     xg, _, _ = s(m, c["x"].cuda(), c["E"].cuda(), c["layers"].cuda(), 4, 0, False)
@@ -309,7 +357,7 @@ def test_dpm2_sampling(models):
                               last_step_euler=True)
     eg = rel_l2(xg.cpu().numpy(), xo.numpy())
     print(f"DPM2 guarded final {eg:.2e}")
-    assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL
+    assert np.isfinite(xg.cpu().numpy()).all() and eg < TOL_LOOP
 
 
 def test_consistency_sampling(models):
@@ -326,7 +374,7 @@ def test_consistency_sampling(models):
     e1 = rel_l2(x0.cpu().numpy(), gold["Consistency_x0_last"])
     e2 = rel_l2(x.cpu().numpy(), gold["Consistency_x"])
     print(f"Consistency xs {e0:.2e} x0 {e1:.2e} final {e2:.2e}")
-    assert max(e0, e1, e2) < TOL
+    assert max(e0, e1, e2) < TOL_LOOP
 
 
 def test_hgcal_ddim(models):
@@ -338,7 +386,7 @@ def test_hgcal_ddim(models):
     e0 = rel_l2(torch.stack(x0s).cpu().numpy(), c["gold"]["DDim_x0s"])
     e2 = rel_l2(x.cpu().numpy(), c["gold"]["DDim_x"])
     print("hgcal DDim", f"x0s {e0:.2e} final {e2:.2e}")
-    assert max(e0, e2) < TOL
+    assert max(e0, e2) < TOL_LOOP
 
 
 def test_batch_independence_and_ragged_batch(models):
@@ -353,7 +401,7 @@ def test_batch_independence_and_ragged_batch(models):
     for i in range(3):
         one = m.denoise(x[i:i + 1], E=E[i:i + 1], sigma=sig[i:i + 1], layers=L[i:i + 1])
         # equal up to fp16 rounding noise (tile alignment changes the fp32 partial-sum order of the statistics)
-        assert rel_l2(one.cpu().numpy(), full[i:i + 1].cpu().numpy()) < TOL / 2
+        assert rel_l2(one.cpu().numpy(), full[i:i + 1].cpu().numpy()) < TOL_EVAL / 2
 
 
 def test_error_behaviour(models):
@@ -467,7 +515,7 @@ def test_fused_attention_matches_unfused(models, case):
         m._lib.cd_unet_set_option(h, b"fused_attention", 1)
     e1, e0, d = rel_l2(y1, c["gold"]["denoise_a"]), rel_l2(y0, c["gold"]["denoise_a"]), rel_l2(y1, y0)
     print(case, f"fused vs ref {e1:.2e}, unfused vs ref {e0:.2e}, fused vs unfused {d:.2e}")
-    assert max(e1, e0) < TOL and d < TOL
+    assert max(e1, e0) < TOL_EVAL and d < TOL_EVAL
 
 
 @pytest.mark.parametrize("case", ["ds2", "ds3"])
@@ -487,4 +535,4 @@ def test_online_attention_matches_two_pass(models, case):
         m._lib.cd_unet_set_option(h, b"online_attention", 1)
     e1, e0, d = rel_l2(y1, c["gold"]["denoise_b"]), rel_l2(y0, c["gold"]["denoise_b"]), rel_l2(y1, y0)
     print(case, f"online vs ref {e1:.2e}, two-pass vs ref {e0:.2e}, online vs two-pass {d:.2e}")
-    assert max(e1, e0) < TOL and d < TOL
+    assert max(e1, e0) < TOL_EVAL and d < TOL_EVAL

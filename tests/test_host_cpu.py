@@ -78,18 +78,25 @@ class _InterpretedModel:
 
     def run_program(self, start, E, layers, evals, start_scale, final_buf, noise_bank=None, seed=0, shower_offset=0,
                     n_rec_x=0, n_rec_x0=0):
-        buf = [None] * 4
+        buf = [None] * 8
         buf[0] = start * np.float32(start_scale)
         xs, x0s = [None] * n_rec_x, [None] * n_rec_x0
         B = start.shape[0]
         for e in evals:
-            if e.pre_b != 0.0:
-                buf[e.x_in] = e.pre_a * buf[e.x_in] + e.pre_b * noise_bank[e.pre_noise_index]
+            recorded = False
+            if e.pre_b != 0.0 or e.pre_src >= 0:
+                src = e.pre_src if e.pre_src >= 0 else e.x_in
+                if e.rec_x >= 0 and e.rec_x_buf == e.x_in and src == e.x_in:
+                    xs[e.rec_x], recorded = buf[e.rec_x_buf], True      # recorded before the churn noise
+                noise = noise_bank[e.pre_noise_index] if e.pre_b != 0.0 else 0.0
+                buf[e.x_in] = e.pre_a * buf[src] + e.pre_b * noise
             x0 = self.o.denoise(buf[e.x_in], E, torch.full((B,), e.sigma), layers)
             if e.x0_buf >= 0:
                 buf[e.x0_buf] = x0
             if e.rec_x0 >= 0:
                 x0s[e.rec_x0] = x0
+            if e.d_out >= 0:
+                buf[e.d_out] = e.d_scale * (buf[e.x_in] - x0)
             if e.x_out >= 0:
                 with np.errstate(all="ignore"):
                     out = e.k[0] * x0 + e.k[1] * buf[e.x_in]
@@ -102,7 +109,7 @@ class _InterpretedModel:
                     if e.a3 >= 0:
                         out = out + e.k[4] * buf[e.a3]
                 buf[e.x_out] = out
-            if e.rec_x >= 0:
+            if e.rec_x >= 0 and not recorded:
                 xs[e.rec_x] = buf[e.rec_x_buf]
         return buf[final_buf], xs, x0s
 
@@ -137,8 +144,8 @@ def test_edm_program_reproduces_reference(name):
 
 
 @pytest.mark.parametrize("order", [4, 2])
-def test_lms_host_loop_reproduces_reference(order):
-    """The LMS class (host loop over model.denoise) with the oracle denoiser vs the live reference's LMS."""
+def test_lms_program_reproduces_reference(order):
+    """The LMS class (a cd_eval program with a derivative ring) with the oracle denoiser vs the live reference's LMS."""
     import os
     from conftest import GOLDEN
     gold = np.load(os.path.join(GOLDEN, "lms.npz"))
@@ -152,6 +159,30 @@ def test_lms_host_loop_reproduces_reference(order):
     assert rel_l2(x.numpy(), gold[f"LMS_order{order}_x"]) < 5e-5
     with pytest.raises(ValueError):
         b200_sample.linear_multistep_coeff(3, [3.0, 2.0, 1.0, 0.0], 1, 0)   # utils/sampling.py:78-79
+
+
+@pytest.mark.parametrize("name", ["Euler", "Heun", "DPM2"])
+def test_churn_programs_reproduce_reference(name):
+    """NOISY_SAMPLE churn (models/sample.py:639-662): x_hat = x_cur + sqrt(t_hat^2 - t_cur^2)*S_noise*noise before the
+    evaluation, for the first- and second-order samplers, vs the live reference (tests/golden/churn.npz).  Heun's d' reads
+    the un-noised x_cur (:820), the recorded xs are the un-noised states (:660)."""
+    import os
+    from conftest import GOLDEN
+    gold = np.load(os.path.join(GOLDEN, "churn.npz"))
+    c = load_case("ds2")
+    cfg = dict(c["cfg"], NOISY_SAMPLE=True)
+    model = _InterpretedModel(DenoiserOracle(cfg, c["sd"]))
+    sampler = b200_utils.load_attr("sampler", name)(cfg)
+    assert sampler.S_churn == 40
+    sampler.noise_bank = noise_bank(c["shape"], c["B"], 5)
+    with torch.no_grad():
+        x, xs, x0s = sampler(model, c["x"], c["E"], c["layers"], 5, 0, True)
+    ok = [i for i in range(5) if np.isfinite(gold[f"{name}_xs"][i]).all() and np.isfinite(gold[f"{name}_x0s"][i]).all()]
+    assert len(ok) >= 4
+    assert rel_l2(torch.stack([x0s[i] for i in ok]).numpy(), gold[f"{name}_x0s"][ok]) < 1e-4
+    assert rel_l2(torch.stack([xs[i] for i in ok]).numpy(), gold[f"{name}_xs"][ok]) < 1e-4
+    if name == "Euler":
+        assert rel_l2(x.numpy(), gold["Euler_x"]) < 1e-4
 
 
 def test_restart_program_reproduces_reference():
