@@ -18,9 +18,12 @@ from conftest import GOLDEN, ROOT, load_case, noise_bank, rel_l2
 
 pytestmark = pytest.mark.gpu
 
-# measured on B200 (profiles/r02_error_vs_step.txt): gates are ~2.5x the measured value
-TOL_LONG = {"ds2_ddpm400": 6e-3, "ds3_heun50": 6e-3, "hgcal_ddim200": 6e-3, "ds1_ddim50": 4e-3}
-TOL_ROWWISE = 2e-3
+# measured on B200 (profiles/r02_error_vs_step.txt): worst recorded step / final = 1.62e-3 / 7.3e-4 (ds2 DDPM 400),
+# 5.7e-4 / 2.5e-4 (ds3 Heun 50), 9.4e-4 / 3.6e-4 (hgcal DDim 200), 6.9e-4 / 4.8e-4 (ds1 DDim 50).  The error does NOT grow
+# with the number of steps (the x0 error is largest at the high-noise start and the sampler contracts it); gates ~2.5x measured.
+TOL_LONG = {"ds2_ddpm400": 4e-3, "ds3_heun50": 1.5e-3, "hgcal_ddim200": 2.5e-3, "ds1_ddim50": 2e-3}
+TOL_FINAL = {"ds2_ddpm400": 2e-3, "ds3_heun50": 8e-4, "hgcal_ddim200": 1e-3, "ds1_ddim50": 1.3e-3}
+TOL_ROWWISE = 3e-3     # two fp16 runs with different tile alignment: measured worst per-shower 1.22e-3
 
 
 def _model(case, sampler, max_batch):
@@ -73,6 +76,7 @@ def test_long_horizon_sampling(name):
     print(name, "x0 errors", [f"{e:.2e}" for e in e_x0], "final", f"{e_f:.2e}")
     assert np.isfinite(xf.cpu().numpy()).all()
     assert max(e_x0 + e_x + [e_f]) < TOL_LONG[name], (e_x0, e_x, e_f)
+    assert e_f < TOL_FINAL[name], e_f
 
 
 def test_long_horizon_ds1_in_loop_converter():
@@ -107,7 +111,7 @@ def test_long_horizon_ds1_in_loop_converter():
     e_f = rel_l2(xf.cpu().numpy(), gold["x"])
     _curve("ds1_ddim50", idx, e_x0, e_x, e_f)
     print("ds1_ddim50 x0 errors", [f"{e:.2e}" for e in e_x0], "final", f"{e_f:.2e}")
-    assert max(e_x0 + e_x + [e_f]) < TOL_LONG["ds1_ddim50"]
+    assert max(e_x0 + e_x + [e_f]) < TOL_LONG["ds1_ddim50"] and e_f < TOL_FINAL["ds1_ddim50"]
 
 
 def test_bench_batch_rowwise():
