@@ -41,7 +41,9 @@ __device__ long long g_mma_dbg[16];
 #define DBG_ADD(i, v) dbg_local[i] += (v)
 #define DBG_DECL() long long dbg_local[16] = {0}
 #define DBG_FLUSH(cond) do { if (cond) for (int i_ = 0; i_ < 16; ++i_) if (dbg_local[i_]) atomicAdd((unsigned long long*)&g_mma_dbg[i_], (unsigned long long)dbg_local[i_]); } while (0)
+#define DBG_MODE(bit) (p.dbg_mode & (bit))     // 4: no exchange/shuffles, 8: no global stores, 16: no statistics, 32: no TMEM loads, 64: one issuer, 128: no MMAs
 #else
+#define DBG_MODE(bit) 0
 #define DBG_T() 0LL
 #define DBG_ADD(i, v)
 #define DBG_DECL()
@@ -50,10 +52,13 @@ __device__ long long g_mma_dbg[16];
 
 namespace {
 
-constexpr int kEpiWarps = 8;                    // 2 groups x 4 lane quarters
+#ifndef CD_EPI_SPLIT
+#define CD_EPI_SPLIT 1                          // 1: split a block's channels over two sets of epilogue warps
+#endif
+constexpr int kEpiWarps = CD_EPI_SPLIT ? 16 : 8;   // 2 groups x (1 or 2 channel halves) x 4 lane quarters
 constexpr int kIssuers = 2;                     // MMA-issuing warps (one elected thread each), alternating sub-tiles
 constexpr int kFirstEpiWarp = 1 + kIssuers;
-constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);   // warp 0: loads, warps 1-2: MMA issue (warp 1 owns TMEM), warps 3..10: epilogue
+constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);   // warp 0: loads, warps 1-2: MMA issue (warp 1 owns TMEM), warps 3..18: epilogue
 constexpr int kMaxWStages = 4;
 constexpr int kAStages = 4;
 constexpr int kMaxAcc = 8;
@@ -123,6 +128,23 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000LL) { printf("cd_conv_mma: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
     }
 }
+// waits of the warps that are NOT on the MMA issue path (epilogue, producer): back off between polls so that a spinning warp
+// does not take issue slots from the MMA-issuing warp sharing its scheduler
+#ifndef CD_RELAX_WAIT
+#define CD_RELAX_WAIT 1
+#endif
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+#if CD_RELAX_WAIT
+    if (mbar_try(bar, parity)) return;
+    long long t0 = clock64();
+    while (!mbar_try(bar, parity)) {
+        __nanosleep(40);
+        if (clock64() - t0 > 4000000000LL) { printf("cd_conv_mma: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
+    }
+#else
+    mbar_wait(bar, parity);
+#endif
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
@@ -139,6 +161,20 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
     asm volatile(
         "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+// warp-convergent forms: every lane executes the call, one elected lane performs the operation.  Keeping the C++ control
+// flow convergent lets ptxas hold descriptors / addresses in uniform registers (no per-MMA R2UR waterfall loop).
+__device__ __forceinline__ void umma_f16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n.reg .pred p, e;\nelect.sync _|e, 0xffffffff;\nsetp.ne.b32 p, %4, 0;\n@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}"
+                 ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_elect(uint32_t bar) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e mbarrier.arrive.shared::cta.b64 _, [%0];\n}" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -177,6 +213,12 @@ constexpr int kXchFloats = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quar
 constexpr int kXchBytes = kXchFloats * 4 + 1024;  // 8 KB exchange + 128 floats of bias + 128 floats of folded-PreNorm weight sums
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
+// A sub-tile's epilogue is one long dependent instruction stream per warp (TMEM loads, exchange, 2 shuffles + 5 flops per
+// output element, stores); with 4 warps per sub-tile it took ~4300 clk against ~1000 clk of MMAs.  The channels of a block
+// are therefore split over two sets of 4 warps ("halves") whenever CB is a multiple of 32: both sets read the same TMEM
+// lane quarters (a warp may only touch lanes 32*(warp%4)..+31) at different columns.
+template <int CB, bool K3> __host__ __device__ constexpr int kHalves() { return (CD_EPI_SPLIT && CB % 32 == 0) ? 2 : 1; }
+
 template <int CB, bool K3, int CPG>   // CPG: channels per GroupNorm group for the statistics (divides CB)
 __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -186,14 +228,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     const int w_smem_bytes = p.resident ? p.w_bytes_cb : p.nwstages * p.wstage_bytes;
     unsigned char* abuf = wbuf + ((w_smem_bytes + 127) / 128) * 128;
     const uint32_t wbuf_s = smem_u32(wbuf), abuf_s = smem_u32(abuf);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // broadcast: provably warp-uniform (role branches stay convergent)
+    const int lane = threadIdx.x & 31;
     const Geom& g = p.g;
     constexpr int N = K3 ? 3 * CB : CB;
     DBG_DECL();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), kIssuers); }
-        for (int s = 0; s < kMaxAcc; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 4); }
+        for (int s = 0; s < kMaxAcc; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 4 * kHalves<CB, K3>()); }
         for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), kIssuers); }
         mbar_init(smem_u32(&ctl->w_res), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -240,9 +283,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 const int stage = item % p.astages;
                 const uint32_t ph = (item / p.astages) & 1;
                 const long long d0 = (long long)tile * p.tile_rows + p.d_lead;
-                mbar_wait(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
-                mbar_expect_tx(smem_u32(&ctl->a_full[stage]), p.a_stage_bytes);
-                for (int ch = 0; ch < p.gchunks; ++ch) {
+                mbar_wait_relaxed(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
+                const bool stale = DBG_MODE(2) && item >= p.astages;      // debug: reuse the windows already in shared memory
+                if (stale) mbar_arrive(smem_u32(&ctl->a_full[stage]));
+                else mbar_expect_tx(smem_u32(&ctl->a_full[stage]), p.a_stage_bytes);
+                for (int ch = 0; ch < (stale ? 0 : p.gchunks); ++ch) {
                     const int c = kgi * p.gchunks + ch;                     // chunk of the (concatenated) input
                     const int sidx = c < p.src_chunks[0] ? 0 : 1;
                     const int k = sidx ? c - p.src_chunks[0] : c;
@@ -275,8 +320,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
         // (measured, scripts/mma_microbench.cu: descriptor arithmetic -> R2UR -> UTCHMMA is a serial chain), while the
         // tensor pipe executes one in 56 clk.  Two issuing warps, each owning every other sub-tile (its own TMEM
         // accumulator slot), reach the 56 clk execution bound.  All offsets are precomputed in 16-byte descriptor units.
-        if (lane == 0) {
-            const uint32_t iw = warp - 1;
+        // The issue loop runs warp-convergent (all 32 lanes walk it, only the elected lane executes the tcgen05 / arrive
+        // instructions): descriptor arithmetic then stays in the uniform datapath, and the per-MMA descriptor low words are
+        // taken from tables built once per launch, so an MMA costs a handful of instructions instead of a ~20-instruction
+        // dependent chain (measured: 164 clk per MMA per issuing thread before, against a 56 clk tensor-pipe slot).
+        {
+            const uint32_t iw = (uint32_t)warp - 1u;
+            const bool leader = lane == 0;
             constexpr int NS = K3 ? 9 : 1;
             uint32_t soff[NS];
 #pragma unroll
@@ -295,6 +345,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             if (p.resident) mbar_wait(smem_u32(&ctl->w_res), 0);
             const int gq = p.gchunks >> 1;                       // K16 steps per staged K group
             const uint32_t bshift = (uint32_t)p.nchunks * N;     // weight offset (16-byte units) between (dz,dp) shifts
+            // descriptor low words of the NS x GQ MMAs of one sub-tile and K group (GQ = 2: every 32-wide K group)
+            constexpr int GQF = 2;
+            const uint32_t ahi32 = (uint32_t)(adesc_hi >> 32), bhi32 = (uint32_t)(bdesc_hi >> 32);
+            uint32_t aoff[NS * GQF], boff[NS * GQF];
+#pragma unroll
+            for (int s = 0; s < NS; ++s)
+#pragma unroll
+                for (int q = 0; q < GQF; ++q) {
+                    aoff[s * GQF + q] = (uint32_t)adesc_hi + soff[s] + (uint32_t)q * qstep;
+                    boff[s * GQF + q] = (uint32_t)bdesc_hi + (wbuf_s >> 4) + (uint32_t)s * bshift + (uint32_t)q * bstep;
+                }
+            uint32_t boff1[NS];      // gq == 1: the shift stride of the weights is one K16 step
+#pragma unroll
+            for (int s = 0; s < NS; ++s) boff1[s] = (uint32_t)bdesc_hi + (wbuf_s >> 4) + (uint32_t)s * bshift;
             for (int it = 0; it < my_tiles; ++it) {
                 if (p.resident) {
                     // a tile's K range arrives in ksplit stages; every sub-tile accumulator stays open until the last one
@@ -303,15 +367,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         const int stage = item % p.astages;
                         const uint32_t ph = (item / p.astages) & 1;
                         const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
-                        const uint32_t b_lo0 = (wbuf_s >> 4) + (uint32_t)(kgi * p.gchunks) * N;
+                        const uint32_t b_kg = (uint32_t)(kgi * p.gchunks) * N;
+                        const uint32_t b_lo0 = (wbuf_s >> 4) + b_kg;
                         const long long tA = DBG_T();
                         mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
-                        if (blockIdx.x == 0 && iw == 0) { DBG_ADD(0, DBG_T() - tA); DBG_ADD(3, 1); }
+                        if (blockIdx.x == 0 && iw == 0 && leader) { DBG_ADD(0, DBG_T() - tA); DBG_ADD(3, 1); }
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                         bool issued = false;
                         for (int j = 0; j < p.MT; ++j) {
                             const uint32_t n = cnt + j;
-                            if ((n & 1u) != iw) continue;
+                            if ((DBG_MODE(64) ? 0u : (n & 1u)) != iw) continue;        // debug 64: issuer 0 issues every sub-tile
                             const uint32_t a_lo = a_lo0 + (uint32_t)j * jstep;
                             const uint32_t slot = slot_of(n), tph = phase_of(n);
                             const uint32_t dcol = tmem_base + slot * N;
@@ -321,22 +386,37 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                             }
                             const long long tC = DBG_T();
+                            if (gq == GQF) {
+                                if (!DBG_MODE(128)) {
 #pragma unroll
-                            for (int s = 0; s < NS; ++s) {
-                                uint32_t al = a_lo + soff[s], b_lo = b_lo0 + (uint32_t)s * bshift;
-                                for (int q = 0; q < gq; ++q, al += qstep, b_lo += bstep)
-                                    umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (kgi | s | q) != 0);
+                                    for (int i = 0; i < NS * GQF; ++i)
+                                        umma_f16_elect(dcol, ((uint64_t)ahi32 << 32) | (aoff[i] + a_lo),
+                                                       ((uint64_t)bhi32 << 32) | (boff[i] + b_kg), p.idesc, (kgi | i) != 0);
+                                }
+                            } else if (gq == 1) {        // 16-channel K groups (the init conv): every other table entry
+#pragma unroll
+                                for (int s = 0; s < NS; ++s)
+                                    umma_f16_elect(dcol, ((uint64_t)ahi32 << 32) | (aoff[s * GQF] + a_lo),
+                                                   ((uint64_t)bhi32 << 32) | (boff1[s] + b_kg), p.idesc, (kgi | s) != 0);
+                            } else {
+#pragma unroll
+                                for (int s = 0; s < NS; ++s) {
+                                    uint32_t al = a_lo + soff[s], b_lo = b_lo0 + (uint32_t)s * bshift;
+                                    for (int q = 0; q < gq; ++q, al += qstep, b_lo += bstep)
+                                        if (!DBG_MODE(128)) umma_f16_elect(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (kgi | s | q) != 0);
+                                }
                             }
-                            if (kgi == p.ksplit - 1) umma_commit(smem_u32(&ctl->t_full[slot]));
+                            if (kgi == p.ksplit - 1) umma_commit_elect(smem_u32(&ctl->t_full[slot]));
                             issued = true;
-                            if (blockIdx.x == 0 && iw == 0) { DBG_ADD(1, tC - tB); DBG_ADD(2, DBG_T() - tC); }
+                            if (blockIdx.x == 0 && iw == 0 && leader) { DBG_ADD(1, tC - tB); DBG_ADD(2, DBG_T() - tC); }
                         }
-                        if (issued) umma_commit(smem_u32(&ctl->a_empty[stage]));
-                        else mbar_arrive(smem_u32(&ctl->a_empty[stage]));
+                        if (issued) umma_commit_elect(smem_u32(&ctl->a_empty[stage]));
+                        else mbar_arrive_elect(smem_u32(&ctl->a_empty[stage]));
                     }
                     cnt += p.MT;
                     continue;
                 }
+                if (!leader) { cnt += p.MT; continue; }      // streamed-weight form: the elected lane walks alone
                 const int stage = it % p.astages;
                 const uint32_t ph = (it / p.astages) & 1;
                 const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
@@ -384,7 +464,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     } else {
         // ===================== epilogue: TMEM -> registers -> global (+ GroupNorm statistics) =====================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read (warp id % 4)
-        const int group = (warp - kFirstEpiWarp) >> 2;   // 0 / 1: the two groups alternate sub-tiles
+        const int eset = (warp - kFirstEpiWarp) >> 2;    // 4 sets of 4 warps; each set covers the four lane quarters
+        const int group = eset & 1;               // 0 / 1: the two groups alternate sub-tiles
+        const int half = eset >> 1;               // which half of the block's channels this warp handles (0 when not split)
+        constexpr int HALVES = kHalves<CB, K3>();
+        constexpr int CH = CB / HALVES;           // channels per half
         const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
         float* sbias = xch + kXchFloats;          // bias of this channel block, broadcast-read from shared memory
         float* swsum = sbias + 128;              // folded PreNorm: sum_c W'[o][c]; sbias then holds sum_c W[o][c]*beta[c]
@@ -392,8 +476,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             sbias[c] = p.pn_stats ? __ldg(p.pn_wb + cb * CB + c) : (p.bias ? __ldg(p.bias + cb * CB + c) : 0.f);
             swsum[c] = p.pn_stats ? __ldg(p.pn_wsum + cb * CB + c) : 0.f;
         }
-        asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
-        constexpr int NG = K3 ? CB / CPG : 1;     // statistics groups per channel block
+        asm volatile("bar.sync 5, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        constexpr int NG = K3 ? CH / CPG : 1;     // statistics groups per half of the channel block
+        static_assert(!K3 || CH % CPG == 0, "a GroupNorm group must not straddle the channel halves");
         float gs[NG], gq[NG];                     // this thread's running sum / sum of squares per group (sample cur_b)
 #pragma unroll
         for (int i = 0; i < NG; ++i) { gs[i] = 0.f; gq[i] = 0.f; }
@@ -406,7 +491,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) { s_tot += __shfl_xor_sync(0xffffffffu, s_tot, o); q_tot += __shfl_xor_sync(0xffffffffu, q_tot, o); }
                     if (lane == 0) {
-                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + i * CPG) * 2;
+                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + half * CH + i * CPG) * 2;
                         atomicAdd(d, (double)s_tot);
                         atomicAdd(d + 1, (double)q_tot);
                     }
@@ -415,7 +500,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             }
         };
         const int halo_delta = g.P * g.Rp;
-        const int total_sub = my_tiles * p.MT;
+        const int total_sub = half < HALVES ? my_tiles * p.MT : 0;     // CB not a multiple of 32: the second half idles
         for (int n = group; n < total_sub; n += 2) {
             const int tile = tile_begin + n / p.MT, j = n % p.MT;
             const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
@@ -447,7 +532,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             const bool halo_up = valid && p.write_halo && pp == 1u;               // copy to pp = P+1
             const bool halo_dn = valid && p.write_halo && pp == (uint32_t)g.P;    // copy to pp = 0
             const long long tE0 = DBG_T();
-            mbar_wait(smem_u32(&ctl->t_full[slot]), tph);
+            mbar_wait_relaxed(smem_u32(&ctl->t_full[slot]), tph);
             const long long tE1 = DBG_T();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #ifdef CD_MMA_DEBUG
@@ -460,7 +545,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #endif
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * N;
             if constexpr (K3) {
-                constexpr int CW = CB < 32 ? CB : 32;      // channels recombined per pass (CB = 16, 32, 48, 64)
+                constexpr int CW = 16;                     // channels recombined per pass
+                static_assert(CH % CW == 0, "channel half must be a multiple of 16");
                 const int par = (n >> 1) & 1;
                 float* xup = xch + (size_t)(((group * 2 + par) * 2 + 0) * 4) * 64;
                 float* xdn = xch + (size_t)(((group * 2 + par) * 2 + 1) * 4) * 64;
@@ -476,10 +562,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                 }
 #pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += CW) {
+                for (int cr = 0; cr < CH; cr += CW) {
                     constexpr int W = CW;
-                    const int w = (CB - c0) < W ? (CB - c0) : W;   // 16 for the tail of CB = 48
+                    constexpr int w = W;
+                    const int c0 = half * CH + cr;                 // first channel of this pass within the block
                     uint32_t r0[W], r1[W], r2[W];
+#pragma unroll
+                    for (int k = 0; k < W; ++k) { r0[k] = 0; r1[k] = 0; r2[k] = 0; }
+                    if (!DBG_MODE(32))
 #pragma unroll
                     for (int k = 0; k < W; k += 16) {
                         if (k < w) {
@@ -490,93 +580,98 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                     tmem_ld_wait();
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(9, DBG_T() - tE1);
-                    if (c0 + CW >= CB) {
-                        // last TMEM read of this sub-tile: the accumulator slot is free again
+                    if (cr + CW >= CH) {
+                        // this warp's last TMEM read of the sub-tile: the slot is free once all 4*HALVES warps have arrived
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         __syncwarp();
                         if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
                     }
-                    // publish the rows the neighbouring quarters need, then adopt theirs
-                    if (lane == 31) {
+                    // Neighbour rows: lanes 1..31 take D_0 of row m-1 from lane-1, lanes 0..30 take D_2 of row m+1 from lane+1
+                    // (rotate shuffles).  The two rows that live in the neighbouring lane quarters (another warp) go through shared
+                    // memory: published right after the TMEM loads, read back by lane 0 / lane 31 only AFTER the 32 shuffles, so
+                    // the store -> barrier -> load round trip (slow while the MMAs saturate the shared-memory pipe: it cost 0.19 ms
+                    // of 0.68 when it sat in front of the shuffles) overlaps with them instead of stalling the warp.
+                    // (A split-phase mbarrier with lanes 0 / 31 finished in a second pass measured slower: 0.64 vs 0.50 ms.)
+                    const bool xchg = !DBG_MODE(4) && !DBG_MODE(1024);
+                    if (xchg) {
+                        if (lane == 31) {
 #pragma unroll
-                        for (int k = 0; k < W; k += 4) if (k < w) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
-                    }
-                    if (lane == 0) {
+                            for (int k = 0; k < W; k += 4) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
+                        }
+                        if (lane == 0) {
 #pragma unroll
-                        for (int k = 0; k < W; k += 4) if (k < w) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
-                    }
-                    asm volatile("bar.sync %0, 128;" ::"r"(1 + group) : "memory");
-                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
-                    if (lane == 31) {       // row m-1 of the next quarter's lane 0 is this quarter's lane 31; it receives lane 31's r0 by rotation
-                        const float* src = xup + (q > 0 ? q - 1 : 0) * 64 + c0;
-#pragma unroll
-                        for (int k = 0; k < W; k += 4) if (k < w) { const uint4 u = *reinterpret_cast<const uint4*>(src + k); r0[k] = u.x; r0[k + 1] = u.y; r0[k + 2] = u.z; r0[k + 3] = u.w; }
-                    }
-                    if (lane == 0) {
-                        const float* src = xdn + (q < 3 ? q + 1 : 3) * 64 + c0;
-#pragma unroll
-                        for (int k = 0; k < W; k += 4) if (k < w) { const uint4 u = *reinterpret_cast<const uint4*>(src + k); r2[k] = u.x; r2[k + 1] = u.y; r2[k + 2] = u.z; r2[k + 3] = u.w; }
+                            for (int k = 0; k < W; k += 4) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
+                        }
                     }
                     const int src_up = (lane + 31) & 31, src_dn = (lane + 1) & 31;
                     float acc[W];
 #pragma unroll
                     for (int k = 0; k < W; k += 4) {
-                        if (k < w) {
-                            const float4 bv = *reinterpret_cast<const float4*>(sbias + c0 + k);
-                            const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+                        const float4 bv = *reinterpret_cast<const float4*>(sbias + c0 + k);
+                        const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float u = __uint_as_float(__shfl_sync(0xffffffffu, r0[k + e], src_up));
-                                const float d = __uint_as_float(__shfl_sync(0xffffffffu, r2[k + e], src_dn));
-                                acc[k + e] = (__uint_as_float(r1[k + e]) + bb[e]) + (u + d);
-                            }
+                        for (int e = 0; e < 4; ++e) {
+                            // lane 0's `u` and lane 31's `d` come from the wrong row here; they are replaced below
+                            const uint32_t u = DBG_MODE(4) ? r0[k + e] : __shfl_sync(0xffffffffu, r0[k + e], src_up);
+                            const uint32_t d = DBG_MODE(4) ? r2[k + e] : __shfl_sync(0xffffffffu, r2[k + e], src_dn);
+                            acc[k + e] = __uint_as_float(r1[k + e]) + bb[e];
+                            r0[k + e] = u; r2[k + e] = d;
                         }
                     }
+                    if (xchg) {
+                        if (!DBG_MODE(512)) asm volatile("bar.sync %0, 128;" ::"r"(1 + eset) : "memory");
+                        if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
+                        if (lane == 0 && q > 0) {          // D_0 of the previous quarter's last row
+                            const float* src = xup + (q - 1) * 64 + c0;
+#pragma unroll
+                            for (int k = 0; k < W; k += 4) { const uint4 t = *reinterpret_cast<const uint4*>(src + k); r0[k] = t.x; r0[k + 1] = t.y; r0[k + 2] = t.z; r0[k + 3] = t.w; }
+                        }
+                        if (lane == 31 && q < 3) {         // D_2 of the next quarter's first row
+                            const float* src = xdn + (q + 1) * 64 + c0;
+#pragma unroll
+                            for (int k = 0; k < W; k += 4) { const uint4 t = *reinterpret_cast<const uint4*>(src + k); r2[k] = t.x; r2[k + 1] = t.y; r2[k + 2] = t.z; r2[k + 3] = t.w; }
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < W; ++k) acc[k] += __uint_as_float(r0[k]) + __uint_as_float(r2[k]);
                     if (p.addsrc && valid) {
 #pragma unroll
                         for (int k = 0; k < W; k += 8) {
-                            if (k < w) {
-                                float f[8];
-                                unpack8(load8(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
+                            float f[8];
+                            unpack8(load8(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
 #pragma unroll
-                                for (int e = 0; e < 8; ++e) acc[k + e] += f[e];
-                            }
+                            for (int e = 0; e < 8; ++e) acc[k + e] += f[e];
                         }
                     }
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
 #pragma unroll
                     for (int k = 0; k < W; k += 8) {
-                        if (k < w) {
-                            Half8 h = pack8(acc + k);
-                            if (!keep) h = Half8{};
-                            __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
-                            if (do_store) store8(o, h);
-                            if (halo_up) store8(o + (long long)halo_delta * 8, h);
-                            if (halo_dn) store8(o - (long long)halo_delta * 8, h);
-                        }
+                        Half8 h = pack8(acc + k);
+                        if (!keep) h = Half8{};
+                        __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
+                        if (do_store && !DBG_MODE(8)) store8(o, h);
+                        if (halo_up) store8(o + (long long)halo_delta * 8, h);
+                        if (halo_dn) store8(o - (long long)halo_delta * 8, h);
                     }
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(12, DBG_T() - tE1);
-                    if (p.stats && valid) {
+                    if (p.stats && valid && !DBG_MODE(16)) {
                         if (uniform) {
 #pragma unroll
-                            for (int k = 0; k < W; ++k)
-                                if (k < w) { gs[(c0 + k) / CPG] += acc[k]; gq[(c0 + k) / CPG] = fmaf(acc[k], acc[k], gq[(c0 + k) / CPG]); }
+                            for (int k = 0; k < W; ++k) { gs[(cr + k) / CPG] += acc[k]; gq[(cr + k) / CPG] = fmaf(acc[k], acc[k], gq[(cr + k) / CPG]); }
                         } else {
                             // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
 #pragma unroll
                             for (int k = 0; k < W; ++k) {
-                                if (k < w) {
-                                    double* d = p.stats + ((long long)sample * p.Cout + cb * CB + ((c0 + k) / CPG) * CPG) * 2;
-                                    atomicAdd(d, (double)acc[k]);
-                                    atomicAdd(d + 1, (double)(acc[k] * acc[k]));
-                                }
+                                double* d = p.stats + ((long long)sample * p.Cout + cb * CB + ((c0 + k) / CPG) * CPG) * 2;
+                                atomicAdd(d, (double)acc[k]);
+                                atomicAdd(d + 1, (double)(acc[k] * acc[k]));
                             }
                         }
                     }
                 }
             } else {
                 // 1x1x1: no recombination, no statistics: batches of up to 48 columns with all TMEM loads in flight at once
-                constexpr int BW = (CB % 48 == 0) ? 48 : ((CB % 32 == 0) ? 32 : 16);
+                constexpr int BW = (CH % 48 == 0) ? 48 : ((CH % 32 == 0) ? 32 : 16);
                 // folded PreNorm: y = rstd*acc + (wb - mean*rstd*wsum), statistics of this row's sample
                 float pn_a = 1.f, pn_m = 0.f;
                 if (p.pn_stats && inrange) {
@@ -588,12 +683,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     pn_m = -(float)mean * pn_a;
                 }
 #pragma unroll
-                for (int c0 = 0; c0 < CB; c0 += BW) {
+                for (int cr = 0; cr < CH; cr += BW) {
+                    const int c0 = half * CH + cr;
                     uint32_t r1[BW];
 #pragma unroll
                     for (int k = 0; k < BW; k += 16) tmem_ld16_issue(taddr + c0 + k, r1 + k);
                     tmem_ld_wait();
-                    if (c0 + BW >= CB) {
+                    if (cr + BW >= CH) {
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         __syncwarp();
                         if (lane == 0) mbar_arrive(smem_u32(&ctl->t_empty[slot]));
@@ -770,7 +866,8 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     //    With K staged in groups all of a tile's accumulators stay open together: keep one slot free for the epilogue.
     for (int ksplit = 1; ksplit <= 8 && !found; ksplit *= 2) {
         if (p.nchunks % ksplit != 0 || (p.nchunks / ksplit) % 2 != 0) continue;
-        const int mt_max = ksplit > 1 ? (p.nacc - 1 < 4 ? p.nacc - 1 : 4) : 4;
+        int mt_max = ksplit > 1 ? (p.nacc - 1 < 4 ? p.nacc - 1 : 4) : 4;
+        if (const char* e = getenv("CD_MMA_MT")) { const int v = atoi(e); if (v >= 1 && v < mt_max) mt_max = v; }   // diagnostics
         for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
             for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
     }

@@ -17,7 +17,7 @@ y = torch.zeros(B, Cout, *list(z), device="cuda")
 w = (torch.randn(Cout, Cin, 3, 3, 3) / 30).contiguous(); b = torch.randn(Cout).contiguous()
 ks = (C.c_int * 3)(3, 3, 3); st = (C.c_int * 3)(1, 1, 1)
 out = (C.c_longlong * 16)()
-for mode in (0, 2):
+for mode in ([int(a) for a in sys.argv[5].split(',')] if len(sys.argv) > 5 else (0, 2)):
     os.environ["CD_DBG_MODE"] = str(mode)
     for rep in range(2):
         lib.cd_debug_counters(out, 1)

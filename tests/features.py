@@ -14,7 +14,9 @@ def shower_features(data, e_inc, shape_zpr):
     f = {}
     f["total_E"] = tot                                                        # :885-898
     f["Edep_over_Einc"] = tot / np.asarray(e_inc, dtype=np.float64).reshape(-1)   # :406-425
-    f["n_hits"] = (d > 1e-3 * d.max()).sum((1, 2, 3)).astype(np.float64)      # :913-916 (threshold relative: random weights)
+    # :913-916 counts voxels above 1e-3 GeV; with random weights the scale is arbitrary, so the threshold is relative to the
+    # shower's own largest voxel (a per-shower quantity: comparable between independently sampled sets)
+    f["n_hits"] = (d > 1e-3 * d.reshape(n, -1).max(1).reshape(n, 1, 1, 1)).sum((1, 2, 3)).astype(np.float64)
     f["depth_mean"] = (layer * np.arange(Z)).sum(1) / safe                    # energy-weighted layer index
     f["depth_width"] = np.sqrt(np.maximum((layer * np.arange(Z) ** 2).sum(1) / safe - f["depth_mean"] ** 2, 0))
     rprof = d.sum((1, 2))                                                     # :619-625
