@@ -53,6 +53,16 @@ class ReverseNormDesc(C.Structure):
     ]
 
 
+class ReverseNormExDesc(C.Structure):
+    _fields_ = [
+        ("nseg", C.c_int), ("total", C.c_int), ("map_kind", C.c_int), ("a_scale", C.c_float), ("a_shift", C.c_float),
+        ("alpha", C.c_float), ("log_cap", C.c_float), ("post_scale", C.c_float), ("post_shift", C.c_float),
+        ("totalE_mean", C.c_float), ("totalE_std", C.c_float), ("layers_mean", C.c_float), ("layers_std", C.c_float),
+        ("guard_eps", C.c_float), ("energy_mode", C.c_int), ("emin", C.c_float), ("emax", C.c_float),
+        ("max_deposit", C.c_float), ("ecut", C.c_float), ("e_stride", C.c_int), ("final_scale", C.c_int),
+    ]
+
+
 class LibraryMissing(RuntimeError):
     pass
 
@@ -92,6 +102,8 @@ def load():
     lib.cd_sample_run.argtypes = [vp, vp, f32, vp, C.POINTER(Eval), i32, vp, u64, i32, i32, vp, vp, vp, i32, vp, i32]
     lib.cd_fill_normal.argtypes = [vp, i64, i64, u64, i32, i32, vp]
     lib.cd_reverse_norm.argtypes = [C.POINTER(ReverseNormDesc), vp, vp, vp, vp, vp, i32, vp]
+    lib.cd_reverse_norm_ex.argtypes = [C.POINTER(ReverseNormExDesc), vp, vp, vp, vp, vp, vp, i32, vp]
+    lib.cd_geom_decode_sparse.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp, i32, i32, u64, vp, vp]
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
     lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]

@@ -187,8 +187,8 @@ class CaloDiffusion(Diffusion):
 
     def init_embedding_model(self, embed=None):
         """models/calodiffusion.py:100-119.  Dataset 1: NNConverter from the binning XML (`BIN_FILE`).  HGCal without
-        pre-embedding: the reference builds HGCalConverter from a geometry pickle on the host; here the per-layer matrices
-        come in through config['GEOM_EMBED'] = dict(enc_mat, dec_mat[, enc_mask, dec_mask]) (geometry.MatrixConverter)."""
+        pre-embedding: HGCalConverter built from the geometry pickle `BIN_FILE` (geometry.HGCalConverter), or, when
+        config['GEOM_EMBED'] = dict(enc_mat, dec_mat[, enc_mask, dec_mask]) is given, those matrices (geometry.MatrixConverter)."""
         cfg = self.config
         shower_embed = cfg.get("SHOWER_EMBED", "")
         if "NN" in shower_embed and not self.hgcal:
@@ -197,11 +197,15 @@ class CaloDiffusion(Diffusion):
             return geometry.NNConverter(bins=bins).to(device=self.device)
         if self.hgcal and not self.pre_embed:
             mats = cfg.get("GEOM_EMBED")
-            if mats is None:
-                raise ValueError("HGCal in-loop embedding needs config['GEOM_EMBED'] (enc_mat, dec_mat of the reference's "
-                                 "HGCalConverter); building them from the geometry pickle is host code outside the B200 path")
-            return geometry.MatrixConverter(cfg["SHAPE_FINAL"], mats["enc_mat"], mats["dec_mat"], mats.get("enc_mask"),
-                                            mats.get("dec_mask"), trainable=cfg.get("TRAINABLE_EMBED", False)).to(self.device)
+            trainable = cfg.get("TRAINABLE_EMBED", False)
+            if mats is not None:      # matrices handed in directly (a checkpoint's, or a test's)
+                return geometry.MatrixConverter(cfg["SHAPE_FINAL"], mats["enc_mat"], mats["dec_mat"], mats.get("enc_mask"),
+                                                mats.get("dec_mask"), trainable=trainable).to(self.device)
+            # models/calodiffusion.py:113-117: the GLaM maps built from the geometry pickle named by BIN_FILE
+            conv = geometry.HGCalConverter(bins=cfg["SHAPE_FINAL"], geom_file=cfg["BIN_FILE"], device=self.device, trainable=trainable)
+            if not trainable:
+                conv.init(norm=self.pre_embed, dataset_num=self.dataset_num)
+            return conv.to(self.device)
         return None
 
     def noise_generation(self, shape):

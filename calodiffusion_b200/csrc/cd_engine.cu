@@ -1111,21 +1111,59 @@ int cd_geom_apply(const int32_t* rowptr_dev, const int32_t* col_dev, const float
     return 0;
 }
 
-int cd_reverse_norm(const cd_reverse_norm_desc* d, const float* vox_dev, const float* e_dev, const float* layerE_dev,
-                    float* out_dev, float* energy_out_dev, int B, void* stream) {
+int cd_reverse_norm_ex(const cd_reverse_norm_ex_desc* d, const int32_t* seg_dev, const float* vox_dev, const float* e_dev,
+                       const float* layerE_dev, float* out_dev, float* energy_out_dev, int B, void* stream) {
     if (!d || !vox_dev || !e_dev || !out_dev) return fail("null argument");
     if (cd_device_check()) return 1;
-    if (B < 1 || B > 65535 || d->Z < 1 || d->Z > 65535 || d->PR < 1) return fail("bad reverse_norm shape");
-    if (!(d->emin > 0.f) || !(d->emax > 0.f) || !(d->logit_std > 0.f)) return fail("bad reverse_norm constants");
+    if (B < 1 || B > 65535 || d->nseg < 1 || d->nseg > 65535 || d->total < d->nseg) return fail("bad reverse_norm shape");
+    if (!seg_dev && d->total % d->nseg != 0) return fail("reverse_norm: %d values do not split into %d equal layers", d->total, d->nseg);
+    if (d->map_kind < 0 || d->map_kind > 2) return fail("reverse_norm: unknown map kind %d", d->map_kind);
+    if (d->energy_mode == 0 && (!(d->emin > 0.f) || !(d->emax > 0.f))) return fail("bad reverse_norm constants");
+    if (d->e_stride < 1) return fail("reverse_norm: e_stride must be >= 1");
     RevNormParams p;
-    p.vox = vox_dev; p.e = e_dev; p.layerE = layerE_dev; p.out = out_dev; p.energy_out = energy_out_dev;
-    p.Z = d->Z; p.PR = d->PR;
-    p.logit_mean = d->logit_mean; p.logit_std = d->logit_std; p.totalE_mean = d->totalE_mean; p.totalE_std = d->totalE_std;
-    p.layers_mean = d->layers_mean; p.layers_std = d->layers_std; p.emin = d->emin; p.emax = d->emax;
-    p.max_deposit = d->max_deposit; p.ecut = d->ecut;
+    p.vox = vox_dev; p.e = e_dev; p.e_stride = d->e_stride; p.layerE = layerE_dev; p.out = out_dev; p.energy_out = energy_out_dev;
+    p.nseg = d->nseg; p.total = d->total; p.seg = seg_dev; p.map_kind = d->map_kind;
+    p.a_scale = d->a_scale; p.a_shift = d->a_shift; p.alpha = d->alpha; p.log_cap = d->log_cap;
+    p.post_scale = d->post_scale; p.post_shift = d->post_shift;
+    p.totalE_mean = d->totalE_mean; p.totalE_std = d->totalE_std; p.layers_mean = d->layers_mean; p.layers_std = d->layers_std;
+    p.guard_eps = d->guard_eps; p.energy_mode = d->energy_mode; p.emin = d->emin; p.emax = d->emax;
+    p.max_deposit = d->max_deposit; p.ecut = d->ecut; p.final_scale = d->final_scale;
     launch_reverse_norm(p, B, (cudaStream_t)stream);
     cudaError_t e = cudaPeekAtLastError();
     if (e != cudaSuccess) return fail("reverse_norm: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int cd_reverse_norm(const cd_reverse_norm_desc* d, const float* vox_dev, const float* e_dev, const float* layerE_dev,
+                    float* out_dev, float* energy_out_dev, int B, void* stream) {
+    if (!d) return fail("null argument");
+    if (d->Z < 1 || d->Z > 65535 || d->PR < 1) return fail("bad reverse_norm shape");
+    if (!(d->emin > 0.f) || !(d->emax > 0.f) || !(d->logit_std > 0.f)) return fail("bad reverse_norm constants");
+    cd_reverse_norm_ex_desc x;
+    memset(&x, 0, sizeof(x));
+    x.nseg = d->Z; x.total = d->Z * d->PR; x.map_kind = 0; x.a_scale = d->logit_std; x.a_shift = d->logit_mean; x.alpha = 1e-6f;
+    x.post_scale = 1.f; x.post_shift = 0.f;
+    x.totalE_mean = d->totalE_mean; x.totalE_std = d->totalE_std; x.layers_mean = d->layers_mean; x.layers_std = d->layers_std;
+    x.guard_eps = 1e-6f; x.energy_mode = 0; x.emin = d->emin; x.emax = d->emax; x.max_deposit = d->max_deposit; x.ecut = d->ecut;
+    x.e_stride = 1; x.final_scale = 1;
+    return cd_reverse_norm_ex(&x, nullptr, vox_dev, e_dev, layerE_dev, out_dev, energy_out_dev, B, stream);
+}
+
+int cd_geom_decode_sparse(const int32_t* colptr_dev, const int32_t* row_dev, const float* val_dev, int n_cols, int n_rows,
+                          int cells_per_layer, int bins_per_layer, const float* x_dev, float* out_dev, int B, int per_batch,
+                          uint64_t seed, const float* u_bank_dev, void* stream) {
+    if (!colptr_dev || !row_dev || !val_dev || !x_dev || !out_dev) return fail("null argument");
+    if (cd_device_check()) return 1;
+    if (n_cols < 1 || n_rows < 1 || B < 1 || cells_per_layer < 1 || bins_per_layer < 1 || n_cols % bins_per_layer ||
+        n_rows % cells_per_layer || n_cols / bins_per_layer != n_rows / cells_per_layer)
+        return fail("bad sparse decode shape (%d bins, %d cells, %d / %d per layer)", n_cols, n_rows, bins_per_layer, cells_per_layer);
+    SparseDecParams p;
+    p.colptr = colptr_dev; p.row = row_dev; p.val = val_dev; p.n_cols = n_cols; p.n_rows = n_rows;
+    p.cells_per_layer = cells_per_layer; p.bins_per_layer = bins_per_layer; p.x = x_dev; p.out = out_dev;
+    p.per_batch = per_batch; p.seed = seed; p.u_bank = u_bank_dev;
+    launch_sparse_decode(p, B, (cudaStream_t)stream);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("sparse decode: %s", cudaGetErrorString(e));
     return 0;
 }
 

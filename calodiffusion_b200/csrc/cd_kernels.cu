@@ -545,6 +545,60 @@ void launch_geom_apply(const GeomMap& m, const float* x, float* y, int B, cudaSt
     geom_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m, x, y, n);
 }
 
+// Sampled GLaM decoding (generate_sparse_mat, HGCal_utils.py:355-407, applied as in Decoder.forward :344-346).
+// Thread = (shower b, grid bin c).  Over the bin's positive decoder entries (cells n with w > 1e-6): r = u + w with
+// u ~ U[0,1); the entries with r > 1 and the one with the largest r are kept, and the bin's energy is split equally
+// between them (atomicAdd into the cell vector: several bins feed one cell).
+__device__ __forceinline__ float philox_uniform(uint64_t seed, uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t c0 = c, c1 = a, c2 = b, c3 = 0x53504152u;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        philox_round(c0, c1, c2, c3, k0, k1);
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return (float)(c0 >> 8) * 5.9604644775390625e-8f;     // [0, 1): 24 random bits, like torch.rand for float32
+}
+
+__global__ void __launch_bounds__(256) sparse_decode_kernel(SparseDecParams p, long long n) {
+    long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const int b = (int)(v / p.n_cols);
+    const int c = (int)(v - (long long)b * p.n_cols);
+    const int k0 = p.colptr[c], k1 = p.colptr[c + 1];
+    if (k0 == k1) return;                                  // bin without cells: its energy is dropped (mask, :393)
+    const float x = p.x[v];
+    const int rb = p.per_batch ? 0 : b;
+    const int l = c / p.bins_per_layer, e = c - l * p.bins_per_layer;
+    auto draw = [&](int k) -> float {
+        const int nloc = p.row[k] - l * p.cells_per_layer;
+        float u;
+        if (p.u_bank) u = p.u_bank[(((long long)rb * (p.n_cols / p.bins_per_layer) + l) * p.cells_per_layer + nloc) * p.bins_per_layer + e];
+        else u = philox_uniform(p.seed, (uint32_t)rb, (uint32_t)c, (uint32_t)nloc);
+        return u + p.val[k];
+    };
+    int best = k0, count = 0;
+    float rbest = -1.f;
+    for (int k = k0; k < k1; ++k) {                        // entries are stored in increasing cell order: first maximum wins (argmax)
+        const float r = draw(k);
+        if (r > rbest) { rbest = r; best = k; }
+        if (r > 1.f) ++count;
+    }
+    if (!(rbest > 1.f)) ++count;                           // the forced entry was not selected by itself
+    const float share = x / (float)count;
+    float* ob = p.out + (long long)b * p.n_rows;
+    for (int k = k0; k < k1; ++k) {
+        const float r = draw(k);
+        if (r > 1.f || k == best) atomicAdd(ob + p.row[k], share);
+    }
+}
+
+void launch_sparse_decode(const SparseDecParams& p, int B, cudaStream_t st) {
+    cudaMemsetAsync(p.out, 0, (size_t)B * p.n_rows * sizeof(float), st);
+    long long n = (long long)B * p.n_cols;
+    sparse_decode_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, n);
+}
+
 void launch_geom_decode(const FinalParams& p, const GeomMap& dec, const float* grid_pred, int B, cudaStream_t st) {
     long long nvox = (long long)B * dec.n_rows;
     geom_decode_kernel<<<(unsigned)((nvox + 255) / 256), 256, 0, st>>>(p, dec, grid_pred, nvox);

@@ -49,12 +49,27 @@ struct LayerMlpParams {
 };
 
 struct RevNormParams {
-    const float* vox; const float* e; const float* layerE;   // (B,Z,PR), (B), (B,Z+1) or nullptr
-    float* out; float* energy_out;                          // (B,Z*PR), (B) or nullptr
-    int Z, PR;
-    float logit_mean, logit_std, totalE_mean, totalE_std, layers_mean, layers_std;
+    const float* vox; const float* e; int e_stride; const float* layerE;   // (B,total), (B,e_stride), (B,nseg+1) or nullptr
+    float* out; float* energy_out;                                         // (B,total), (B) or nullptr
+    int nseg, total;                      // calorimeter layers ("segments") per shower, values per shower
+    const int* seg;                       // device [nseg+1] segment offsets, or nullptr: nseg equal segments
+    int map_kind;                         // 0 reverse logit, 1 exp (log maps), 2 identity
+    float a_scale, a_shift, alpha, log_cap, post_scale, post_shift;
+    float totalE_mean, totalE_std, layers_mean, layers_std, guard_eps;
+    int energy_mode;                      // 0: emin*(emax/emin)^e, 1: emin + (emax-emin)*e
     float emin, emax, max_deposit, ecut;
+    int final_scale;                      // 1: multiply by max_deposit * E_inc (0 for an intermediate stage)
 };
+// sampled ("sparse") GLaM decoding: CSC of the positive decoder entries, see cd_kernels.cu
+struct SparseDecParams {
+    const int* colptr; const int* row; const float* val;   // per grid bin c: cells row[k] (global index l*N+n) with weights val[k]
+    int n_cols, n_rows, cells_per_layer, bins_per_layer;
+    const float* x; float* out;            // (B, n_cols) grid energies -> (B, n_rows) cell energies (zeroed by the launcher)
+    int per_batch;                         // 1: one sampled matrix shared by the whole batch
+    unsigned long long seed;
+    const float* u_bank;                   // optional uniforms laid out like the reference's rand_like: [b][l][n][e]
+};
+void launch_sparse_decode(const SparseDecParams& p, int B, cudaStream_t st);
 void launch_reverse_norm(const RevNormParams& p, int B, cudaStream_t st);
 
 void launch_prep_input(const Geom& g, const float* x, const float* sigma, int sigma_stride, float sigma_data,

@@ -11,7 +11,10 @@ inside every denoiser evaluation (prep_input_geom_kernel / geom_decode_kernel). 
   NNConverter     <- utils/utils.py:575-656   (Dataset 1; trainable per-layer Linear maps `encs.i.weight`, `decs.i.weight`)
   MatrixConverter <- utils/HGCal_utils.py:296-349, 636-663 (Embeder / Decoder of HGCalConverter: per-layer dense
                      matrices `enc_mat (L,E,N)`, `dec_mat (L,N,E)` with boolean masks)
+  HGCalConverter  <- utils/HGCal_utils.py:412-690 (the GLaM maps built from the HGCal geometry pickle: load_geom, init_map,
+                     init; enc / dec with the optional normalisation; sampled "sparse" decoding, generate_sparse_mat :355-407)
 """
+import pickle
 import xml.etree.ElementTree as ET
 
 import numpy as np
@@ -225,10 +228,14 @@ class MatrixConverter(nn.Module, _DeviceMaps):
         if trainable:
             self.enc_mat, self.dec_mat = nn.Parameter(enc_mat), nn.Parameter(dec_mat)
         else:
-            self.register_buffer("enc_mat", enc_mat)
-            self.register_buffer("dec_mat", dec_mat)
-        self.register_buffer("enc_mask", torch.ones_like(enc_mat, dtype=torch.bool) if enc_mask is None else torch.as_tensor(enc_mask, dtype=torch.bool))
-        self.register_buffer("dec_mask", torch.ones_like(dec_mat, dtype=torch.bool) if dec_mask is None else torch.as_tensor(dec_mask, dtype=torch.bool))
+            # plain tensors in the reference (not in its state_dict): non-persistent buffers, so they follow .to(device) but a
+            # reference checkpoint still loads with strict=True
+            self.register_buffer("enc_mat", enc_mat, persistent=False)
+            self.register_buffer("dec_mat", dec_mat, persistent=False)
+        self.register_buffer("enc_mask", torch.ones_like(enc_mat, dtype=torch.bool) if enc_mask is None else torch.as_tensor(enc_mask, dtype=torch.bool),
+                             persistent=False)
+        self.register_buffer("dec_mask", torch.ones_like(dec_mat, dtype=torch.bool) if dec_mask is None else torch.as_tensor(dec_mask, dtype=torch.bool),
+                             persistent=False)
 
     def _weights_version(self):
         return (self.enc_mat._version, self.dec_mat._version, self.enc_mat.data_ptr(), self.dec_mat.data_ptr())
@@ -259,3 +266,197 @@ class MatrixConverter(nn.Module, _DeviceMaps):
 
     def forward(self, x):
         return self.enc(x)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# HGCal: GLaM maps from the geometry pickle
+# ------------------------------------------------------------------------------------------------------------------
+class _GeoStub:
+    """Stand-in for the pickled `HGCalGeo` instance (plain attributes: ncells, nlayers, xmap, ymap, ring_map, ...)."""
+
+
+class _GeoUnpickler(pickle.Unpickler):
+    # the pickle names its class as `HGCalGeo.HGCalGeo` (HGCal_utils.py:488-496 renames the module); only its __dict__ is needed
+    def find_class(self, module, name):
+        if module.split(".")[-1] == "HGCalGeo":
+            return _GeoStub
+        return super().find_class(module, name)
+
+
+def load_hgcal_geom(geom_filename):
+    """HGCal_utils.py:503-514: the geometry object plus theta_map (angle of every cell, arctan2(x, y) mod 2pi) and max_ncell."""
+    with open(geom_filename, "rb") as f:
+        geom = _GeoUnpickler(f).load()
+    geom.theta_map = np.arctan2(geom.xmap, geom.ymap) % (2.0 * np.pi)
+    geom.max_ncell = int(round(np.amax(geom.ncells)))
+    return geom
+
+
+def init_glam_map(num_alpha_bins, num_r_bins, geom, ilay):
+    """HGCal_utils.py:412-486 (init_map): the initial GLaM weight matrix (A*R, max_ncell) of one layer and its trainable-
+    neighbourhood mask.  Every cell goes to the (angle bin, ring bin) it sits in - rings 0..22 one bin each, three rings per
+    bin beyond - cells within 1e-2 rad of an angular bin edge are split half / half over the two bins, cell 0 (the centre)
+    is spread over all angle bins of the first ring bin.  Same arithmetic as the reference's per-cell loop, vectorised."""
+    dim_in = geom.max_ncell
+    ncells = int(round(geom.ncells[ilay]))
+    A, R = int(num_alpha_bins), int(num_r_bins)
+    weight = np.zeros((A, R, dim_in), np.float32)
+    mask = np.zeros((A, R, dim_in), np.float32)
+    inner, max_ring, outer_step = 23, 100, 3
+    r_binning = np.arange(0, max_ring, 1)
+    r_binning[inner:] = (r_binning[inner:] - inner) // outer_step + inner
+    # torch float32 arithmetic of the reference (:431-446), kept in torch so the bin edges round identically
+    step_size = 2.0 * np.pi / A
+    ang_bins = torch.arange(0, 2.0 * np.pi + step_size, step_size)
+    ang_bins += np.pi / A
+    eps, eps2 = 1e-4, 1e-2
+    cell_alphas = torch.tensor(geom.theta_map[ilay][:dim_in])
+    cell_ang_bins = torch.bucketize(cell_alphas + eps, ang_bins, right=True)
+    cell_ang_bins[cell_ang_bins == A] = 0
+    diffs = torch.abs(cell_alphas - ang_bins[cell_ang_bins - 1])
+    close = ((diffs < eps2) | (torch.abs(diffs - 2.0 * np.pi) < eps2)).numpy()
+    cab = cell_ang_bins.numpy()
+    weight[:, 0, 0] = 1.0 / A
+    mask[:, 0, 0] = 1.0
+    i = np.arange(1, ncells)
+    a = cab[i] % A
+    r = r_binning[np.rint(geom.ring_map[ilay, i]).astype(np.int64)]
+    am1 = (a - 1) % A                       # the reference indexes a_bin - 1 = -1 (wraps to the last bin)
+    c = close[i]
+    lo, hi = r > 0, r < R - 1
+    # cells on an angular bin edge (:456-470)
+    ic, ac, a1c, rc = i[c], a[c], am1[c], r[c]
+    weight[ac, rc, ic] = 0.5
+    weight[a1c, rc, ic] = 0.5
+    mask[ac, rc, ic] = 1.0
+    mask[ac[lo[c]], rc[lo[c]] - 1, ic[lo[c]]] = 1.0
+    mask[ac[hi[c]], rc[hi[c]] + 1, ic[hi[c]]] = 1.0
+    mask[a1c, rc, ic] = 1.0
+    mask[a1c[lo[c]], rc[lo[c]] - 1, ic[lo[c]]] = 1.0
+    mask[a1c[hi[c]], rc[hi[c]] - 1, ic[hi[c]]] = 1.0          # (:469-470 writes r_bin - 1 again; kept)
+    # all other cells (:472-483)
+    n = ~c
+    i_n, an, rn = i[n], a[n], r[n]
+    weight[an, rn, i_n] = 1.0
+    mask[an, rn, i_n] = 1.0
+    mask[(an - 1) % A, rn, i_n] = 1.0
+    mask[(an + 1) % A, rn, i_n] = 1.0
+    mask[an[lo[n]], rn[lo[n]] - 1, i_n[lo[n]]] = 1.0
+    mask[an[hi[n]], rn[hi[n]] + 1, i_n[hi[n]]] = 1.0
+    return torch.from_numpy(weight.reshape(A * R, dim_in)), torch.from_numpy(mask.reshape(A * R, dim_in))
+
+
+class HGCalConverter(MatrixConverter):
+    """HGCal_utils.py:517-690: irregular HGCal cells (B, 1, L, max_ncell) <-> the regular (B, 1, L, A, R) grid through the
+    per-layer GLaM matrices built from the geometry pickle (`geom_file`, config['BIN_FILE']).  `init()` fills them:
+    enc = init_glam_map, dec = its pseudo-inverse (host LAPACK, float32, as the reference); enc / dec run on the device.
+
+    Device representation of the decoder: the pseudo-inverse is numerically dense (round-off ~1e-9 in 11.7 M of 14 M entries,
+    total magnitude 0.07); the reference's own inverse mask keeps |v| > 1e-6 (:607), and those 79 k entries are what the CSR
+    holds - outputs differ from the dense einsum by < 1e-6 relative."""
+    DEC_EPS = 1e-6
+
+    def __init__(self, bins=None, geom_file=None, hidden_size=32, device=None, trainable=False):
+        self.geom = load_hgcal_geom(geom_file)
+        L, A, R = int(bins[-3]), int(bins[-2]), int(bins[-1])
+        N = self.geom.max_ncell
+        super().__init__(bins, torch.zeros(L, A * R, N), torch.zeros(L, N, A * R), torch.zeros(L, A * R, N, dtype=torch.bool),
+                         torch.zeros(L, N, A * R, dtype=torch.bool), trainable=trainable)
+        self.bins = bins
+        self.norm = False
+        self.embed_mean, self.embed_std = 0.0, 1.0
+        self._sparse = None
+        if device is not None:
+            self.to(device)
+
+    def init(self, noise_scale=0.0, norm=False, dataset_num=101):
+        """HGCal_utils.py:590-634."""
+        from .postprocess import DATASET_PARAMS
+        with torch.no_grad():
+            for i in range(int(self.geom.nlayers)):
+                conv_map, mask = init_glam_map(self.num_alpha_bins, self.num_r_bins, self.geom, i)
+                inv_init = torch.linalg.pinv(conv_map)
+                eps = 1e-6
+                inv_mask = torch.abs(inv_init) > eps
+                if noise_scale > 0.0:
+                    conv_map = conv_map + torch.randn_like(conv_map) * noise_scale
+                    inv_init = inv_init + eps * torch.randn_like(inv_init)
+                self.enc_mat[i] = conv_map.to(self.enc_mat.device)
+                self.enc_mask[i] = (mask > eps).to(self.enc_mask.device)
+                self.dec_mat[i] = inv_init.to(self.dec_mat.device)
+                self.dec_mask[i] = inv_mask.to(self.dec_mask.device)
+        self._init_count = getattr(self, "_init_count", 0) + 1
+        self._sparse = None
+        if norm:
+            self.norm = True
+            c = DATASET_PARAMS[dataset_num]
+            self.embed_mean, self.embed_std = c["embed_mean"], c["embed_std"]
+
+    def _weights_version(self):
+        return super()._weights_version() + (getattr(self, "_init_count", 0),)
+
+    def csr_maps(self):
+        enc, _ = super().csr_maps()
+        m = self.dec_mat.detach().cpu().numpy()
+        if self.trainable:
+            m = m * self.dec_mask.cpu().numpy()
+        L, N, E = m.shape
+        l, r, c = np.nonzero(np.abs(m) > self.DEC_EPS)
+        return enc, _csr_from_coo(L * N, L * E, l * N + r, l * E + c, m[l, r, c])
+
+    def enc(self, x):
+        out = super().enc(x)
+        if self.norm:                                   # :636-640
+            out = (out - self.embed_mean) / self.embed_std
+        return out
+
+    def _sparse_csc(self, device):
+        """CSC over grid bins of the decoder's positive entries (w > 1e-6, generate_sparse_mat's `mask`)."""
+        key = (str(device), self._weights_version())
+        if self._sparse is None or self._sparse[0] != key:
+            m = self.dec_mat.detach().cpu().numpy()
+            if self.trainable:
+                m = m * self.dec_mask.cpu().numpy()
+            L, N, E = m.shape
+            l, n, e = np.nonzero(m > 1e-6)
+            t = _csr_from_coo(L * E, L * N, l * E + e, l * N + n, m[l, n, e])     # CSR of the transpose = CSC, cells ascending
+            to = lambda a: torch.from_numpy(a).to(device)
+            self._sparse = (key, dict(colptr=to(t["rowptr"]), row=to(t["col"]), val=to(t["val"]), n_cols=L * E, n_rows=L * N))
+        return self._sparse[1]
+
+    def dec(self, x, sparse_decoding=False, sparse_per_batch=False, seed=None, u_bank=None):
+        """(B, 1, L, A, R) -> (B, 1, L, N)   HGCal_utils.py:340-349, 659-663.  sparse_decoding: every grid bin's energy goes to a
+        random subset of its cells (generate_sparse_mat); the draw comes from the library's Philox stream (`seed`, default
+        from torch's RNG) or, for parity tests, from `u_bank` laid out like the reference's rand_like(in_mat)."""
+        if self.norm:
+            x = (x * self.embed_std) + self.embed_mean
+        if not sparse_decoding:
+            return super().dec(x)
+        from . import _lib
+        lib = _lib.load()
+        if not x.is_cuda:
+            raise RuntimeError("geometry enc/dec run in the CUDA library: pass a CUDA tensor (there is no CPU path)")
+        m = self._sparse_csc(x.device)
+        B = x.shape[0]
+        xin = x.to(torch.float32).reshape(B, m["n_cols"]).contiguous()
+        out = torch.empty((B, m["n_rows"]), device=x.device, dtype=torch.float32)
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        ub = None if u_bank is None else u_bank.to(device=x.device, dtype=torch.float32).contiguous()
+        _lib.check(lib.cd_geom_decode_sparse(m["colptr"].data_ptr(), m["row"].data_ptr(), m["val"].data_ptr(), m["n_cols"], m["n_rows"],
+                                             self.max_ncell, self.num_alpha_bins * self.num_r_bins, xin.data_ptr(), out.data_ptr(), B,
+                                             int(bool(sparse_per_batch)), int(seed) & (2 ** 64 - 1),
+                                             ub.data_ptr() if ub is not None else None,
+                                             torch.cuda.current_stream().cuda_stream), "geom_decode_sparse")
+        return out.reshape(B, 1, self.num_layers, self.max_ncell)
+
+    def dec_batches(self, x, batch_size=128, sparse_decoding=False, sparse_per_batch=False):
+        """:665-680 - numpy in, numpy out, in batches."""
+        dev = self.enc_mat.device
+        outs = [self.dec(torch.as_tensor(x[lo:lo + batch_size]).to(dev), sparse_decoding, sparse_per_batch).cpu().numpy()
+                for lo in range(0, len(x), batch_size)]
+        return np.concatenate(outs)
+
+    def enc_batches(self, x, batch_size=256):
+        dev = self.enc_mat.device
+        return np.concatenate([self.enc(torch.as_tensor(x[lo:lo + batch_size]).to(dev)).cpu().numpy() for lo in range(0, len(x), batch_size)])

@@ -155,10 +155,42 @@ typedef struct cd_reverse_norm_desc {
     float emin, emax;                 /* incident energy = emin*(emax/emin)^e (logE) */
     float max_deposit, ecut;          /* ecut <= 0: no threshold */
 } cd_reverse_norm_desc;
-/* vox_dev (B,Z,PR) network-space showers, e_dev (B) scaled incident energies, layerE_dev (B,Z+1) = [totalE, layers] or
- * NULL; writes out_dev (B,Z*PR) deposited energies and, if not NULL, energy_out_dev (B) incident energies. */
+/* ReverseNormCaloChall for datasets 2 / 3 in network shape (utils/utils.py:446-573): vox_dev (B,Z,PR) network-space showers,
+ * e_dev (B) scaled incident energies, layerE_dev (B,Z+1) = [totalE, layers] or NULL; writes out_dev (B,Z*PR) deposited
+ * energies and, if not NULL, energy_out_dev (B) incident energies. */
 int cd_reverse_norm(const cd_reverse_norm_desc* desc, const float* vox_dev, const float* e_dev, const float* layerE_dev,
                     float* out_dev, float* energy_out_dev, int B, void* stream);
+
+/* General form of the same pipeline: ReverseNormCaloChall on the flat Dataset-0/1 voxel vector (ragged layers from the binning
+ * file, utils/utils.py:549-558) and ReverseNormHGCal (utils/HGCal_utils.py:167-292; its three stages - inverse map on the grid,
+ * GLaM decoding, per-layer renormalisation on the cells - are three calls with final_scale only on the last).
+ *   data = inverse(v*a_scale + a_shift) * post_scale + post_shift ; ['layer'] per-segment renormalisation ; * max_deposit*E_inc */
+typedef struct cd_reverse_norm_ex_desc {
+    int nseg, total;                  /* layers per shower, values per shower (all layers) */
+    int map_kind;                     /* 0 reverse logit, 1 exp of min(x, log_cap) ('log' maps), 2 identity */
+    float a_scale, a_shift;           /* '*-norm': std, mean;  '*-scaled': 0.5*(max-min), 0.5*(max-min)+min */
+    float alpha;                      /* reverse_logit alpha: 1e-6 (utils.py:233), 1e-8 (HGCal_utils.py:13) */
+    float log_cap;                    /* log(max_deposit) */
+    float post_scale, post_shift;     /* HGCalConverter.dec normalisation (embed_std, embed_mean); 1, 0 otherwise */
+    float totalE_mean, totalE_std, layers_mean, layers_std;
+    float guard_eps;                  /* layers / previous sums below this are not rescaled: 1e-6 (utils.py:528), 1e-8 (HGCal) */
+    int energy_mode;                  /* 0: emin*(emax/emin)^e (logE), 1: emin + (emax-emin)*e */
+    float emin, emax, max_deposit, ecut;
+    int e_stride;                     /* floats per shower in e_dev (HGCal gen info has 3 columns; column 0 is used) */
+    int final_scale;                  /* 1: multiply by max_deposit*E_inc */
+} cd_reverse_norm_ex_desc;
+/* seg_dev: device int32 [nseg+1] segment offsets into the `total` values of one shower, or NULL for nseg equal segments. */
+int cd_reverse_norm_ex(const cd_reverse_norm_ex_desc* desc, const int32_t* seg_dev, const float* vox_dev, const float* e_dev,
+                       const float* layerE_dev, float* out_dev, float* energy_out_dev, int B, void* stream);
+
+/* Sampled ("sparse") GLaM decoding (HGCal_utils.py:340-349 with sparse_decoding, generate_sparse_mat :355-407): every grid
+ * bin's energy is split equally over a random subset of its cells - cell n of bin e is kept when u + w[n,e] > 1 (u uniform,
+ * w the decoder weight, only w > 1e-6 take part) and the entry with the largest u + w is always kept.  The decoder comes as
+ * a CSC matrix over (grid bin -> cells) holding its positive entries.  per_batch != 0: one draw shared by the batch.
+ * u_bank_dev (optional, tests): the uniforms, laid out like the reference's rand_like(in_mat): [b or 0][layer][cell][bin]. */
+int cd_geom_decode_sparse(const int32_t* colptr_dev, const int32_t* row_dev, const float* val_dev, int n_cols, int n_rows,
+                          int cells_per_layer, int bins_per_layer, const float* x_dev, float* out_dev, int B, int per_batch,
+                          uint64_t seed, const float* u_bank_dev, void* stream);
 
 /* test hooks: one layer in isolation on PLCP tensors held by the handle (used by tests/ only) */
 int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,

@@ -1,6 +1,7 @@
 """CPU: geometry-embedding oracle vs the live reference's golden outputs (BASELINE config 1, Dataset 1 photons), and the
 product's host-side converter logic (binning parser, GeomConverter matrices, CSR export) vs that oracle."""
 import numpy as np
+import pytest
 import scipy.sparse as sp
 import torch
 
@@ -106,3 +107,32 @@ def test_host_matrixconverter_csr_matches_oracle():
         assert False
     except ValueError:
         pass
+
+
+def test_hgcal_converter_init_matches_reference_fingerprints():
+    """HGCalConverter.init (GLaM maps from geom_william.pkl; HGCal_utils.py:412-486, 590-634) against fingerprints of the live
+    reference's matrices (tests/golden/hgcal_geom.npz).  Host-side construction only: no compute call on the device."""
+    import os
+    from conftest import GOLDEN, ROOT
+    pk = os.path.join(ROOT, "oracle", "_ref", "HGCalShowers", "geoms", "geom_william.pkl")
+    if not os.path.exists(pk):
+        pk = "/root/reference/HGCalShowers/geoms/geom_william.pkl"
+    if not os.path.exists(pk):
+        pytest.skip("HGCal geometry pickle not staged")
+    from calodiffusion_b200.geometry import HGCalConverter
+    gold = np.load(os.path.join(GOLDEN, "hgcal_geom.npz"))
+    c = HGCalConverter(bins=[-1, 1, 28, 12, 21], geom_file=pk)
+    c.init(norm=False, dataset_num=111)
+    e, d = c.enc_mat, c.dec_mat
+    assert np.array_equal((e != 0).sum((1, 2)).numpy(), gold["enc_nnz"])
+    assert np.allclose(e.double().sum((1, 2)).numpy(), gold["enc_sum"], rtol=0, atol=1e-9)
+    assert np.array_equal(c.enc_mask.sum((1, 2)).numpy(), gold["enc_mask_nnz"])
+    g = torch.Generator().manual_seed(21)
+    ve, vd = torch.randn(e.shape[2], generator=g), torch.randn(d.shape[2], generator=g)
+    assert np.allclose((e @ ve).numpy(), gold["enc_proj"], rtol=1e-6, atol=1e-6)
+    assert np.allclose((d @ vd).numpy(), gold["dec_proj"], rtol=1e-4, atol=1e-5)
+    enc_csr, dec_csr = c.csr_maps()
+    assert len(enc_csr["val"]) == int(gold["enc_nnz"].sum())
+    assert abs(len(dec_csr["val"]) - int(gold["dec_nnz_eps"].sum())) <= 4      # entries within round-off of the 1e-6 threshold
+    from calodiffusion_b200.postprocess import DATASET_PARAMS
+    assert DATASET_PARAMS[101]["embed_mean"] == 0.0835 and DATASET_PARAMS[101]["embed_std"] == 3.1083   # consts.py:171-172
