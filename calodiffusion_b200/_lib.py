@@ -12,7 +12,9 @@ EXPORTS = [
     "cd_last_error", "cd_version", "cd_device_check", "cd_unet_create", "cd_unet_destroy", "cd_unet_set_weight",
     "cd_unet_finalize", "cd_unet_set_option", "cd_unet_workspace_bytes", "cd_unet_launch_count", "cd_unet_forward",
     "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_reverse_norm", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
-    "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply", "cd_layer_model_create",
+    "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply", "cd_layer_model_create", "cd_reverse_norm_ex", "cd_geom_decode_sparse",
+    "cd_train_step", "cd_train_loss", "cd_train_adam", "cd_train_refresh", "cd_train_flat_size", "cd_train_num_params",
+    "cd_train_param_info", "cd_train_buffer",
 ]
 
 
@@ -104,6 +106,16 @@ def load():
     lib.cd_reverse_norm.argtypes = [C.POINTER(ReverseNormDesc), vp, vp, vp, vp, vp, i32, vp]
     lib.cd_reverse_norm_ex.argtypes = [C.POINTER(ReverseNormExDesc), vp, vp, vp, vp, vp, vp, i32, vp]
     lib.cd_geom_decode_sparse.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp, i32, i32, u64, vp, vp]
+    lib.cd_train_step.argtypes = [vp, vp, vp, vp, vp, f32, i32, vp]
+    lib.cd_train_loss.argtypes = [vp, C.POINTER(C.c_double), vp]
+    lib.cd_train_adam.argtypes = [vp, f32, f32, f32, f32, f32, vp]
+    lib.cd_train_refresh.argtypes = [vp, vp]
+    lib.cd_train_flat_size.argtypes = [vp]
+    lib.cd_train_flat_size.restype = i64
+    lib.cd_train_num_params.argtypes = [vp]
+    lib.cd_train_param_info.argtypes = [vp, i32, C.c_char_p, i32, C.POINTER(i64), C.POINTER(i64)]
+    lib.cd_train_buffer.argtypes = [vp, i32]
+    lib.cd_train_buffer.restype = vp
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
     lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]

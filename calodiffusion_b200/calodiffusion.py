@@ -132,6 +132,23 @@ class CondUnetB200(nn.Module):
         raise RuntimeError("CondUnetB200 holds parameters only; call the owning CaloDiffusion (CUDA library) instead")
 
 
+class _LossWithGrads(torch.autograd.Function):
+    """Connects the loss value computed by `cd_train_step` to the torch parameters: backward() returns the gradients the
+    library already left in its flat buffer (divided by the loss scale), so `loss.backward(); optimizer.step()` works unchanged."""
+
+    @staticmethod
+    def forward(ctx, loss, model, *params):
+        ctx.model = model
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        tr = ctx.model._train
+        inv = grad_out / tr["loss_scale"]
+        grads = [(tr["G"][o:o + n] * inv).reshape(p.shape) for p, (o, n) in tr["slices"]]
+        return (None, None, *grads)
+
+
 class CaloDiffusion(Diffusion):
     def __init__(self, config, n_steps=400, loss_type="l2", max_batch=None):
         super().__init__(config, n_steps, loss_type)
@@ -159,6 +176,7 @@ class CaloDiffusion(Diffusion):
         self._max_batch = int(max_batch or cfg.get("BATCH", 128))
         self._handle = None
         self._handle_versions = None
+        self._train = None
         self._io = {}
         self._lib = _lib.load()
         _lib.check(self._lib.cd_device_check(), "device check")
@@ -253,6 +271,7 @@ class CaloDiffusion(Diffusion):
         return d
 
     def _engine(self, batch):
+        self.sync_params_from_engine()
         versions = tuple(p._version for p in self.model.parameters())
         if self.do_embed:
             versions += self.NN_embed._weights_version()
@@ -329,6 +348,117 @@ class CaloDiffusion(Diffusion):
         if getattr(self, "_handle", None) is not None:
             self._lib.cd_unet_destroy(self._handle)
             self._handle = None
+        if getattr(self, "_train", None) is not None:
+            self._lib.cd_unet_destroy(self._train["h"])
+            self._train = None
+
+    # ------------------------------------------------------------------ training step
+    class _DevBuf:
+        """A raw device buffer of the library exposed through __cuda_array_interface__ (zero-copy torch view)."""
+
+        def __init__(self, ptr, n):
+            self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+    def _train_engine(self, batch):
+        """The training handle (option train: no buffer reuse, tape for the backward pass) plus torch views of its flat
+        parameter / gradient / Adam buffers and the name -> (offset, numel) table."""
+        tr = getattr(self, "_train", None)
+        if tr is not None and batch <= tr["max_batch"]:
+            return tr
+        if tr is not None:
+            self.sync_params_from_engine()
+            self._lib.cd_unet_destroy(tr["h"])
+            self._train = None
+        lib = self._lib
+        if self.do_embed:
+            raise ValueError("training with an in-loop geometry embedding is not supported by the B200 backend")
+        h = self._create_handle(lib, int(batch))
+        try:
+            _lib.check(lib.cd_unet_set_option(h, b"train", 1), "set_option")
+            for name, p in self.model.named_parameters():
+                t = p.detach().to("cpu", torch.float32).contiguous()
+                shp = (C.c_int64 * t.dim())(*t.shape)
+                _lib.check(lib.cd_unet_set_weight(h, ("model." + name).encode(), t.data_ptr(), shp, t.dim()), "set_weight")
+            _lib.check(lib.cd_unet_finalize(h), "finalize")
+        except Exception:
+            lib.cd_unet_destroy(h)
+            raise
+        n = int(lib.cd_train_flat_size(h))
+        view = lambda which: torch.as_tensor(self._DevBuf(lib.cd_train_buffer(h, which), n), device=self.device)
+        table = {}
+        buf = C.create_string_buffer(256)
+        off, num = C.c_int64(), C.c_int64()
+        for i in range(int(lib.cd_train_num_params(h))):
+            _lib.check(lib.cd_train_param_info(h, i, buf, len(buf), C.byref(off), C.byref(num)), "param_info")
+            table[buf.value.decode()] = (int(off.value), int(num.value))
+        params = dict(self.model.named_parameters())
+        slices = [(params[k[len("model."):]], table[k]) for k in table]
+        self._train = dict(h=h, max_batch=int(batch), P=view(0), G=view(1), M=view(2), V=view(3), table=table, slices=slices,
+                           versions=tuple(p._version for p in self.model.parameters()), stale=False, loss_scale=None)
+        return self._train
+
+    def _sync_params_to_engine(self, tr):
+        """torch parameters changed (an external optimizer stepped, a checkpoint was loaded): copy them into the flat master
+        buffer on the device and re-derive the kernels' weight layouts."""
+        versions = tuple(p._version for p in self.model.parameters())
+        if versions == tr["versions"]:
+            return
+        with torch.no_grad():
+            torch._foreach_copy_([tr["P"][o:o + n] for _, (o, n) in tr["slices"]], [p.detach().reshape(-1) for p, _ in tr["slices"]])
+        _lib.check(self._lib.cd_train_refresh(tr["h"], self._stream()), "train_refresh")
+        tr["versions"] = versions
+
+    def sync_params_from_engine(self):
+        """After `fused_adam_step` the master copy on the device is ahead of the torch parameters: copy it back (called before
+        sampling, state_dict() and whenever a caller wants `model.parameters()` to be current)."""
+        tr = getattr(self, "_train", None)
+        if tr is None or not tr["stale"]:
+            return
+        with torch.no_grad():
+            torch._foreach_copy_([p.detach().reshape(-1) for p, _ in tr["slices"]], [tr["P"][o:o + n] for _, (o, n) in tr["slices"]])
+        tr["versions"] = tuple(p._version for p in self.model.parameters())
+        tr["stale"] = False
+        self._handle_versions = None
+
+    def state_dict(self, *a, **k):
+        self.sync_params_from_engine()
+        return super().state_dict(*a, **k)
+
+    def training_loss(self, data, E, sigma, noise, layers, loss_scale=None):
+        """hybrid_weight.loss_function on the device (models/loss.py:168-179): forward, loss and the whole backward pass in one
+        library call.  Returns the loss as a 0-d tensor that is connected to the parameters: `loss.backward()` hands every
+        parameter its gradient (drop-in for train/train_diffusion.py:58-62 with any torch optimizer); `fused_adam_step()` is
+        the all-device alternative."""
+        B = data.shape[0]
+        tr = self._train_engine(B)
+        if not tr["stale"]:
+            self._sync_params_to_engine(tr)
+        d = self._dev(data, (B, self._voxels))
+        nz = self._dev(noise, (B, self._voxels))
+        sg = self._dev(sigma).reshape(-1)
+        if sg.numel() == 1:
+            sg = sg.expand(B).contiguous()
+        cond = self._cond(E, layers)
+        scale = float(loss_scale) if loss_scale is not None else float(B * self._voxels)
+        _lib.check(self._lib.cd_train_step(tr["h"], d.data_ptr(), nz.data_ptr(), sg.data_ptr(), cond.data_ptr(), scale, B,
+                                           self._stream()), "train_step")
+        tr["loss_scale"] = scale
+        out = C.c_double()
+        _lib.check(self._lib.cd_train_loss(tr["h"], C.byref(out), self._stream()), "train_loss")
+        loss = torch.tensor(out.value, device=self.device, dtype=torch.float32)
+        return _LossWithGrads.apply(loss, self, *[p for p, _ in tr["slices"]])
+
+    def grad_buffer(self):
+        """Flat fp32 gradient of the last `training_loss` (times its loss scale): the tensor a data-parallel trainer all-reduces."""
+        return self._train["G"]
+
+    def fused_adam_step(self, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        """torch.optim.Adam's update (train/train.py:144 defaults) on the device-resident master parameters, followed by the
+        re-derivation of the convolution weight layouts.  The torch parameters are refreshed lazily (sync_params_from_engine)."""
+        tr = self._train
+        _lib.check(self._lib.cd_train_adam(tr["h"], float(lr), float(betas[0]), float(betas[1]), float(eps), float(tr["loss_scale"]),
+                                           self._stream()), "train_adam")
+        tr["stale"] = True
 
     def __del__(self):
         try:

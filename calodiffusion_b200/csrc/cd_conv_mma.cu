@@ -743,6 +743,8 @@ static int pick_cb(int Cout, int taps) {
     return 0;
 }
 
+int mma_pick_cb(int Cout, int taps) { return pick_cb(Cout, taps); }
+
 bool mma_conv_supported(int Cin, int Cout, int taps) {
     return (taps == 27 || taps == 1) && Cin % 16 == 0 && Cin >= 16 && Cout % 16 == 0 && pick_cb(Cout, taps) > 0;
 }

@@ -58,7 +58,27 @@ struct Run {  // per-call state
     FinalParams fin;       // output routing of the final kernel
 };
 
-struct Buf { int level, C; __half* ptr; bool busy; };
+struct Buf { int level, C; __half* ptr; bool busy; __half* grad = nullptr; };
+
+// ---- training tape (option "train" before cd_unet_finalize): what the backward pass needs to know about every op ----
+struct TapeOp {
+    int kind = 0;                 // 0 conv, 1 GroupNorm(+act+cond+residual), 2 attention core, 3 final conv + loss, 4 init marker
+    // conv
+    std::string wname, bname;
+    int Cin_real = 0, Cin_pad = 0, Cout = 0, kz = 1, kp = 1, kr = 1, stride = 1, transposed = 0, level_in = 0, level_out = 0;
+    int pz = 0, cp = 0, pr = 0;
+    std::vector<int> srcs; int dst = -1;
+    float* w = nullptr; __half* wmma = nullptr;              // forward layouts (refreshed from the master after every optimizer step)
+    float* wd[2] = {nullptr, nullptr}; __half* wdm[2] = {nullptr, nullptr};   // data-gradient layouts, one per source
+    bool need_dgrad = true, bias_via_gn = false;
+    // GroupNorm
+    std::string gname, betaname;
+    int src = -1, C = 0, groups = 1, act = 0, addvec_off = -1, residual = -1, residual2 = -1, conv_of_src = -1;
+    size_t stats_off = 0;
+    // attention core
+    int qkv = -1, y = -1; size_t skm = 0, sctx = 0; std::string woname, boname;
+};
+struct ParamSlot { std::string name; long long offset, numel; };
 
 constexpr int kRow = 12;   // floats per sampler coefficient-table row: sigma, k0..k4, pre_a, pre_b, d_scale, 3 spare
 
@@ -90,6 +110,21 @@ struct cd_unet {
     std::vector<cudaEvent_t> prof_evs;
     bool finalized = false;
     int conv_backend = 0;
+    // training
+    bool train = false;
+    std::vector<cd::TapeOp> tape;
+    std::vector<cd::ParamSlot> params;
+    std::map<std::string, int> param_index;
+    float* P = nullptr; float* G = nullptr; float* M = nullptr; float* V = nullptr;   // flat master params, grads, Adam moments
+    long long n_params = 0;
+    int adam_step = 0;
+    float* gn_acc = nullptr; float* gn_m12 = nullptr; float* attn_dcx = nullptr; float* daddvec = nullptr; float* embed_rec = nullptr;
+    float* x_noisy = nullptr; float* x0_buf = nullptr; float* coef = nullptr; double* loss_dev = nullptr;
+    cd::EmbedBwdLayout embed_layout = {};
+    int tin_buf_index = -1;
+    std::vector<std::string> proj_names;        // state-dict prefix of every conditioned block's Linear (e.g. model.downs.0.0.mlp.1)
+    float* pptr(const std::string& name) { auto it = param_index.find(name); return it == param_index.end() ? nullptr : P + params[it->second].offset; }
+    float* gptr(const std::string& name) { auto it = param_index.find(name); return it == param_index.end() ? nullptr : G + params[it->second].offset; }
     int64_t workspace_bytes = 0;
     int64_t launches = 0;
     int launches_per_forward = 0;
@@ -157,12 +192,14 @@ static Geom make_geom(int Z, int P, int R, int max_batch) {
 }
 
 static int acquire(cd_unet* h, int level, int C) {
-    for (size_t i = 0; i < h->bufs.size(); ++i)
+    // training keeps every activation for the backward pass: no reuse
+    for (size_t i = 0; i < h->bufs.size() && !h->train; ++i)
         if (!h->bufs[i].busy && h->bufs[i].level == level && h->bufs[i].C == C) { h->bufs[i].busy = true; return (int)i; }
     Buf b;
     b.level = level; b.C = C; b.busy = true;
     size_t n = (size_t)(C / 8) * (size_t)h->geom[level].chunk_stride * 8;
     b.ptr = h->dalloc<__half>(n, true);
+    if (h->train) b.grad = h->dalloc<__half>(n, true);
     h->bufs.push_back(b);
     return (int)h->bufs.size() - 1;
 }
@@ -198,7 +235,7 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         const HostTensor* b = find_w(h, bname);
         if (!b) { fail("missing weight %s", bname.c_str()); return false; }
         if ((int)b->data.size() != Cout) { fail("bias %s has unexpected size", bname.c_str()); return false; }
-        out->bias = h->upload(b->data);
+        out->bias = (h->train && h->pptr(bname)) ? h->pptr(bname) : h->upload(b->data);
     }
     if (want_mma && !transposed && mma_conv_supported(Cin_pad, Cout, taps)) {
         std::vector<__half> hp(mma_packed_elems(Cin_pad, Cout, taps));
@@ -206,7 +243,7 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
-    if (want_gather && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {
+    if (want_gather && !h->train && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {   // training: the SIMT form (fp32 weights refreshed in place)
         const bool pairT = transposed && kr == 4;     // transposed convs use the merged output-pair taps
         std::vector<__half> hp(pairT ? gather_packed_elems_pairT(Cin_pad, Cout, kz, kp) : gather_packed_elems(Cin_pad, Cout, taps));
         if (pairT) gather_pack_weights_pairT(pk.data(), Cin_pad, Cout, kz, kp, kr, hp.data());
@@ -221,6 +258,7 @@ static float* upload_vec(cd_unet* h, const std::string& name, int n) {
     const HostTensor* t = find_w(h, name);
     if (!t) { fail("missing weight %s", name.c_str()); return nullptr; }
     if ((int)t->data.size() != n) { fail("weight %s has unexpected size %zu (want %d)", name.c_str(), t->data.size(), n); return nullptr; }
+    if (h->train && h->pptr(name)) return h->pptr(name);      // training: every fp32 consumer reads the master copy in place
     return h->upload(t->data);
 }
 
@@ -235,6 +273,9 @@ struct Builder {
     cd_unet* h;
     bool ok = true;
     size_t scratch_prefix = 0;  // bytes per sample
+    // training: names / real input width of the conv about to be added (set by the call sites right before conv())
+    std::string t_wname, t_bname; int t_cin_real = 0;
+    void tag(const std::string& w, const std::string& b, int cin_real) { t_wname = w; t_bname = b; t_cin_real = cin_real; }
 
     size_t slot(size_t bytes_per_sample) {
         size_t off = scratch_prefix;
@@ -247,6 +288,14 @@ struct Builder {
               int write_halo, long long stats_off /* -1: none */) {
         cd_unet* hh = h;
         ConvW w = cw;
+        if (hh->train) {
+            TapeOp t;
+            t.kind = 0; t.wname = t_wname; t.bname = t_bname; t.Cin_real = t_cin_real ? t_cin_real : w.Cin; t.Cin_pad = w.Cin; t.Cout = w.Cout;
+            t.kz = w.kz; t.kp = w.kp; t.kr = w.kr; t.stride = stride; t.transposed = w.transposed; t.level_in = level_in; t.level_out = level_out;
+            t.pz = pz; t.cp = cp; t.pr = pr; t.srcs = srcs; t.dst = dst; t.w = w.w; t.wmma = w.wmma;
+            hh->tape.push_back(t);
+            t_wname.clear(); t_bname.clear(); t_cin_real = 0;
+        }
         {
             const Geom& go = hh->geom[level_out];
             const Geom& gi = hh->geom[level_in];
@@ -336,6 +385,15 @@ struct Builder {
         float* beta = upload_vec(hh, bname, C);
         if (!gamma || !beta) { ok = false; return; }
         if (C > 256) { fail("GroupNorm over more than 256 channels is not supported"); ok = false; return; }
+        if (hh->train) {
+            TapeOp t;
+            t.kind = 1; t.gname = gname; t.betaname = bname; t.level_in = t.level_out = level; t.src = src; t.dst = dst; t.C = C;
+            t.groups = groups; t.stats_off = (size_t)stats_off; t.act = act; t.addvec_off = addvec_off; t.residual = residual;
+            t.residual2 = residual2;
+            for (int i = (int)hh->tape.size() - 1; i >= 0; --i)      // the convolution that produced `src` (its bias gradient comes from here)
+                if (hh->tape[i].kind == 0 && hh->tape[i].dst == src) { t.conv_of_src = i; hh->tape[i].bias_via_gn = true; break; }
+            hh->tape.push_back(t);
+        }
         {
             const Geom& g = hh->geom[level];
             double m = (double)g.Z * g.P * g.R;
@@ -376,6 +434,7 @@ struct Builder {
             h->embed.pb[k] = upload_vec(h, pre + "mlp.1.bias", Cout);
             if (!h->embed.pw[k] || !h->embed.pb[k]) { ok = false; return -1; }
             h->embed.pC[k] = Cout;
+            h->proj_names.push_back(pre + "mlp.1");
             h->embed.poff[k] = h->addvec_stride;
             addvec_off = h->addvec_stride;
             h->addvec_stride += Cout;
@@ -391,7 +450,7 @@ struct Builder {
         //  single conv would stream its weights or stage K in many small groups; measured on DS2 L1 128->32 and DS3 L0 64->32)
         const Geom& gl = h->geom[level];
         const size_t win_bytes = (size_t)(128 + 2 * (gl.Pp * gl.Rp + gl.Rp + 1)) * Cin * 2;
-        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 + 2 * win_bytes > (size_t)300 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT")) {
+        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 + 2 * win_bytes > (size_t)300 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT") && !h->train) {
             const int Ca = h->bufs[srcs[0]].C, Cb = h->bufs[srcs[1]].C;
             const HostTensor* wfull = find_w(h, pre + "block1.proj.conv.weight");
             if (wfull && Ca + Cb == Cin && mma_conv_supported(Ca, Cout, 27) && mma_conv_supported(Cb, Cout, 27)) {
@@ -408,25 +467,30 @@ struct Builder {
                 h->weights.erase("__split_a"); h->weights.erase("__split_b");
             }
         }
+        tag(pre + "block1.proj.conv.weight", pre + "block1.proj.conv.bias", Cin);
         if (split) conv_split(c1, ca, cb2, level, srcs, t1, (long long)s1);
         else
         conv(c1, level, level, srcs, t1, 1, 1, 1, 1, 0, (long long)s1);
         int hbuf = acquire(h, level, Cout);
         gn(pre + "block1.norm.weight", pre + "block1.norm.bias", level, t1, hbuf, Cout, groups, (long long)s1, 1, addvec_off, -1);
-        conv(c2, level, level, {hbuf}, t1, 1, 1, 1, 1, 0, (long long)s2);
+        int t2 = h->train ? acquire(h, level, Cout) : t1;     // training keeps block1's pre-norm tensor
+        tag(pre + "block2.proj.conv.weight", pre + "block2.proj.conv.bias", Cout);
+        conv(c2, level, level, {hbuf}, t2, 1, 1, 1, 1, 0, (long long)s2);
         int res = srcs[0];
         int rbuf = -1;
         if (has_res) {
             rbuf = acquire(h, level, Cout);
+            tag(pre + "res_conv.conv.weight", pre + "res_conv.conv.bias", Cin);
             conv(cres, level, level, srcs, rbuf, 1, 0, 0, 0, 0, -1);
             res = rbuf;
         }
         // hbuf is free again as the destination: gn_apply reads t1 + residual only
         int res2 = (!has_res && srcs.size() == 2) ? srcs[1] : -1;  // identity residual over a concatenated input
-        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t1, hbuf, Cout, groups, (long long)s2, 1, -1, res, res2, out_stats_off);
+        int obuf = h->train ? acquire(h, level, Cout) : hbuf;     // training keeps block2's input (hbuf)
+        gn(pre + "block2.norm.weight", pre + "block2.norm.bias", level, t2, obuf, Cout, groups, (long long)s2, 1, -1, res, res2, out_stats_off);
         release(h, t1);
         if (rbuf >= 0) release(h, rbuf);
-        return hbuf;
+        return obuf;
     }
 
     // Residual(PreNorm(LinearAttention)) (models.py:111-117, 281-329); returns output buffer.
@@ -448,6 +512,34 @@ struct Builder {
         size_t sfold = slot((size_t)C * 32 * 2);     // fused attention: per-sample folded (Ctx/S, to_out) matrix, fp16
         int xn = acquire(h, level, C);
         int qkv = acquire(h, level, 96);
+        if (h->train) {
+            // training: the unfused chain, one tape entry per step - PreNorm GroupNorm(1,C) -> to_qkv 1x1x1 conv -> attention core
+            // (+ to_out conv) -> GroupNorm(1,C) + residual
+            gn(pre + "fn.norm.weight", pre + "fn.norm.bias", level, x, xn, C, 1, (long long)s0, 0, -1, -1);
+            tag(pre + "fn.fn.to_qkv.conv.weight", "", C);
+            conv(cq, level, level, {xn}, qkv, 1, 0, 0, 0, 0, -1);
+            int y = acquire(h, level, C);
+            {
+                const Geom& g = hh->geom[level];
+                double m = (double)g.Z * g.P * g.R;
+                char nm[96];
+                snprintf(nm, sizeof(nm), "attention_L%d", level);
+                hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m + 2.0 * 32 * C * m, 2.0 * m * (32 * 4 + C)});
+                TapeOp t;
+                t.kind = 2; t.level_in = t.level_out = level; t.qkv = qkv; t.y = y; t.C = C; t.skm = skm; t.sctx = sctx;
+                t.woname = pre + "fn.fn.to_out.0.conv.weight"; t.boname = pre + "fn.fn.to_out.0.conv.bias";
+                hh->tape.push_back(t);
+            }
+            hh->ops.push_back([=](Run& r) {
+                launch_attention(hh->geom[level], hh->bufs[qkv].ptr, (unsigned*)(hh->scratch + skm * r.B),
+                                 (float*)(hh->scratch + sctx * r.B), wout, bout, hh->bufs[y].ptr, C,
+                                 (double*)(hh->scratch + s1 * r.B), r.B, r.st);
+                hh->launches += 3;
+            });
+            int out = acquire(h, level, C);
+            gn(pre + "fn.fn.to_out.1.weight", pre + "fn.fn.to_out.1.bias", level, y, out, C, 1, (long long)s1, 0, -1, x);
+            return out;
+        }
         // PreNorm (GroupNorm(1,C), models.py:321-329) folded into the to_qkv 1x1x1 conv on the tcgen05 path:
         //   W (gamma*(x-mean)*rstd + beta) = rstd * (W diag(gamma)) x - mean*rstd * rowsum(W diag(gamma)) + W beta
         // so the conv reads x directly (no normalised copy) and its epilogue applies the per-sample scalars.
@@ -617,6 +709,21 @@ static int build_plan(cd_unet* h) {
     int nl = h->n_levels;
     const int* ls = d.layer_sizes;
 
+    if (h->train) {
+        // flat fp32 master copy of every parameter (PyTorch layouts, name order), its gradient and the Adam moments
+        long long off = 0;
+        for (auto& kv : h->weights) {
+            h->param_index[kv.first] = (int)h->params.size();
+            h->params.push_back({kv.first, off, (long long)kv.second.data.size()});
+            off += ((long long)kv.second.data.size() + 3) / 4 * 4;      // 16-byte aligned slots
+        }
+        h->n_params = off;
+        h->P = h->dalloc<float>((size_t)off, true); h->G = h->dalloc<float>((size_t)off, true);
+        h->M = h->dalloc<float>((size_t)off, true); h->V = h->dalloc<float>((size_t)off, true);
+        if (!h->P || !h->G || !h->M || !h->V) return fail("out of device memory for the training parameters");
+        for (auto& ps : h->params)
+            cudaMemcpy(h->P + ps.offset, h->weights[ps.name].data.data(), (size_t)ps.numel * sizeof(float), cudaMemcpyHostToDevice);
+    }
     // embedding MLPs
     EmbedParams& e = h->embed;
     memset(&e, 0, sizeof(e));
@@ -661,7 +768,9 @@ static int build_plan(cd_unet* h) {
     ConvW cinit;
     if (!pack_conv(h, M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels, 16, ls[0], 3, 3, 3, 0, true, &cinit, true)) return 1;
     int x = acquire(h, 0, ls[0]);
+    b.tag(M + "init_conv.conv.weight", M + "init_conv.conv.bias", d.in_channels);
     b.conv(cinit, 0, 0, {tin_buf}, x, 1, 1, 1, 1, 1, -1);
+    if (h->train) { h->tape.back().need_dgrad = false; h->tin_buf_index = tin_buf; }
     release(h, tin_buf);
 
     std::vector<int> skips;
@@ -683,6 +792,7 @@ static int build_plan(cd_unet* h) {
             ConvW cd_;
             if (!pack_conv(h, p + "2.conv.weight", p + "2.conv.bias", cout_, cout_, cout_, 3, 4, 4, 0, false, &cd_, true)) return 1;
             x = acquire(h, i + 1, cout_);
+            b.tag(p + "2.conv.weight", p + "2.conv.bias", cout_);
             b.conv(cd_, i, i + 1, {a}, x, 2, 1, 1, 1, 1, -1);
         } else {
             x = a;
@@ -725,6 +835,7 @@ static int build_plan(cd_unet* h) {
             ConvW cu;
             if (!pack_conv(h, p + "2.convTrans.weight", p + "2.convTrans.bias", dim_in, dim_in, dim_in, (int)wt->shape[2], 4, 4, 1, false, &cu, true)) return 1;
             x = acquire(h, lev - 1, dim_in);
+            b.tag(p + "2.convTrans.weight", p + "2.convTrans.bias", dim_in);
             b.conv(cu, lev, lev - 1, {a}, x, 2, 1, 1, 1, 1, -1);
             release(h, a);
         } else {
@@ -743,6 +854,7 @@ static int build_plan(cd_unet* h) {
     h->final_b = fb->data[0];
     h->final_C = ls[0];
     h->final_h = h->bufs[x].ptr;
+    if (h->train) { TapeOp t; t.kind = 3; t.src = x; t.C = ls[0]; h->tape.push_back(t); }
     {
         double m = (double)d.Z * d.P * d.R;
         h->op_info.push_back({"final_conv_update", 2.0 * m * ls[0], m * (2.0 * ls[0] + 16)});
@@ -751,13 +863,14 @@ static int build_plan(cd_unet* h) {
         FinalParams f = r.fin;
         f.g = h->geom[0];
         f.h = h->final_h; f.C = h->final_C; f.w = h->final_w; f.bias = h->final_b;
+        f.bias_ptr = h->train ? h->pptr("model.final_conv.1.conv.bias") : nullptr;
         f.x = r.x; f.sigma = r.sigma; f.sigma_stride = r.sigma_stride;
         f.sigma_data = r.scale_input ? h->d.sigma_data : -1.f;
         if (h->has_geom) {
             // grid-space raw output first, then decode + pre-conditioning + sampler update on the flat voxels
             FinalParams fg;
             memset(&fg, 0, sizeof(fg));
-            fg.g = f.g; fg.h = f.h; fg.C = f.C; fg.w = f.w; fg.bias = f.bias;
+            fg.g = f.g; fg.h = f.h; fg.C = f.C; fg.w = f.w; fg.bias = f.bias; fg.bias_ptr = f.bias_ptr;
             fg.sigma = r.sigma; fg.sigma_stride = r.sigma_stride; fg.sigma_data = -1.f;
             fg.pred_out = h->grid_pred;
             launch_final(fg, r.B, r.st);
@@ -850,6 +963,8 @@ __global__ void plcp_to_dense_kernel(Geom g, const __half* __restrict__ src, flo
     }
 }
 }  // namespace cd
+
+namespace cd { static int train_setup(cd_unet* h); }
 
 // -------------------------------------------------------------------------------------------------
 // C ABI
@@ -969,6 +1084,11 @@ int cd_unet_set_option(cd_unet* h, const char* key, int value) {
         return 0;
     }
     if (!strcmp(key, "debug_sync")) { h->debug_sync = value; return 0; }
+    if (!strcmp(key, "train")) {
+        if (h->finalized) return fail("option train must be set before cd_unet_finalize");
+        h->train = value != 0;
+        return 0;
+    }
     if (!strcmp(key, "check_finite")) { h->check_finite = value ? 1 : 0; return 0; }
     if (!strcmp(key, "online_attention")) {
         h->online_attention = value ? 1 : 0;
@@ -1036,6 +1156,7 @@ int cd_unet_finalize(cd_unet* h) {
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return fail("finalize: %s", cudaGetErrorString(e));
     for (auto& b : h->bufs) if (!b.ptr) return fail("out of device memory for activations");
+    if (h->train && cd::train_setup(h)) return 1;
     h->weights.clear();
     h->finalized = true;
     return 0;
@@ -1397,3 +1518,5 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     if (e != cudaSuccess) return fail("test conv: %s", cudaGetErrorString(e));
     return rc;
 }
+
+#include "cd_train.inl"

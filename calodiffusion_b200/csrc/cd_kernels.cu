@@ -496,7 +496,7 @@ __global__ void final_kernel(FinalParams p, long long nvox) {
     int ph = rem2 / g.R;
     int r = rem2 - ph * g.R;
     long long row = interior_row(g, b, z, ph, r);
-    float pred = p.bias;
+    float pred = p.bias_ptr ? *p.bias_ptr : p.bias;
     int nch = p.C >> 3;
     for (int k = 0; k < nch; ++k) {
         Half8 hv = load8(p.h + plcp_offset(g, k, row));

@@ -17,6 +17,7 @@ struct FinalParams {
     Geom g;
     const __half* h; int C;
     const float* w; float bias;         // final conv weights (C) + bias
+    const float* bias_ptr;              // optional device copy of the bias (training: read in place from the master parameters)
     const float* x;                     // denoiser input (B, voxels) fp32
     const float* sigma; int sigma_stride; float sigma_data;
     float* pred_out;                    // optional raw network output
@@ -120,5 +121,78 @@ bool mma_conv_supported(int Cin, int Cout, int taps);
 size_t mma_packed_elems(int Cin, int Cout, int taps);
 // w: fp32 [tap][ci][co]; out: fp16 blocks in the layout the tcgen05 kernel streams (see cd_conv_mma.cu)
 void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out);
+
+
+// ---- training step (cd_backward.cu) ---------------------------------------------------------------
+constexpr int kBwdMaxC = 128;
+
+struct LossBwdParams {
+    Geom g;
+    const __half* h; int C;                 // input of the final 1x1x1 conv
+    const float* w; const float* bias;      // its weights (C) and bias (device)
+    const float* x; const float* data;      // noised showers fed to the denoiser, clean showers (B, voxels) fp32
+    const float* sigma; float sigma_data;
+    const float* coef; const float* lossw;  // per shower: loss_scale*2*w_b/(mean(w)*numel), w_b/(mean(w)*numel)
+    __half* dh;                             // gradient of h (interior rows)
+    float* dw; float* db; double* loss; float* x0_out;
+};
+
+struct GnBwdParams {
+    Geom g;
+    const __half* x; const __half* dy;      // pre-norm tensor, gradient of the op's output
+    const double* stats; const float* gamma; const float* beta;
+    int C, groups, act; double count_per_channel;
+    float* acc;                             // scratch [B][C][4]
+    float* m12;                             // scratch [B][groups][2]
+    float* dgamma; float* dbeta; float* dbias;      // parameter gradients (dbias: bias of the convolution that produced x, or null)
+    float* daddvec; int addvec_stride;      // gradient of the additive conditioning (already offset to this block), or null
+    __half* dx; int dx_accumulate;
+    __half* dres; __half* dres2; int res_split, dres_accumulate, dres2_accumulate;   // residual gradient(s), or null
+    int rows_per_block;
+};
+
+struct WgradParams {
+    Geom g;
+    const __half* x0; const __half* x1; int src_chunks0;   // forward input (one or two concatenated sources)
+    const __half* dy;                                      // gradient of the conv output (Cout channels)
+    float* dw;                                             // master layout [co][ci][tap], Cin_real input channels
+    int Cin_pad, Cin_real, Cout, taps, B, ncob;
+};
+
+struct AttnBwdParams {
+    Geom g;
+    const __half* qkv; const __half* dy;    // raw 96-channel qkv tensor, gradient of the to_out conv output (C channels)
+    const unsigned* kmax; const float* ctx; // forward statistics: ordered-uint max of k, [B][33][32] context + S
+    const float* wout; int C;               // to_out weights [C][32]
+    float* dcx;                             // scratch [B][32][32]
+    float* dwout; float* dbout;             // parameter gradients
+    __half* dqkv;                           // gradient of the qkv tensor (96 channels)
+    int rows_per_block;
+};
+
+struct EmbedBwdLayout { int stride, cvec, dt3, t2, dc3, c2, dt2, t1, dt1, t0, dc2, c1, dc1, c0; };
+
+struct RepackParams {
+    const float* master; float* out_f; __half* out_h;
+    long long n; int mode, taps, Cin_real, Cin_pad, Cout, transposed, CB, ci_lo, n_out;
+};
+
+void launch_loss_backward(const LossBwdParams& p, int B, cudaStream_t st);
+void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st);
+int launch_wgrad_mma(const WgradParams& p, cudaStream_t st);
+void launch_conv_strided_backward(const ConvParams& p, const __half* x, const __half* dy, __half* dx, int dx_accumulate, float* dw,
+                                  int Cin_real, int master_transposed, cudaStream_t st);
+void launch_channel_sum(const Geom& g, const __half* t, int C, float* out, int B, cudaStream_t st);
+void launch_plcp_accumulate(const Geom& g, const __half* src, __half* dst, int C, int accumulate, int B, cudaStream_t st);
+int launch_attn_backward(AttnBwdParams p, int B, cudaStream_t st);
+void launch_embed_backward(const EmbedParams& p, const EmbedBwdLayout& L, const float* sigma, const float* cond, const float* daddvec,
+                           float* rec, int B, cudaStream_t st);
+void launch_linear_wgrad(const float* dY, long long sy, const float* X, long long sx, int B, int n_out, int n_in, float* dW, float* dbias,
+                         cudaStream_t st);
+void launch_adam(float* w, float* m, float* v, float* g, long long n, float lr, float beta1, float beta2, float eps, int step,
+                 float inv_scale, cudaStream_t st);
+void launch_repack_conv(const RepackParams& p, cudaStream_t st);
+void launch_fill_zero(float* p, long long n, cudaStream_t st);
+int mma_pick_cb(int Cout, int taps);     // channel block the tcgen05 weight layout uses (cd_conv_mma.cu)
 
 }  // namespace cd

@@ -52,3 +52,8 @@ class Diffusion(torch.nn.Module, ABC):
         if debug:
             return x.detach().cpu().numpy(), xs, x0s
         return x.detach().cpu().numpy()
+
+    def compute_loss(self, data, energy, noise, layers, time=None, rnd_normal=None):
+        """models/diffusion.py:106-110: loss of one training step.  Like the reference, `time` is accepted but not forwarded
+        (a discrete noise schedule draws its own steps inside Loss.__call__); call `self.loss_function(...)` to pass it."""
+        return self.loss_function(self, data, energy, noise=noise, layers=layers, rnd_normal=rnd_normal)

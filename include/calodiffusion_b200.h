@@ -192,6 +192,24 @@ int cd_geom_decode_sparse(const int32_t* colptr_dev, const int32_t* row_dev, con
                           int cells_per_layer, int bins_per_layer, const float* x_dev, float* out_dev, int B, int per_batch,
                           uint64_t seed, const float* u_bank_dev, void* stream);
 
+/* ---- training step -------------------------------------------------------------------------------------
+ * Replaces, for TRAINING_OBJ hybrid_weight / LOSS_TYPE l2, the body of train/train_diffusion.py:42-66:
+ *   noise -> x = data + sigma*noise -> x0 = denoise(x) -> L = sum w (x0-data)^2 / (mean(w) numel), w = 1 + 1/sigma^2
+ *   (models/loss.py:118-142, 168-179, 103-104) -> backward -> optimizer step (torch.optim.Adam, train/train.py:144).
+ * The handle must be created as usual and given cd_unet_set_option(h, "train", 1) before cd_unet_finalize.  Parameters,
+ * gradients and the Adam moments live in four flat fp32 device buffers (PyTorch layouts; cd_train_param_info gives every
+ * parameter's name / offset / size; cd_train_buffer(h, 0..3) the buffers P, G, M, V) so that a data-parallel caller can
+ * all-reduce G in place with one ncclAllReduce.  Gradients in G carry `loss_scale` (activation gradients are fp16). */
+int cd_train_step(cd_unet* h, const float* data_dev /* (B, voxels) clean showers */, const float* noise_dev, const float* sigma_dev /* (B) */,
+                  const float* cond_dev /* (B, cond_size) */, float loss_scale, int B, void* stream);   /* forward + backward; G, loss */
+int cd_train_loss(cd_unet* h, double* loss_host, void* stream);                     /* loss of the last step (synchronises) */
+int cd_train_adam(cd_unet* h, float lr, float beta1, float beta2, float eps, float loss_scale, void* stream);   /* P -= Adam(G / loss_scale) */
+int cd_train_refresh(cd_unet* h, void* stream);                                     /* re-derive the kernels' weight layouts after P changed */
+int64_t cd_train_flat_size(const cd_unet* h);
+int cd_train_num_params(const cd_unet* h);
+int cd_train_param_info(const cd_unet* h, int index, char* name, int cap, int64_t* offset, int64_t* numel);
+void* cd_train_buffer(cd_unet* h, int which /* 0 P, 1 G, 2 M, 3 V, 4 x0 of the last step (B, voxels) */);
+
 /* test hooks: one layer in isolation on PLCP tensors held by the handle (used by tests/ only) */
 int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,
                  const int* stride, int transposed, const float* w_host, const float* bias_host,

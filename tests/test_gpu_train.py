@@ -1,0 +1,107 @@
+"""Training step on the device (BASELINE config 5) against the CPU oracle's autograd (itself pinned to the live
+reference's compute_loss().backward() by tests/test_train_oracle.py): the loss, the gradient of every parameter tensor, one Adam
+update, and the drop-in form `loss.backward(); torch.optim.Adam.step()`.
+Gate: relative L2 per parameter tensor (north_star's 16-bit bound 1e-2; activations and activation gradients are fp16)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_case, rel_l2
+from test_train_oracle import train_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(case, max_batch=2):
+    from calodiffusion_b200.calodiffusion import CaloDiffusion
+    c = load_case(case)
+    cfg = dict(c["cfg"], SAMPLER="DDPM")
+    m = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=max_batch)
+    m.load_state_dict(dict(c["sd"]))
+    return m, c
+
+
+def _oracle(c, E, layers, data, noise, rnd, time):
+    from oracle.train_oracle import loss_and_grads, sigma_for
+    torch.set_num_threads(os.cpu_count() or 1)
+    return loss_and_grads(c["cfg"], c["sd"], data, E, layers, noise, sigma_for(c["cfg"], rnd, time))
+
+
+@pytest.mark.parametrize("case", ["ds2", "ds3"])
+def test_gradients_match_oracle(case):
+    m, c = _model(case)
+    E, layers, data, noise, rnd, time = train_inputs(c["shape"], 2, c["meta"]["cond_e"], c["meta"]["cond_layers"])
+    loss_ref, grads_ref = _oracle(c, E, layers, data, noise, rnd, time)
+    Lc = None if layers is None else layers.cuda()
+    loss = m.loss_function(m, data.cuda(), E.cuda(), noise=noise.cuda(), time=time.cuda(), layers=Lc, rnd_normal=rnd.cuda())
+    loss.backward()
+    e_loss = abs(float(loss) - loss_ref) / abs(loss_ref)
+    errs = {}
+    for name, p in m.model.named_parameters():
+        g = grads_ref["model." + name].numpy()
+        assert p.grad is not None, name
+        errs[name] = rel_l2(p.grad.cpu().numpy(), g)
+    worst = sorted(errs.items(), key=lambda kv: -kv[1])[:8]
+    total = rel_l2(np.concatenate([p.grad.cpu().numpy().ravel() for _, p in m.model.named_parameters()]),
+                   np.concatenate([grads_ref["model." + n].numpy().ravel() for n, _ in m.model.named_parameters()]))
+    print(f"{case}: loss rel.err {e_loss:.2e}; all-parameter gradient rel-L2 {total:.2e}; worst tensors: " +
+          ", ".join(f"{k} {v:.2e}" for k, v in worst))
+    # measured on B200: ds2 total 2.5e-3, worst tensor 6.1e-3; ds3 total 3.4e-4, worst 2.2e-3; loss 5e-5
+    assert e_loss < 5e-4
+    assert total < (6e-3 if case == "ds2" else 1.5e-3)
+    assert max(errs.values()) < 1e-2, worst
+
+
+def test_fused_adam_matches_torch_adam():
+    """One optimizer step: cd_train_adam on the device-resident master parameters vs torch.optim.Adam on the oracle's gradients."""
+    m, c = _model("ds2")
+    E, layers, data, noise, rnd, time = train_inputs(c["shape"], 2, 1, 46)
+    _, grads_ref = _oracle(c, E, layers, data, noise, rnd, time)
+    ref = {k: v.clone().requires_grad_(True) for k, v in c["sd"].items()}
+    opt = torch.optim.Adam(list(ref.values()), lr=4e-4)
+    for k, v in ref.items():
+        v.grad = grads_ref[k]
+    opt.step()
+    m.compute_loss(data.cuda(), E.cuda(), noise.cuda(), layers.cuda(), rnd_normal=rnd.cuda())
+    m.fused_adam_step(lr=4e-4)
+    sd = m.state_dict()                      # pulls the updated master copy back into the torch parameters
+    # Adam's first step is lr * g / (|g| + eps): where |g| >> eps it is lr*sign(g) and any gradient with the right sign matches,
+    # where |g| ~ eps (1e-8) it amplifies the gradient's relative error.  Compare the update over all parameters at once, and
+    # element-wise on the entries whose reference gradient is well above eps.
+    steps, steps_ref, big = [], [], []
+    for k, v in ref.items():
+        steps_ref.append((v.detach() - c["sd"][k]).numpy().ravel())
+        steps.append((sd[k].cpu() - c["sd"][k]).numpy().ravel())
+        big.append(np.abs(grads_ref[k].numpy().ravel()) > 1e-6)
+    steps, steps_ref, big = np.concatenate(steps), np.concatenate(steps_ref), np.concatenate(big)
+    e_all, e_big = rel_l2(steps, steps_ref), rel_l2(steps[big], steps_ref[big])
+    print(f"fused Adam first-step update vs torch.optim.Adam: rel-L2 {e_all:.2e} over all {steps.size} parameters, "
+          f"{e_big:.2e} over the {int(big.sum())} with |grad| > 1e-6")
+    assert e_all < 5e-2 and e_big < 1e-2
+    # the sampler sees the updated weights
+    y = m.denoise(data.cuda(), E=E.cuda(), sigma=torch.ones(2).cuda(), layers=layers.cuda())
+    assert torch.isfinite(y).all()
+
+
+def test_dropin_training_loop_decreases_loss():
+    """train/train_diffusion.py:42-66 verbatim shape: zero_grad -> compute_loss -> backward -> torch optimizer step."""
+    m, c = _model("ds2", max_batch=4)
+    opt = torch.optim.Adam(m.parameters(), lr=2e-3)
+    g = torch.Generator().manual_seed(3)
+    data = torch.randn([4] + list(c["shape"]), generator=g).cuda()
+    E = torch.rand(4, 1, generator=g).cuda()
+    layers = torch.randn(4, 46, generator=g).cuda()
+    noise = torch.randn([4] + list(c["shape"]), generator=g).cuda()
+    rnd = torch.randn(4, generator=g).cuda()
+    losses = []
+    for _ in range(6):
+        m.zero_grad()
+        opt.zero_grad()
+        loss = m.compute_loss(data, E, noise=noise, layers=layers, rnd_normal=rnd)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    print("drop-in loop losses:", [f"{v:.4e}" for v in losses])
+    assert losses[-1] < losses[0] and np.isfinite(losses).all()
