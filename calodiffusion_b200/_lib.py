@@ -14,7 +14,7 @@ EXPORTS = [
     "cd_denoise", "cd_sample_run", "cd_fill_normal", "cd_reverse_norm", "cd_test_conv", "cd_level_shape", "cd_unet_profile_report",
     "cd_unet_set_geom_map", "cd_unet_voxels", "cd_geom_apply", "cd_layer_model_create", "cd_reverse_norm_ex", "cd_geom_decode_sparse",
     "cd_train_step", "cd_train_loss", "cd_train_adam", "cd_train_refresh", "cd_train_flat_size", "cd_train_num_params",
-    "cd_train_param_info", "cd_train_buffer",
+    "cd_train_param_info", "cd_train_buffer", "cd_conv_noalloc", "cd_conv_noalloc_max_bytes",
 ]
 
 
@@ -118,6 +118,9 @@ def load():
     lib.cd_train_buffer.restype = vp
     lib.cd_test_conv.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, i32, vp]
     lib.cd_level_shape.argtypes = [vp, i32, C.POINTER(i32)]
+    lib.cd_conv_noalloc.argtypes = [vp, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), i32, vp, vp, vp, vp, i32, vp]
+    lib.cd_conv_noalloc_max_bytes.argtypes = []
+    lib.cd_conv_noalloc_max_bytes.restype = i64
     lib.cd_unet_profile_report.argtypes = [vp, C.c_char_p, i32]
     lib.cd_unet_set_geom_map.argtypes = [vp, i32, i32, i32, vp, vp, vp]
     lib.cd_unet_voxels.argtypes = [vp]

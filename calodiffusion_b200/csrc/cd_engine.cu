@@ -10,6 +10,7 @@
 #include <cstring>
 #include <functional>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1517,6 +1518,94 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     cudaFree(xin); cudaFree(yout);
     if (e != cudaSuccess) return fail("test conv: %s", cudaGetErrorString(e));
     return rc;
+}
+
+// -------------------------------------------------------------------------------------------------
+// The same convolution with NO allocation: all scratch (repacked weights + the two fp16 PLCP staging tensors) lives in one
+// file-scope device array.  Every call on a device shares it (it keeps the previous call's contents; what must start at zero
+// is cleared per call), so calls that overlap on the GPU race.  No counterpart in the reference.
+// -------------------------------------------------------------------------------------------------
+#define CD_NOALLOC_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[CD_NOALLOC_SCRATCH_BYTES];
+
+namespace cd {
+// torch layout (Cout,Cin,taps) / transposed (Cin,Cout,taps) fp32 -> the SIMT kernel's [tap][ci][co]
+__global__ void noalloc_pack_w_kernel(const float* __restrict__ w, float* __restrict__ pk, int Cin, int Cout, int taps, int transposed) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= taps * Cin * Cout) return;
+    int co = i % Cout, ci = (i / Cout) % Cin, t = i / (Cout * Cin);
+    size_t src = transposed ? (((size_t)ci * Cout + co) * taps + t) : (((size_t)co * Cin + ci) * taps + t);
+    pk[i] = w[src];
+}
+// device address of the scratch array, looked up once per device with that device current (the array's name in host code is
+// a host-side stand-in, not a device address)
+static unsigned char* noalloc_scratch_ptr() {
+    static std::mutex mu;
+    static unsigned char* ptrs[64] = {};
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { fail("no-alloc conv: cannot query the current device"); return nullptr; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) { fail("no-alloc conv: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return nullptr; }
+        ptrs[dev] = static_cast<unsigned char*>(p);
+    }
+    return ptrs[dev];
+}
+}  // namespace cd
+
+extern "C" int64_t cd_conv_noalloc_max_bytes(void) { return (int64_t)CD_NOALLOC_SCRATCH_BYTES; }
+
+extern "C" int cd_conv_noalloc(const cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize, const int* stride,
+                               int transposed, const float* w_dev, const float* bias_dev, const float* x_dev, float* y_dev,
+                               int B, void* stream) {
+    if (!h) return fail("null handle");
+    if (!h->finalized) return fail("cd_unet_finalize has not been called");
+    if (B < 1 || B > h->d.max_batch) return fail("batch %d outside [1, max_batch=%d]", B, h->d.max_batch);
+    if (!ksize || !stride || !w_dev || !x_dev || !y_dev) return fail("null argument");
+    if (level_in < 0 || level_in >= h->n_levels || level_out < 0 || level_out >= h->n_levels) return fail("bad level");
+    if (Cin < 8 || Cout < 8 || Cin % 8 || Cout % 8) return fail("channels must be multiples of 8");
+    const int taps = ksize[0] * ksize[1] * ksize[2];
+    if (taps < 1 || taps > 64) return fail("bad kernel size");
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geom& gi = h->geom[level_in];
+    const Geom& go = h->geom[level_out];
+    auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t wbytes = up((size_t)taps * Cin * Cout * sizeof(float));
+    const size_t nin = (size_t)(Cin / 8) * gi.chunk_stride * 8, nout = (size_t)(Cout / 8) * go.chunk_stride * 8;
+    const size_t inbytes = up(nin * sizeof(__half)), outbytes = up(nout * sizeof(__half));
+    const size_t need = wbytes + inbytes + outbytes;
+    if (need > (size_t)CD_NOALLOC_SCRATCH_BYTES)
+        return fail("no-alloc conv needs %zu bytes of scratch, the static array holds %u (weights %zu + input %zu + output %zu; "
+                    "the staging tensors scale with the handle's max_batch)", need, CD_NOALLOC_SCRATCH_BYTES, wbytes, inbytes, outbytes);
+    unsigned char* base = noalloc_scratch_ptr();
+    if (!base) return 1;
+    float* pk = reinterpret_cast<float*>(base);
+    __half* xin = reinterpret_cast<__half*>(base + wbytes);
+    __half* yout = reinterpret_cast<__half*>(base + wbytes + inbytes);
+    // halo rows / guards of both staging tensors must read as zero: the array keeps the previous call's contents
+    CD_CUDA(cudaMemsetAsync(xin, 0, inbytes + outbytes, st));
+    const int nw = taps * Cin * Cout;
+    noalloc_pack_w_kernel<<<(nw + 255) / 256, 256, 0, st>>>(w_dev, pk, Cin, Cout, taps, transposed);
+    long long nrows = (long long)B * gi.rows_per_sample;
+    dense_to_plcp_kernel<<<(unsigned)((nrows + 127) / 128), 128, 0, st>>>(gi, x_dev, xin, Cin, nrows);
+    ConvParams p;
+    p.gin = gi; p.gout = go; p.nsrc = 1; p.Cin_total = Cin;
+    p.src[0].base = xin; p.src[0].C = Cin; p.src[1].base = nullptr; p.src[1].C = 0;
+    p.dst = yout; p.Cout = Cout; p.w = pk; p.bias = bias_dev;
+    p.kz = ksize[0]; p.kp = ksize[1]; p.kr = ksize[2];
+    p.sz = stride[0]; p.sp = stride[1]; p.sr = stride[2];
+    const bool is1 = taps == 1;
+    p.pz = is1 ? 0 : 1; p.cp = is1 ? 0 : 1; p.pr = is1 ? 0 : 1;
+    p.transposed = transposed; p.write_halo = 0; p.stats = nullptr; p.stats_cpg = 1; p.B = B;
+    p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
+    launch_conv_generic(p, st);
+    long long nvox = (long long)B * go.Z * go.P * go.R;
+    plcp_to_dense_kernel<<<(unsigned)((nvox + 127) / 128), 128, 0, st>>>(go, yout, y_dev, Cout, nvox);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) return fail("no-alloc conv: %s", cudaGetErrorString(e));
+    return 0;
 }
 
 #include "cd_train.inl"

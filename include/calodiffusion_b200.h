@@ -217,6 +217,22 @@ int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, con
                  int B, int backend /* 0 R-stacked tcgen05, 1 SIMT, 2 gather tcgen05 */, void* stream);
 int cd_level_shape(const cd_unet* h, int level, int* zpr /* [3] */);
 
+/* cd_conv_noalloc: no counterpart in the reference - added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same single
+ * CylindricalConv / CylindricalConvTrans as cd_test_conv's SIMT backend (backend 1), but every byte of scratch - the repacked
+ * fp32 weights and the two fp16 staging tensors in the engine's activation layout - lives in ONE static device array of
+ * cd_conv_noalloc_max_bytes() = 16 MiB that every GPU loading the library holds until exit.  The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine), does not synchronise, and only enqueues work on `stream`; the handle
+ * is read for the level geometry only.  Weights come in the PyTorch layout ON THE DEVICE: (Cout,Cin,kz,kp,kr), transposed
+ * (Cin,Cout,kz,kp,kr); bias_dev (Cout) or NULL.  Needs taps*Cin*Cout*4 + (Cin + Cout)/8 * 16 * rows(level, max_batch) bytes
+ * (each part rounded up to 256); a request beyond the 16 MiB is rejected with an error naming the three parts.  All calls on
+ * a device share the array, which keeps the previous call's contents (the staging tensors are cleared by every call): calls
+ * that overlap on the GPU - two streams, or two threads - race; serialise them on one stream. */
+int64_t cd_conv_noalloc_max_bytes(void);
+int cd_conv_noalloc(const cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize, const int* stride,
+                    int transposed, const float* w_dev, const float* bias_dev, const float* x_dev /* (B,Cin,Z,P,R) fp32 */,
+                    float* y_dev /* (B,Cout,Zo,Po,Ro) fp32 */, int B, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
