@@ -55,6 +55,10 @@ WORKLOADS = {
         name="CaloChallenge Dataset-1 photons (368 voxels, in-loop GeoEmbed to 5x10x30), cylindrical U-Net, DDIM 50 steps",
         sampler="DDim", steps=50, evals_per_shower=50, batch=1000, n_layers=6, gflop_per_eval=1.4708, binning="ds1_meta.json"),
 }
+# BASELINE config 5: the Dataset-2 training step (train/train_diffusion.py:42-66), 128 showers per GPU, throughput only
+WORKLOADS["ds2_train"] = dict(WORKLOADS["ds2"], train=True, batch=128, ref_key="ds2",
+                              name="CaloChallenge Dataset-2 (45x16x9) training step: noise -> denoise -> hybrid-weight l2 -> backward -> Adam")
+TRAIN_LR = 4e-4      # configs/config_dataset2.json "LR"
 
 
 def _peaks():
@@ -129,6 +133,11 @@ REF_CONFIGS = {"ds2": ("config_dataset2.json", None), "ds3": ("config_dataset3.j
 
 def config_block(wl, B, steps, world):
     """The `config` object of the JSON line: identical on both arms (the driver compares them)."""
+    if wl.get("train"):
+        return {"workload": wl["name"], "batch_per_gpu": B, "optimizer": f"Adam lr {TRAIN_LR}",
+                "parallelism": f"dp{world} (replicated weights, one all-reduce of the flat fp32 gradient per step)",
+                "l2": "activations saved for the backward pass (GBs) exceed the 126 MB L2; no explicit flush",
+                "weights": "random init (seed 0)"}
     evals = wl["evals_per_shower"] * steps / wl["steps"]
     return {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
             "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
@@ -145,6 +154,8 @@ def reference_leg(key, budget_s=10.0, batch=None):
     import torch
     from oracle import ref_shim
     wl = WORKLOADS[key]
+    if wl.get("train"):
+        return reference_train_leg(key, budget_s=budget_s, batch=batch)
     if not ref_shim.available():
         v, cores, sample, _ = port_leg(wl, budget_s=budget_s)
         return dict(value=v, cores=cores, kind="port", sample=sample, device="cpu", ms_per_eval=None)
@@ -181,6 +192,54 @@ def reference_leg(key, budget_s=10.0, batch=None):
               f"scaled to {wl['evals_per_shower']} evaluations per shower")
     return dict(value=value, cores=cores, kind="reference", sample=sample, device=model.device.type,
                 ms_per_eval=1e3 * t_total / evals_done, batch=B)
+
+
+def reference_train_leg(key, budget_s=10.0, batch=None):
+    """The UNMODIFIED reference's training-loop body (train/train_diffusion.py:42-66: zero_grad, randn noise, compute_loss,
+    backward, torch.optim.Adam.step of train/train.py:144) on synthetic showers, on whatever device the reference picks.
+    Bounded sample: whole optimizer steps at a reduced batch on the CPU (16), the real batch on a GPU."""
+    import torch
+    from oracle import ref_shim
+    wl = WORKLOADS[key]
+    if not ref_shim.available():
+        raise RuntimeError("oracle/_ref is not staged (run oracle/build_ref.sh in the build container)")
+    cfg_name, overrides = REF_CONFIGS[wl["ref_key"]]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model, cfg = ref_shim.load_reference_model(cfg_name, wl["sampler"], overrides)
+    model.train()
+    on_gpu = model.device.type == "cuda"
+    B = int(batch or (wl["batch"] if on_gpu else 16))
+    opt = torch.optim.Adam(model.parameters(), lr=float(cfg.get("LR", TRAIN_LR)))
+    g = torch.Generator().manual_seed(1)
+    E = torch.rand(B, 1, generator=g).to(model.device)
+    layers = torch.randn(B, wl["n_layers"], generator=g).to(model.device)
+    data = torch.randn([B] + cfg["SHAPE_PAD"][1:], generator=g).to(model.device)
+
+    def step():
+        model.zero_grad()
+        opt.zero_grad()
+        t = torch.randint(0, model.nsteps, (B,), device=model.device).long()
+        noise = torch.randn_like(data)
+        loss = model.compute_loss(data=data, energy=E, noise=noise, layers=layers, time=t)
+        loss.backward()
+        opt.step()
+        return loss.item()          # the loop's own host read (train_loss += batch_loss.item())
+
+    step()
+    n, t_total = 0, 0.0
+    while t_total < budget_s and n < 4096:
+        t0 = time.perf_counter()
+        step()
+        if on_gpu:
+            torch.cuda.synchronize()
+        t_total += time.perf_counter() - t0
+        n += 1
+    sample = (f"unmodified reference training-loop body (compute_loss -> backward -> torch.optim.Adam) on {model.device.type}: "
+              f"{n} optimizer steps at batch {B} in {t_total:.1f} s")
+    return dict(value=B * n / t_total, cores=cores, kind="reference", sample=sample, device=model.device.type,
+                ms_per_eval=1e3 * t_total / n, batch=B)
 
 
 def reference_leg_subprocess(key, device, budget_s=10.0, timeout=900):
@@ -251,6 +310,10 @@ def port_leg(wl, budget_s=12.0, batch=16):
     return showers_per_s, cores, sample, t_total
 
 
+def _metric(wl):
+    return ("training samples/sec", "samples/s") if wl.get("train") else ("showers/sec sampled", "showers/s")
+
+
 def run_reference_arm(args, wl):
     """--impl reference: the reference's own implementation of the path on the host cores (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -266,14 +329,15 @@ def run_reference_arm(args, wl):
         vals.append(last["value"])
     dt = time.perf_counter() - t0
     v = sum(vals) / len(vals)
+    metric, unit = _metric(wl)
     line = {
-        "impl": "reference", "metric": "showers/sec sampled", "value": v, "unit": "showers/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_block(wl, B, steps, args.gpus),
-        "cpu_baseline": {"value": v, "unit": "showers/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"],
+        "cpu_baseline": {"value": v, "unit": unit, "cores": last["cores"], "kind": last["kind"], "sample": last["sample"],
                          "device": last["device"]},
-        "e2e": {"value": v, "unit": "showers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "each step = a bounded sample of the workload (see cpu_baseline.sample) on the host CPU, CUDA hidden",
     }
@@ -478,6 +542,139 @@ def run_gpu_arm(args, wl):
         dist.destroy_process_group()
 
 
+def run_train_arm(args, wl):
+    """--workload ds2_train (BASELINE config 5): one step = one optimizer step on 128 synthetic showers per GPU."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from calodiffusion_b200.calodiffusion import CaloDiffusion
+    from calodiffusion_b200.distributed import DataParallelTrainer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    cfg, B = dict(wl["cfg"]), int(args.batch or wl["batch"])
+    torch.manual_seed(0)
+    model = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=B)
+    trainer = DataParallelTrainer(model, lr=TRAIN_LR)       # broadcasts rank 0's weights, hooks the gradient all-reduce
+    shape = _data_shape(cfg)
+    vox = int(np.prod(shape))
+    g = torch.Generator().manual_seed(1 + rank)             # every rank trains on its own showers
+    data_host = torch.randn([B] + shape, generator=g).pin_memory()
+    E_host = torch.rand(B, 1, generator=g).pin_memory()
+    L_host = torch.randn(B, wl["n_layers"], generator=g).pin_memory()
+    data_dev, E_dev, L_dev = data_host.to(dev), E_host.to(dev), L_host.to(dev)
+    gen = torch.Generator(device=dev).manual_seed(2 + rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        # the loop body of train/train_diffusion.py:42-66 with the batch already on the device; fresh noise and noise levels
+        # every step (torch's device RNG, as the reference draws them), no host read of the loss
+        noise = torch.randn(data_dev.shape, device=dev, generator=gen)
+        rnd = torch.randn(B, device=dev, generator=gen)
+        trainer.step(data_dev, E_dev, L_dev, noise=noise, rnd_normal=rnd, read_loss=False)
+
+    def api_step():
+        # through the public API from pinned host buffers, loss read back like the reference's `batch_loss.item()`
+        d = data_host.to(dev, non_blocking=True)
+        e = E_host.to(dev, non_blocking=True)
+        l = L_host.to(dev, non_blocking=True)
+        return float(trainer.step(d, e, l))
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    barrier()
+    clk = ClockSampler(local_rank)
+    if rank == 0:
+        clk.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        device_step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = clk.finish() if rank == 0 else None
+    loss0 = api_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        loss = api_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    assert np.isfinite(loss) and np.isfinite(loss0), "non-finite training loss"
+    t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    total = world * B * args.steps
+    value, e2e = total / (ms * 1e-3), total / (e2e_ms * 1e-3)
+
+    if rank == 0:
+        peaks = _peaks()
+        model.grad_sync = None                              # per-op profile of one rank's step (no collective inside)
+        model.set_train_profile(2)
+        reps = 3
+        for _ in range(reps):
+            noise = torch.randn(data_dev.shape, device=dev, generator=gen)
+            rnd = torch.randn(B, device=dev, generator=gen)
+            model.loss_function(model, data_dev, E_dev, noise=noise, layers=L_dev, rnd_normal=rnd)
+        torch.cuda.synchronize()
+        rep = model.train_profile_report()
+        model.set_train_profile(0)
+        step_ms = sum(v["ms"] for v in rep.values()) / reps
+        ops_per_step = sum(v["count"] for v in rep.values()) // reps
+        top = max((k for k in rep if rep[k]["flops"] > 0), key=lambda k: rep[k]["ms"])
+        tv = rep[top]
+        tf = tv["flops"] / (tv["ms"] * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": top, "achieved": tf, "peak": peaks["tf_sus"], "unit": "TFLOP/s", "frac": tf / peaks["tf_sus"],
+                "traffic": None, "share_of_step": tv["ms"] / (step_ms * reps), "launches_per_step": tv["count"] // reps,
+                "ms_per_launch": tv["ms"] / tv["count"], "peak_source": peaks["src"] + " (sustained)",
+                "flops_model": "2 x executed MACs of the convolution whose weight/data gradient the kernel computes"}
+        table = sorted(((k, v["ms"] / reps, v["count"] // reps, (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None)
+                        for k, v in rep.items()), key=lambda r: -r[1])
+        cpu = gpu_ref = None
+        if world == 1 and not args.no_cpu_baseline:
+            r = reference_leg_subprocess(args.workload, "cpu", budget_s=12.0)
+            cpu = {"value": r["value"], "unit": "samples/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+            try:
+                r = reference_leg_subprocess(args.workload, "cuda", budget_s=6.0)
+                gpu_ref = {"value": r["value"], "unit": "samples/s", "ms_per_step": r["ms_per_eval"], "batch": r.get("batch"),
+                           "kind": r["kind"], "device": r["device"], "sample": r["sample"]}
+            except Exception as exc:
+                gpu_ref = {"unavailable": str(exc)[-300:]}
+        line = {
+            "metric": "training samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": config_block(wl, B, 0, world),
+            "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": 4 * B * (vox + 1 + wl["n_layers"]), "d2h_bytes_per_step": 8},
+            "gpu_launches": int(ops_per_step * args.steps),
+            "gpu_launches_note": "one per engine op (lower bound: several ops launch 2-3 kernels), forward + backward + Adam re-layout excluded",
+            "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "gpu_reference": gpu_ref,
+            "step_ms_profiled": step_ms, "grad_allreduce_bytes": int(model.grad_buffer().numel() * 4), "loss": loss,
+        }
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"op_profile_{args.workload}_n{world}.txt"), "w") as f:
+            f.write(f"# {wl['name']}; B={B}; per optimizer step, eager per-op CUDA events (forward + backward), {reps} reps\n")
+            for k, m_, c, tfl in table:
+                f.write(f"{k:44s} {m_:8.3f} ms  x{c:3d}  {'' if tfl is None else f'{tfl:7.1f} TFLOP/s'}\n")
+            f.write(f"total {step_ms:.3f} ms\n")
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -497,6 +694,8 @@ def main():
         print(json.dumps(reference_leg(args.workload, budget_s=args.budget)), flush=True)
     elif args.impl == "reference":
         run_reference_arm(args, wl)
+    elif wl.get("train"):
+        run_train_arm(args, wl)
     else:
         run_gpu_arm(args, wl)
 

@@ -144,7 +144,7 @@ class _LossWithGrads(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out):
         tr = ctx.model._train
-        inv = grad_out / tr["loss_scale"]
+        inv = grad_out / (tr["loss_scale"] * tr["grad_div"])
         grads = [(tr["G"][o:o + n] * inv).reshape(p.shape) for p, (o, n) in tr["slices"]]
         return (None, None, *grads)
 
@@ -341,6 +341,17 @@ class CaloDiffusion(Diffusion):
             out[name] = dict(count=int(cnt), ms=float(ms), flops=float(fl), bytes=float(by))
         return out
 
+    def set_train_profile(self, mode):
+        """`set_profile` for the training handle: per-op timing of forward and backward (diagnostic)."""
+        _lib.check(self._lib.cd_unet_set_option(self._train["h"], b"profile", int(mode)), "set_option")
+
+    def train_profile_report(self):
+        h, self._handle = self._handle, self._train["h"]
+        try:
+            return self.profile_report()
+        finally:
+            self._handle = h
+
     def workspace_bytes(self):
         return int(self._lib.cd_unet_workspace_bytes(self._handle)) if self._handle else 0
 
@@ -394,7 +405,7 @@ class CaloDiffusion(Diffusion):
         params = dict(self.model.named_parameters())
         slices = [(params[k[len("model."):]], table[k]) for k in table]
         self._train = dict(h=h, max_batch=int(batch), P=view(0), G=view(1), M=view(2), V=view(3), table=table, slices=slices,
-                           versions=tuple(p._version for p in self.model.parameters()), stale=False, loss_scale=None)
+                           versions=tuple(p._version for p in self.model.parameters()), stale=False, loss_scale=None, grad_div=1.0)
         return self._train
 
     def _sync_params_to_engine(self, tr):
@@ -424,11 +435,13 @@ class CaloDiffusion(Diffusion):
         self.sync_params_from_engine()
         return super().state_dict(*a, **k)
 
-    def training_loss(self, data, E, sigma, noise, layers, loss_scale=None):
+    def training_loss(self, data, E, sigma, noise, layers, loss_scale=None, read_loss=True):
         """hybrid_weight.loss_function on the device (models/loss.py:168-179): forward, loss and the whole backward pass in one
         library call.  Returns the loss as a 0-d tensor that is connected to the parameters: `loss.backward()` hands every
         parameter its gradient (drop-in for train/train_diffusion.py:58-62 with any torch optimizer); `fused_adam_step()` is
-        the all-device alternative."""
+        the all-device alternative.  `self.grad_sync` (set by distributed.enable_data_parallel_training) is called on the flat
+        gradient buffer right after the backward pass is enqueued: the ONE collective of a data-parallel step.
+        read_loss=False skips the host read of the loss value (no synchronisation; returns None)."""
         B = data.shape[0]
         tr = self._train_engine(B)
         if not tr["stale"]:
@@ -443,6 +456,10 @@ class CaloDiffusion(Diffusion):
         _lib.check(self._lib.cd_train_step(tr["h"], d.data_ptr(), nz.data_ptr(), sg.data_ptr(), cond.data_ptr(), scale, B,
                                            self._stream()), "train_step")
         tr["loss_scale"] = scale
+        sync = getattr(self, "grad_sync", None)
+        tr["grad_div"] = float(sync(tr["G"])) if sync is not None else 1.0     # enqueued behind the backward kernels
+        if not read_loss:
+            return None
         out = C.c_double()
         _lib.check(self._lib.cd_train_loss(tr["h"], C.byref(out), self._stream()), "train_loss")
         loss = torch.tensor(out.value, device=self.device, dtype=torch.float32)
@@ -456,8 +473,8 @@ class CaloDiffusion(Diffusion):
         """torch.optim.Adam's update (train/train.py:144 defaults) on the device-resident master parameters, followed by the
         re-derivation of the convolution weight layouts.  The torch parameters are refreshed lazily (sync_params_from_engine)."""
         tr = self._train
-        _lib.check(self._lib.cd_train_adam(tr["h"], float(lr), float(betas[0]), float(betas[1]), float(eps), float(tr["loss_scale"]),
-                                           self._stream()), "train_adam")
+        _lib.check(self._lib.cd_train_adam(tr["h"], float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                           float(tr["loss_scale"] * tr["grad_div"]), self._stream()), "train_adam")
         tr["stale"] = True
 
     def __del__(self):

@@ -122,6 +122,7 @@ struct cd_unet {
     float* gn_acc = nullptr; float* gn_m12 = nullptr; float* attn_dcx = nullptr; float* daddvec = nullptr; float* embed_rec = nullptr;
     float* x_noisy = nullptr; float* x0_buf = nullptr; float* coef = nullptr; double* loss_dev = nullptr;
     cd::EmbedBwdLayout embed_layout = {};
+    std::vector<__half*> bwd_tmp;  // per level: scratch gradient tensor for data gradients accumulated outside the conv epilogue
     int tin_buf_index = -1;
     std::vector<std::string> proj_names;        // state-dict prefix of every conditioned block's Linear (e.g. model.downs.0.0.mlp.1)
     float* pptr(const std::string& name) { auto it = param_index.find(name); return it == param_index.end() ? nullptr : P + params[it->second].offset; }

@@ -139,12 +139,28 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
     launch_fill_zero(h->daddvec, (long long)B * (h->addvec_stride > 0 ? h->addvec_stride : 1), st);
     cudaMemsetAsync(h->loss_dev, 0, sizeof(double), st);
     // scratch gradient tensor for data gradients that have to be accumulated outside the conv epilogue: largest (level, C)
-    static thread_local std::map<cd_unet*, std::vector<__half*>> tmp_cache;
-    std::vector<__half*>& tmp = tmp_cache[h];
+    std::vector<__half*>& tmp = h->bwd_tmp;
     if (tmp.empty()) {
         tmp.resize(h->n_levels, nullptr);
         for (int l = 0; l < h->n_levels; ++l) tmp[l] = h->dalloc<__half>((size_t)(kBwdMaxC / 8) * (size_t)h->geom[l].chunk_stride * 8, true);
     }
+    // diagnostic per-op timing of the backward pass (option "profile"): events between the ops, read back at the end
+    struct Mark { std::string name; double flops; };
+    std::vector<Mark> marks;
+    size_t nev = 0;
+    auto rec = [&]() {
+        if (h->prof_evs.size() <= nev) { cudaEvent_t ev; cudaEventCreate(&ev); h->prof_evs.push_back(ev); }
+        cudaEventRecord(h->prof_evs[nev++], st);
+    };
+    auto mark = [&](const char* what, const TapeOp* t, int lvl, int c0, int c1, double flops) {
+        if (!h->profile) return;
+        char nm[112];
+        if (t && t->kind == 0) snprintf(nm, sizeof(nm), "bwd_%s_k%d%s%s_c%d_%d_L%d", what, t->kz * t->kp * t->kr, t->stride > 1 ? "s2" : "", t->transposed ? "T" : "", c0, c1, lvl);
+        else snprintf(nm, sizeof(nm), "bwd_%s_c%d_L%d", what, c0, lvl);
+        marks.push_back({nm, flops});
+        rec();
+    };
+    if (h->profile) rec();
     for (int i = (int)h->tape.size() - 1; i >= 0; --i) {
         const TapeOp& t = h->tape[i];
         if (t.kind == 3) {
@@ -156,6 +172,7 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
             if (!p.dw || !p.db || !p.bias) return fail("training: final conv parameters missing");
             launch_loss_backward(p, B, st);
             ginit[t.src] = 1;
+            mark("loss", nullptr, 0, t.C, 0, 0.0);
         } else if (t.kind == 1) {
             if (!ginit[t.dst]) return fail("training: GroupNorm output %d has no gradient (tape order)", t.dst);
             const Geom& g = h->geom[t.level_in];
@@ -176,6 +193,7 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
             }
             if (!p.gamma || !p.beta || !p.dgamma || !p.dbeta) return fail("training: GroupNorm parameters %s missing", t.gname.c_str());
             launch_gn_backward(p, B, st);
+            mark(t.residual >= 0 ? "gn_res" : "gn", nullptr, t.level_in, t.C, 0, 0.0);
             ginit[t.src] = 1;
             if (t.residual >= 0) ginit[t.residual] = 1;
             if (t.residual2 >= 0) ginit[t.residual2] = 1;
@@ -190,6 +208,7 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
             if (!p.wout || !p.dwout || !p.dbout) return fail("training: attention parameters missing");
             if (launch_attn_backward(p, B, st)) return fail("training: attention backward does not support %d channels", t.C);
             ginit[t.qkv] = 1;
+            mark("attn", nullptr, t.level_in, t.C, 0, 0.0);
         } else if (t.kind == 0) {
             if (!ginit[t.dst]) return fail("training: conv output %d (%s) has no gradient (tape order)", t.dst, t.wname.c_str());
             const Geom& gi = h->geom[t.level_in];
@@ -197,7 +216,12 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
             const int taps = t.kz * t.kp * t.kr;
             float* dw = h->gptr(t.wname);
             if (!dw) return fail("training: %s has no gradient slot", t.wname.c_str());
-            if (!t.bias_via_gn && !t.bname.empty()) launch_channel_sum(go, h->bufs[t.dst].grad, t.Cout, h->gptr(t.bname), B, st);
+            const double mo = (double)go.Z * go.P * go.R, mi = (double)gi.Z * gi.P * gi.R;
+            const double cflops = 2.0 * (t.transposed ? mi : mo) * t.Cin_pad * t.Cout * taps * B;     // executed MACs x 2
+            if (!t.bias_via_gn && !t.bname.empty()) {
+                launch_channel_sum(go, h->bufs[t.dst].grad, t.Cout, h->gptr(t.bname), B, st);
+                mark("bias", nullptr, t.level_out, t.Cout, 0, 0.0);
+            }
             ConvParams p;       // the forward convolution, for the SIMT adjoints
             p.gin = gi; p.gout = go; p.nsrc = (int)t.srcs.size(); p.Cin_total = t.Cin_pad;
             for (int s = 0; s < p.nsrc; ++s) { p.src[s].base = h->bufs[t.srcs[s]].ptr; p.src[s].C = h->bufs[t.srcs[s]].C; }
@@ -214,21 +238,26 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
                 w.src_chunks0 = h->bufs[t.srcs[0]].C / 8; w.dy = h->bufs[t.dst].grad; w.dw = dw;
                 w.Cin_pad = t.Cin_pad; w.Cin_real = t.Cin_real; w.Cout = t.Cout; w.taps = taps; w.B = B;
                 wdone = launch_wgrad_mma(w, st) == 0;
+                if (wdone) mark("wgrad_mma", &t, t.level_in, t.Cin_pad, t.Cout, cflops);
             }
             if (!wdone) {
                 if (t.srcs.size() != 1) return fail("training: weight gradient of %s (two sources, %d -> %d) has no kernel", t.wname.c_str(), t.Cin_pad, t.Cout);
                 launch_conv_strided_backward(p, h->bufs[t.srcs[0]].ptr, h->bufs[t.dst].grad, nullptr, 0, dw, t.Cin_real, t.transposed, st);
+                mark("wgrad_simt", &t, t.level_in, t.Cin_pad, t.Cout, cflops);
             }
             if (t.need_dgrad) {
                 if (unit) {
                     for (size_t s = 0; s < t.srcs.size(); ++s) {
                         if (conv_dgrad(h, t, (int)s, B, ginit[t.srcs[s]] != 0, tmp[t.level_in], st)) return 1;
                         ginit[t.srcs[s]] = 1;
+                        const int Cs = h->bufs[t.srcs[s]].C;
+                        mark(t.wdm[s] && h->conv_backend == 0 ? "dgrad_mma" : "dgrad_simt", &t, t.level_in, t.Cout, Cs, cflops * Cs / t.Cin_pad);
                     }
                 } else {
                     launch_conv_strided_backward(p, nullptr, h->bufs[t.dst].grad, h->bufs[t.srcs[0]].grad, ginit[t.srcs[0]], nullptr, t.Cin_real,
                                                  t.transposed, st);
                     ginit[t.srcs[0]] = 1;
+                    mark("dgrad_simt", &t, t.level_in, t.Cout, t.Cin_pad, cflops);
                 }
             }
         }
@@ -254,6 +283,16 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
         float* db = h->gptr(h->proj_names[k] + ".bias");
         if (!dW || !db) return fail("training: projection %d has no gradient slot", k);
         launch_linear_wgrad(h->daddvec + e.poff[k], h->addvec_stride, h->embed_rec + L.cvec, L.stride, B, e.pC[k], e.cond_dim, dW, db, st);
+    }
+    mark("embed_mlps", nullptr, 0, e.cond_dim, 0, 0.0);
+    if (h->profile && nev > 1) {
+        cudaEventSynchronize(h->prof_evs[nev - 1]);
+        for (size_t k = 0; k < marks.size(); ++k) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, h->prof_evs[k], h->prof_evs[k + 1]);
+            ProfAcc& a = h->prof[marks[k].name];
+            a.count += 1; a.ms += ms; a.flops += marks[k].flops;
+        }
     }
     cudaError_t err = cudaPeekAtLastError();
     if (err != cudaSuccess) return fail("training backward: %s", cudaGetErrorString(err));

@@ -80,3 +80,62 @@ def sample_sharded(model, energy, layers, num_steps=400, sample_offset=0, start=
     finally:
         sampler.shower_offset = prev
     return gather_showers(x, n)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Data-parallel training (BASELINE config 5): every rank runs the training step of
+# train/train_diffusion.py:42-66 on its own batch, weights replicated; the only exchange is ONE all-reduce of the flat fp32
+# gradient buffer (2.2 M elements, 8.85 MB for Dataset 2) between the backward pass and the optimizer step.  On NVSwitch
+# that is tens of microseconds against a step of tens of milliseconds, so it is a single bucket enqueued behind the last
+# backward kernel, not a pipeline of buckets.
+# ----------------------------------------------------------------------------------------------------------------------
+def allreduce_gradients(flat):
+    """Sum the flat gradient buffer over the ranks in place; returns the divisor (world size) the optimizer step folds into
+    its loss scale, so the average costs no extra pass over the buffer."""
+    rank, ws = world()
+    if ws > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    return float(ws)
+
+
+def broadcast_parameters(module, src=0):
+    """Rank `src`'s parameters and buffers to every rank (what DistributedDataParallel does at construction)."""
+    rank, ws = world()
+    if ws == 1:
+        return
+    with torch.no_grad():
+        for t in list(module.parameters()) + list(module.buffers()):
+            dist.broadcast(t.detach(), src)       # (detach shares the version counter: the engine sees the change)
+
+
+def enable_data_parallel_training(model, src=0):
+    """Make `model.training_loss` (and so `compute_loss(...).backward()` with any torch optimizer, or `fused_adam_step`) a
+    data-parallel step: replicate rank `src`'s weights now, and all-reduce the flat gradient after every backward pass."""
+    broadcast_parameters(model.model, src)
+    model.grad_sync = allreduce_gradients
+    return model
+
+
+class DataParallelTrainer:
+    """The reference's training loop body (train/train_diffusion.py:42-66: compute_loss -> backward -> optimizer.step) for one
+    rank of a data-parallel job, all on the device: cd_train_step, one all-reduce of the flat gradient, fused Adam.
+
+        trainer = DataParallelTrainer(model, lr=4e-4)
+        for E, layers, data in loader:          # THIS rank's batch (`shard_range` cuts a global batch)
+            loss = trainer.step(data, E, layers)
+    """
+
+    def __init__(self, model, lr=4e-4, betas=(0.9, 0.999), eps=1e-8, src=0):
+        self.model, self.lr, self.betas, self.eps = enable_data_parallel_training(model, src), lr, betas, eps
+
+    def step(self, data, E, layers=None, noise=None, time=None, rnd_normal=None, read_loss=True):
+        """One optimizer step on this rank's batch.  Returns this rank's loss (a 0-d tensor), or None with read_loss=False
+        (then nothing in the step synchronises with the host)."""
+        m = self.model
+        m._read_loss = read_loss
+        try:
+            loss = m.loss_function(m, data, E, noise=noise, time=time, layers=layers, rnd_normal=rnd_normal)
+        finally:
+            m._read_loss = True
+        m.fused_adam_step(self.lr, self.betas, self.eps)
+        return loss

@@ -73,4 +73,4 @@ class hybrid_weight(Loss):
         """x_noisy = data + sigma*noise; x0 = denoise(x_noisy); weight = 1 + 1/sigma^2; l2 (models/loss.py:168-179, 103-104)."""
         if self.loss_type != "l2":
             raise NotImplementedError(f"the B200 training step implements LOSS_TYPE 'l2' (got {self.loss_type!r})")
-        return model.training_loss(data, E, sigma, noise, layers)
+        return model.training_loss(data, E, sigma, noise, layers, read_loss=getattr(model, "_read_loss", True))

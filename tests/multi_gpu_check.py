@@ -49,7 +49,55 @@ def main():
         assert e < 5e-3, e
         print("multi_gpu_check: OK")
     dist.barrier()
+    train_check(rank, ws, c, cfg)
+    dist.barrier()
     dist.destroy_process_group()
+
+
+def train_check(rank, ws, c, cfg):
+    """Data-parallel training step (row E2): after the one all-reduce every rank holds the MEAN of the ranks' gradients (rank 0
+    recomputes every shard's gradient alone), and after fused Adam every rank holds identical parameters."""
+    nb = 4                                   # showers per rank
+    g = torch.Generator().manual_seed(21)
+    n = nb * ws
+    data = torch.randn([n] + list(c["shape"]), generator=g).cuda()
+    E = torch.rand(n, 1, generator=g).cuda()
+    L = torch.randn(n, 46, generator=g).cuda()
+    noise = torch.randn([n] + list(c["shape"]), generator=g).cuda()
+    rnd = torch.randn(n, generator=g).cuda()
+    m = CaloDiffusion(cfg, n_steps=cfg["NSTEPS"], loss_type=cfg["LOSS_TYPE"], max_batch=nb)
+    sd = dict(c["sd"])
+    if rank != 0:                            # the broadcast must overwrite these
+        sd = {k: v + 0.01 for k, v in sd.items()}
+    m.load_state_dict(sd)
+    tr = D.DataParallelTrainer(m, lr=1e-3)
+    lo, hi = D.shard_range(n, rank, ws)
+    sl = slice(lo, hi)
+    loss = m.loss_function(m, data[sl], E[sl], noise=noise[sl], layers=L[sl], rnd_normal=rnd[sl])
+    assert bool(torch.isfinite(loss))
+    G = m.grad_buffer().clone()
+    assert m._train["grad_div"] == float(ws)
+    if rank == 0:
+        m.grad_sync = None
+        acc = torch.zeros_like(G)
+        for r in range(ws):
+            a, b = D.shard_range(n, r, ws)
+            s2 = slice(a, b)
+            m.loss_function(m, data[s2], E[s2], noise=noise[s2], layers=L[s2], rnd_normal=rnd[s2])
+            acc += m.grad_buffer()
+        e = float((acc - G).norm() / acc.norm())
+        print(f"multi_gpu_check: all-reduced gradient vs sum of shard gradients rel-L2 = {e:.3e}")
+        assert e < 1e-5, e                   # fp32 atomics in the weight-gradient kernels: not bit-reproducible run to run
+        m.grad_sync = D.allreduce_gradients
+    dist.barrier()
+    for _ in range(2):
+        tr.step(data[sl], E[sl], L[sl], noise=noise[sl], rnd_normal=rnd[sl])
+    P = m._train["P"].clone()
+    P0 = P.clone()
+    dist.broadcast(P0, 0)
+    assert torch.equal(P, P0), "ranks hold different parameters after data-parallel steps"
+    if rank == 0:
+        print("multi_gpu_check: data-parallel training OK")
 
 
 if __name__ == "__main__":

@@ -102,3 +102,86 @@ def test_sample_sharded_world_size_2_gloo(n, own_start):
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(r[1] for r in res), res
     assert all(r[2] == (n, 3, 4) for r in res)
+
+
+# ---- data-parallel training (row E2): one all-reduce of the flat gradient between backward and the optimizer step ----------
+class _FakeTrainModel:
+    """Stands in for CaloDiffusion's training interface with a linear least-squares model in torch: the same hooks
+    (`grad_sync`, flat gradient buffer times a loss scale, fused Adam dividing by loss_scale * grad_div)."""
+
+    def __init__(self, seed):
+        self.model = torch.nn.Linear(5, 1, bias=True)
+        with torch.no_grad():
+            for p in self.model.parameters():
+                p.copy_(torch.randn(p.shape, generator=torch.Generator().manual_seed(seed)))
+        self.grad_sync = None
+        self.G = torch.zeros(6)
+        self.m, self.v, self.t = torch.zeros(6), torch.zeros(6), 0
+        self.loss_scale, self.grad_div = 64.0, 1.0
+
+    def loss_function(self, model, data, E, noise=None, time=None, layers=None, rnd_normal=None):
+        w, b = self.model.weight.detach().reshape(-1), self.model.bias.detach()
+        r = E @ w + b - data
+        g = torch.cat([(2 * r.view(-1, 1) * E).mean(0), (2 * r).mean().view(1)])
+        self.G = g * self.loss_scale
+        self.grad_div = float(self.grad_sync(self.G)) if self.grad_sync is not None else 1.0
+        return (r ** 2).mean() if getattr(self, "_read_loss", True) else None
+
+    def fused_adam_step(self, lr, betas, eps):
+        g = self.G / (self.loss_scale * self.grad_div)
+        self.t += 1
+        self.m = betas[0] * self.m + (1 - betas[0]) * g
+        self.v = betas[1] * self.v + (1 - betas[1]) * g * g
+        upd = lr * (self.m / (1 - betas[0] ** self.t)) / ((self.v / (1 - betas[1] ** self.t)).sqrt() + eps)
+        with torch.no_grad():
+            self.model.weight -= upd[:5].view(1, 5)
+            self.model.bias -= upd[5:]
+
+
+def _train_data(n):
+    g = torch.Generator().manual_seed(3)
+    return torch.randn(n, 5, generator=g), torch.randn(n, generator=g)
+
+
+def _train_worker(rank, ws, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        m = _FakeTrainModel(seed=100 + rank)                 # ranks start from DIFFERENT weights: the broadcast must fix that
+        tr = D.DataParallelTrainer(m, lr=1e-2)
+        X, y = _train_data(16)
+        lo, hi = D.shard_range(16, rank, ws)
+        losses = [float(tr.step(y[lo:hi], X[lo:hi])) for _ in range(3)]
+        assert tr.step(y[lo:hi], X[lo:hi], read_loss=False) is None
+        q.put((rank, m.model.weight.detach().clone(), m.model.bias.detach().clone(), losses, m.grad_div))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_training_world_size_2_gloo():
+    """Two ranks on half a batch each end up with identical weights, equal to one process stepping on the full batch (equal
+    shard sizes: the mean of the shard gradients is the full-batch gradient), starting from rank 0's weights."""
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_train_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
+    assert res[0][4] == 2.0 and res[1][4] == 2.0
+    single = _FakeTrainModel(seed=100)
+    tr = D.DataParallelTrainer(single, lr=1e-2)              # no process group: world size 1, no collective
+    X, y = _train_data(16)
+    for _ in range(4):
+        tr.step(y, X)
+    assert single.grad_div == 1.0
+    assert torch.allclose(single.model.weight, res[0][1], atol=1e-6), (single.model.weight, res[0][1])
+    assert torch.allclose(single.model.bias, res[0][2], atol=1e-6)

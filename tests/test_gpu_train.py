@@ -105,3 +105,48 @@ def test_dropin_training_loop_decreases_loss():
         losses.append(float(loss))
     print("drop-in loop losses:", [f"{v:.4e}" for v in losses])
     assert losses[-1] < losses[0] and np.isfinite(losses).all()
+
+
+def test_grad_sync_hook_and_trainer_single_process():
+    """The data-parallel hooks on one GPU: `grad_sync` sees the flat gradient right after the backward pass and its return
+    value divides the gradient (both in loss.backward() and in the fused Adam); DataParallelTrainer.step without a process
+    group equals compute_loss + fused_adam_step; read_loss=False returns None and leaves the same gradient."""
+    from calodiffusion_b200.distributed import DataParallelTrainer
+    m, c = _model("ds2")
+    E, layers, data, noise, rnd, time = [None if t is None else t.cuda() for t in train_inputs(c["shape"], 2, 1, 46)]
+    loss = m.loss_function(m, data, E, noise=noise, layers=layers, rnd_normal=rnd)
+    loss.backward()
+    g1 = torch.cat([p.grad.reshape(-1) for p in m.model.parameters()]).clone()
+    G1 = m.grad_buffer().clone()
+    seen = []
+
+    def fake_sync(flat):
+        seen.append(flat.data_ptr())
+        flat.mul_(3.0)              # "sum over 3 identical ranks"
+        return 3.0
+    m.grad_sync = fake_sync
+    for p in m.model.parameters():
+        p.grad = None
+    loss2 = m.loss_function(m, data, E, noise=noise, layers=layers, rnd_normal=rnd)
+    loss2.backward()
+    g2 = torch.cat([p.grad.reshape(-1) for p in m.model.parameters()])
+    assert seen == [m.grad_buffer().data_ptr()]
+    e = float((g2 - g1).norm() / g1.norm())
+    print(f"gradient through a x3 / 3 grad_sync vs plain: rel-L2 {e:.2e}")
+    assert e < 1e-5                  # fp32 atomics in the weight-gradient kernels: not bit-reproducible run to run
+    assert m.loss_function(m, data, E, noise=noise, layers=layers, rnd_normal=rnd) is not None
+    m._read_loss = False
+    assert m.loss_function(m, data, E, noise=noise, layers=layers, rnd_normal=rnd) is None
+    m._read_loss = True
+    assert float((m.grad_buffer() / 3.0 - G1).norm() / G1.norm()) < 1e-5
+    # trainer without a process group: no collective, plain fused Adam
+    m2, _ = _model("ds2")
+    m3, _ = _model("ds2")
+    tr = DataParallelTrainer(m2, lr=1e-3)
+    l2 = tr.step(data, E, layers, noise=noise, rnd_normal=rnd)
+    l3 = m3.loss_function(m3, data, E, noise=noise, layers=layers, rnd_normal=rnd)
+    m3.fused_adam_step(1e-3)
+    assert abs(float(l2) - float(l3)) < 1e-5 * abs(float(l3))
+    d = float((m2._train["P"] - m3._train["P"]).abs().max())
+    print(f"trainer vs manual step: max parameter difference {d:.2e}")
+    assert d < 5e-4                   # Adam's first step is +-lr per element; differences only where a gradient is ~0
