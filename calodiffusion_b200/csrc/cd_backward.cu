@@ -279,6 +279,14 @@ constexpr int kWgRows = 128;          // rows per chunk (K of the MMAs: 8 k16 st
 constexpr int kWgWarps = 8;
 constexpr int kWgMaxTapsPerWarp = 4;  // 27 taps over 8 warps
 
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
+    const uint32_t n = valid ? 16u : 0u;       // src-size 0: the 16 bytes are zero-filled, the source is not read
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(n) : "memory");
+}
+
+// The CTA walks a CONTIGUOUS range of 128-row chunks, so the X window (chunk + halo rows on both sides) slides: it lives in a
+// ring of wrows + 128 rows per chunk plane and every step fetches only the 128 new rows (cp.async, overlapped with the MMAs
+// of the current chunk) - X is read ~once instead of (128 + 2*halo)/128 times.  dY chunks are double-buffered the same way.
 __global__ void __launch_bounds__(kWgWarps * 32) wgrad_mma_kernel(WgradParams p) {
     extern __shared__ __align__(16) unsigned char wsm[];
     const Geom& g = p.g;
@@ -286,14 +294,24 @@ __global__ void __launch_bounds__(kWgWarps * 32) wgrad_mma_kernel(WgradParams p)
     const int cib = blockIdx.y / p.ncob, cob = blockIdx.y - cib * p.ncob;     // 32-channel blocks of ci / co
     const int halo = p.taps == 27 ? g.plane + g.Rp + 1 : 0;
     const int wrows = kWgRows + 2 * halo;                                       // X window rows
-    __half* xs = reinterpret_cast<__half*>(wsm);                               // [4 chunks][wrows][8]
-    __half* ys = xs + (size_t)4 * wrows * 8;                                   // [4 chunks][kWgRows][8]
+    const int ring = wrows + kWgRows;
+    __half* xs = reinterpret_cast<__half*>(wsm);                               // [4 chunks][ring][8]
+    __half* ys = xs + (size_t)4 * ring * 8;                                    // [2][4 chunks][kWgRows][8]
     // source tensor / chunk of this ci block (a conv over a concatenated input has two sources)
     const int c0 = cib * 4;                                                     // first 8-channel chunk of the block
     const __half* xsrc; int xk0;
     if (c0 < p.src_chunks0) { xsrc = p.x0; xk0 = c0; } else { xsrc = p.x1; xk0 = c0 - p.src_chunks0; }
-    int ntap_w = 0, taps_w[kWgMaxTapsPerWarp];
-    for (int t = warp; t < p.taps; t += kWgWarps) taps_w[ntap_w++] = t;
+    const int navail = (c0 < p.src_chunks0 ? p.src_chunks0 : p.Cin_pad / 8) - c0;   // chunk planes that exist (a 16-channel input has 2)
+    // 27 taps: warps split the taps.  1 tap: every warp takes it and the warps split the k16 steps of each chunk instead.
+    const bool ksplit = p.taps == 1;
+    int ntap_w = 0, taps_w[kWgMaxTapsPerWarp], off_w[kWgMaxTapsPerWarp];
+    if (ksplit) { taps_w[0] = 0; ntap_w = 1; }
+    else for (int t = warp; t < p.taps; t += kWgWarps) taps_w[ntap_w++] = t;
+#pragma unroll
+    for (int a = 0; a < kWgMaxTapsPerWarp; ++a) {
+        off_w[a] = 0;
+        if (a < ntap_w && p.taps == 27) { const int t = taps_w[a]; off_w[a] = (t / 9 - 1) * g.plane + ((t / 3) % 3 - 1) * g.Rp + (t % 3 - 1); }
+    }
     float acc[kWgMaxTapsPerWarp][2][4][4];       // [tap][ci 16-tile][co 8-tile][frag]
 #pragma unroll
     for (int a = 0; a < kWgMaxTapsPerWarp; ++a)
@@ -305,60 +323,80 @@ __global__ void __launch_bounds__(kWgWarps * 32) wgrad_mma_kernel(WgradParams p)
                 for (int e = 0; e < 4; ++e) acc[a][i][j][e] = 0.f;
     const long long nrows = (long long)p.B * g.rows_per_sample;
     const int nchunks = (int)((nrows + kWgRows - 1) / kWgRows);
-    const int mi = lane >> 3, mr = lane & 7;
-    for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
-        const long long m0 = (long long)ch * kWgRows;
-        __syncthreads();
-        // stage X window rows [m0 - halo, m0 + 128 + halo) (guard rows of the tensor absorb the ends) and dY rows [m0, m0+128)
-        for (int i = threadIdx.x; i < 4 * wrows; i += blockDim.x) {
-            const int k = i / wrows, r = i - k * wrows;
-            const long long row = m0 - halo + r;
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (row >= -(long long)g.guard && row < nrows + g.guard) v = *reinterpret_cast<const uint4*>(xsrc + plcp_offset(g, xk0 + k, row));
-            *reinterpret_cast<uint4*>(xs + ((size_t)k * wrows + r) * 8) = v;
-        }
-        for (int i = threadIdx.x; i < 4 * kWgRows; i += blockDim.x) {
-            const int k = i / kWgRows, r = i - k * kWgRows;
-            const long long row = m0 + r;
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (row < nrows) {
-                const uint32_t rem = (uint32_t)(row % g.rows_per_sample);
-                if (decode_subrow(g, rem).kind == 0) v = *reinterpret_cast<const uint4*>(p.dy + plcp_offset(g, cob * 4 + k, row));
+    const int per = (nchunks + gridDim.x - 1) / gridDim.x;
+    const int c_lo = blockIdx.x * per, c_hi = min(nchunks, c_lo + per);
+    if (c_lo >= c_hi) return;
+    const long long rbase = (long long)c_lo * kWgRows - halo;                  // global row of ring-relative row 0
+    // rows [rel0, rel0 + count) of the window sequence into their ring slots
+    auto load_x = [&](int rel0, int count) {
+        for (int k = 0; k < 4; ++k)
+            for (int r = threadIdx.x; r < count; r += kWgWarps * 32) {
+                const int rel = rel0 + r;
+                const long long row = rbase + rel;
+                const bool ok = k < navail && row >= -(long long)g.guard && row < nrows + g.guard;
+                cp_async16_zfill(xs + ((size_t)k * ring + rel % ring) * 8, ok ? (const void*)(xsrc + plcp_offset(g, xk0 + k, row)) : (const void*)xsrc, ok);
             }
-            *reinterpret_cast<uint4*>(ys + ((size_t)k * kWgRows + r) * 8) = v;
+    };
+    auto load_y = [&](int buf, int ch) {
+        for (int i = threadIdx.x; i < 4 * kWgRows; i += kWgWarps * 32) {
+            const int k = i / kWgRows, r = i - k * kWgRows;
+            const long long row = (long long)ch * kWgRows + r;
+            bool ok = row < nrows;
+            if (ok) ok = decode_subrow(g, (uint32_t)(row % g.rows_per_sample)).kind == 0;     // interior rows only
+            cp_async16_zfill(ys + (((size_t)buf * 4 + k) * kWgRows + r) * 8, ok ? (const void*)(p.dy + plcp_offset(g, cob * 4 + k, row)) : (const void*)p.dy, ok);
         }
+    };
+    load_x(0, wrows);
+    load_y(0, c_lo);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const int mi = lane >> 3, mr = lane & 7;
+    int wstart = 0;                                                             // ring slot of the window's first row
+    for (int i = 0; c_lo + i < c_hi; ++i) {
+        if (c_lo + i + 1 < c_hi) { load_x(wrows + i * kWgRows, kWgRows); load_y((i + 1) & 1, c_lo + i + 1); }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
         __syncthreads();
+        const __half* yb = ys + (size_t)(i & 1) * 4 * kWgRows * 8;
+        int abase[kWgMaxTapsPerWarp];
 #pragma unroll
         for (int a = 0; a < kWgMaxTapsPerWarp; ++a) {
-            if (a >= ntap_w) break;
-            const int tap = taps_w[a];
-            int off = 0;
-            if (p.taps == 27) { const int dz = tap / 9 - 1, dp = (tap / 3) % 3 - 1, dr = tap % 3 - 1; off = dz * g.plane + dp * g.Rp + dr; }
-            const int xr0 = halo + off;          // window row of chunk row 0 for this tap
+            int b = wstart + halo + off_w[a] + (mi >> 1) * 8 + mr;            // < ring + wrows < 2*ring
+            if (b >= ring) b -= ring;
+            abase[a] = b;
+        }
 #pragma unroll 2
-            for (int k16 = 0; k16 < kWgRows / 16; ++k16) {
-                // B fragments (dY): matrices (rows k 0-7 | 8-15) x (co chunk j): x4.trans -> b0,b1 of two co 8-tiles
-                uint32_t bf[4][2];
+        for (int k16 = ksplit ? warp : 0; k16 < kWgRows / 16; k16 += ksplit ? kWgWarps : 1) {
+            // B fragments (dY): matrices (rows k 0-7 | 8-15) x (co chunk j): x4.trans -> b0,b1 of two co 8-tiles
+            uint32_t bf[4][2];
 #pragma unroll
-                for (int jj = 0; jj < 2; ++jj) {
-                    uint32_t r[4];
-                    // m0: (k 0-7, chunk 2jj) m1: (k 8-15, chunk 2jj) m2: (k 0-7, chunk 2jj+1) m3: (k 8-15, chunk 2jj+1)
-                    const int chunk = 2 * jj + (mi >> 1), krow = k16 * 16 + (mi & 1) * 8 + mr;
-                    ldsm_x4_t(smem_u32(ys + ((size_t)chunk * kWgRows + krow) * 8), r);
-                    bf[2 * jj][0] = r[0]; bf[2 * jj][1] = r[1]; bf[2 * jj + 1][0] = r[2]; bf[2 * jj + 1][1] = r[3];
-                }
+            for (int jj = 0; jj < 2; ++jj) {
+                uint32_t r[4];
+                // m0: (k 0-7, chunk 2jj) m1: (k 8-15, chunk 2jj) m2: (k 0-7, chunk 2jj+1) m3: (k 8-15, chunk 2jj+1)
+                const int chunk = 2 * jj + (mi >> 1), krow = k16 * 16 + (mi & 1) * 8 + mr;
+                ldsm_x4_t(smem_u32(yb + ((size_t)chunk * kWgRows + krow) * 8), r);
+                bf[2 * jj][0] = r[0]; bf[2 * jj][1] = r[1]; bf[2 * jj + 1][0] = r[2]; bf[2 * jj + 1][1] = r[3];
+            }
+#pragma unroll
+            for (int a = 0; a < kWgMaxTapsPerWarp; ++a) {
+                if (a >= ntap_w) break;
+                int krow = abase[a] + k16 * 16;
+                if (krow >= ring) krow -= ring;
 #pragma unroll
                 for (int it = 0; it < 2; ++it) {
                     // A fragment (X^T), ci 16-tile it: a0 (ci 0-7, k 0-7) a1 (ci 8-15, k 0-7) a2 (ci 0-7, k 8-15) a3 (ci 8-15, k 8-15)
                     uint32_t af[4];
-                    const int chunk = 2 * it + (mi & 1), krow = xr0 + k16 * 16 + (mi >> 1) * 8 + mr;
-                    ldsm_x4_t(smem_u32(xs + ((size_t)chunk * wrows + krow) * 8), af);
+                    const int chunk = 2 * it + (mi & 1);
+                    ldsm_x4_t(smem_u32(xs + ((size_t)chunk * ring + krow) * 8), af);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) mma16816(acc[a][it][j], af, bf[j][0], bf[j][1]);
                 }
             }
         }
+        __syncthreads();
+        wstart += kWgRows;
+        if (wstart >= ring) wstart -= ring;
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     // D fragment: c0,c1 -> (row g, cols 2t,2t+1), c2,c3 -> (row g+8, ...)   row = ci within the 16-tile, col = co within the 8-tile
     const int gq = lane >> 2, tq = lane & 3;
 #pragma unroll
@@ -446,7 +484,9 @@ __global__ void conv_strided_dgrad_kernel(ConvParams p, const __half* __restrict
     store8(o, pack8(acc));
 }
 
-// block: 32 (co) x 8 (ci quads) threads; grid (taps, ci blocks * co blocks, row splits)
+// block: 32 (co) x 8 (ci quads) threads; grid (taps, ci blocks * co blocks, row splits).  The walk is over the COARSE grid, so
+// every staged (voxel, tap) pair is a real product: output voxels of a strided conv; (circularly padded) input voxels of a
+// transposed conv, whose tap (a,b,c) lands on output (2z+a-pz, 2q+b-(kp-1), 2r+c-pr).
 __global__ void __launch_bounds__(256) conv_strided_wgrad_kernel(ConvParams p, const __half* __restrict__ x, const __half* __restrict__ dy,
                                                                  float* __restrict__ dw, int Cin_real, int master_transposed) {
     __shared__ float xs[32][33], ys[32][33];
@@ -456,13 +496,14 @@ __global__ void __launch_bounds__(256) conv_strided_wgrad_kernel(ConvParams p, c
     const int a = tap / (p.kp * p.kr), bq = (tap / p.kr) % p.kp, c = tap % p.kr;
     const Geom& go = p.gout;
     const Geom& gi = p.gin;
-    const long long nvox = (long long)p.B * go.Z * go.P * go.R;
+    const int wZ = p.transposed ? gi.Z : go.Z, wP = p.transposed ? gi.P + 2 * p.cp : go.P, wR = p.transposed ? gi.R : go.R;
+    const int vps = wZ * wP * wR;
+    const long long nvox = (long long)p.B * vps;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    const int vps = go.Z * go.P * go.R;
     for (long long v0 = (long long)blockIdx.z * 32; v0 < nvox; v0 += (long long)gridDim.z * 32) {
         __syncthreads();
-        // stage 32 output voxels: dY[v][co block] and the X value this tap reads for them (0 outside the grid)
+        // stage 32 walk voxels: dY[out][co block] and X[in][ci block] of this tap (0 where the pair does not exist)
         for (int i = threadIdx.x; i < 32 * 8; i += 256) {
             const int r = i >> 3, k = i & 7;            // voxel r, chunk k (0-3: dY co chunks, 4-7: X ci chunks)
             const long long v = v0 + r;
@@ -470,24 +511,23 @@ __global__ void __launch_bounds__(256) conv_strided_wgrad_kernel(ConvParams p, c
             if (v < nvox) {
                 const int b = (int)(v / vps);
                 int rem = (int)(v - (long long)b * vps);
-                const int zo = rem / (go.P * go.R); rem -= zo * go.P * go.R;
-                const int po = rem / go.R, ro = rem - po * go.R;
-                if (k < 4) {
-                    unpack8(load8(dy + plcp_offset(go, cob * 4 + k, interior_row(go, b, zo, po, ro))), f);
+                const int wz = rem / (wP * wR); rem -= wz * wP * wR;
+                const int wp = rem / wR, wr = rem - wp * wR;
+                int zo, po, ro, zi, pin, rin;
+                if (!p.transposed) {
+                    zo = wz; po = wp; ro = wr;
+                    zi = zo * p.sz + a - p.pz; rin = ro * p.sr + c - p.pr; pin = po * p.sp + bq - p.cp;
                 } else {
-                    int zi, pin, rin; bool ok = true;
-                    if (!p.transposed) {
-                        zi = zo * p.sz + a - p.pz; rin = ro * p.sr + c - p.pr; pin = po * p.sp + bq - p.cp;
-                    } else {
-                        int t = zo + p.pz - a; ok = ok && t >= 0 && t % p.sz == 0; zi = t / p.sz;
-                        t = ro + p.pr - c; ok = ok && t >= 0 && t % p.sr == 0; rin = t / p.sr;
-                        t = po + (p.kp - 1) - bq; ok = ok && t >= 0 && t % p.sp == 0; const int q = t / p.sp;
-                        ok = ok && q < gi.P + 2 * p.cp; pin = q - p.cp;
-                    }
-                    pin %= gi.P; if (pin < 0) pin += gi.P;
-                    ok = ok && zi >= 0 && zi < gi.Z && rin >= 0 && rin < gi.R;
-                    ok = ok && (cib * 4 + (k - 4)) < (p.Cin_total >> 3);          // a 16-channel input has two chunk planes only
-                    if (ok) unpack8(load8(x + plcp_offset(gi, cib * 4 + (k - 4), interior_row(gi, b, zi, pin, rin))), f);
+                    zi = wz; rin = wr; pin = wp - p.cp;
+                    zo = zi * p.sz + a - p.pz; ro = rin * p.sr + c - p.pr; po = wp * p.sp + bq - (p.kp - 1);
+                }
+                pin %= gi.P; if (pin < 0) pin += gi.P;
+                const bool ok = zi >= 0 && zi < gi.Z && rin >= 0 && rin < gi.R && zo >= 0 && zo < go.Z && po >= 0 && po < go.P &&
+                                ro >= 0 && ro < go.R;
+                if (ok) {
+                    if (k < 4) unpack8(load8(dy + plcp_offset(go, cob * 4 + k, interior_row(go, b, zo, po, ro))), f);
+                    else if ((cib * 4 + (k - 4)) < (p.Cin_total >> 3))          // a 16-channel input has two chunk planes only
+                        unpack8(load8(x + plcp_offset(gi, cib * 4 + (k - 4), interior_row(gi, b, zi, pin, rin))), f);
                 }
             }
             float (*dst)[33] = k < 4 ? ys : xs;
@@ -520,13 +560,21 @@ __global__ void __launch_bounds__(256) channel_sum_kernel(Geom g, const __half* 
     for (int c = threadIdx.x; c < C; c += blockDim.x) s_acc[c] = 0.f;
     __syncthreads();
     const int nch = C >> 3;
-    for (long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x; row < nrows; row += (long long)gridDim.x * blockDim.x) {
-        if (decode_subrow(g, (uint32_t)(row % g.rows_per_sample)).kind != 0) continue;
-        for (int k = 0; k < nch; ++k) {
+    for (int k = 0; k < nch; ++k) {
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x; row < nrows; row += (long long)gridDim.x * blockDim.x) {
+            if (decode_subrow(g, (uint32_t)(row % g.rows_per_sample)).kind != 0) continue;
             float f[8];
             unpack8(load8(t + plcp_offset(g, k, row)), f);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[k * 8 + j], f[j]);
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float v = acc[j];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[k * 8 + j], v);
         }
     }
     __syncthreads();
@@ -878,9 +926,41 @@ __global__ void adam_kernel(float* __restrict__ w, float* __restrict__ m, float*
 // master conv weight -> the layouts the kernels read.  mode 0: fp32 [tap][ci_pad][co]; 1: fp16 R-stacked tcgen05 layout (see
 // mma_pack_weights); 2 / 3: the same two layouts of the data-gradient convolution (taps flipped, channels transposed,
 // output channels = input channels [ci_lo, ci_lo + n_out) of the forward conv)
+//   4: gather-tcgen05 layout [tap][kc][co][8] (gather_pack_weights); 5: the merged output-pair layout of the stride-2 transposed
+//   conv [(a*kp+b)*3+dr+1][kc][2*Cout][8] (gather_pack_weights_pairT); both read the mode-0 array `pk`, optionally with the
+//   channel roles swapped.
 __global__ void repack_conv_kernel(RepackParams p) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
+    if (p.mode >= 4) {
+        const int Cg_in = p.swap ? p.Cout : p.Cin_pad, Cg_out = p.swap ? p.Cin_pad : p.Cout;
+        const int nkc = (Cg_in + 15) / 16 * 2;
+        long long t = i;
+        const int j = (int)(t % 8); t /= 8;
+        int n, kc, tap, co;
+        bool live = true;
+        if (p.mode == 4) {
+            n = (int)(t % Cg_out); t /= Cg_out;
+            kc = (int)(t % nkc); t /= nkc;
+            tap = (int)t; co = n;
+        } else {
+            const int N2 = 2 * Cg_out;
+            n = (int)(t % N2); t /= N2;
+            kc = (int)(t % nkc); t /= nkc;
+            const int di = (int)(t % 3); t /= 3;          // t = a*kp + b
+            const int er = n / Cg_out;
+            co = n - er * Cg_out;
+            const int c = er + 1 - 2 * (di - 1);
+            live = c >= 0 && c < p.kr;
+            tap = (int)t * p.kr + c;
+        }
+        const int ci = kc * 8 + j;
+        float v = 0.f;
+        if (live && ci < Cg_in)
+            v = p.swap ? p.pk[((long long)tap * p.Cin_pad + co) * p.Cout + ci] : p.pk[((long long)tap * p.Cin_pad + ci) * p.Cout + co];
+        p.out_h[i] = __float2half_rn(v);
+        return;
+    }
     const bool dgrad = p.mode >= 2;
     const int Cin = dgrad ? p.Cout : p.Cin_pad, Cout = dgrad ? p.n_out : p.Cout;     // of the convolution being packed
     int tap, ci, co;
@@ -935,12 +1015,13 @@ void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st) {
 }
 
 int launch_wgrad_mma(const WgradParams& p, cudaStream_t st) {
-    if (p.Cout % 32 || p.Cin_pad % 32 || (p.taps != 27 && p.taps != 1)) return 1;
-    if (p.src_chunks0 % 4) return 1;          // a ci block must not straddle the two sources
+    if (p.Cout % 32 || p.Cin_pad % 16 || (p.taps != 27 && p.taps != 1)) return 1;
+    if (p.x1 && (p.src_chunks0 % 4 || p.Cin_pad % 32)) return 1;          // a ci block must not straddle the two sources
     const Geom& g = p.g;
     const int halo = p.taps == 27 ? g.plane + g.Rp + 1 : 0;
     if (halo > g.guard) return 1;
-    const size_t smem = ((size_t)4 * (kWgRows + 2 * halo) + 4 * kWgRows) * 16;
+    const size_t smem = ((size_t)4 * (2 * kWgRows + 2 * halo) + 2 * 4 * kWgRows) * 16;      // X ring + two dY buffers
+    if (smem > 227 * 1024) return 1;
     static size_t configured = 0;
     if (smem > configured) {
         if (cudaFuncSetAttribute(wgrad_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;
@@ -948,11 +1029,15 @@ int launch_wgrad_mma(const WgradParams& p, cudaStream_t st) {
     }
     WgradParams q = p;
     q.ncob = p.Cout / 32;
-    const int nblk = (p.Cin_pad / 32) * q.ncob;
+    const int nblk = ((p.Cin_pad + 31) / 32) * q.ncob;
     const long long nrows = (long long)p.B * g.rows_per_sample;
-    int gx = (int)((nrows + kWgRows - 1) / kWgRows);
-    const int cap = (148 * 2 + nblk - 1) / nblk;
-    if (gx > cap) gx = cap;
+    const int nchunks = (int)((nrows + kWgRows - 1) / kWgRows);
+    // one CTA per SM (the accumulators take the register file); contiguous chunk ranges, at least 4 chunks each so the window
+    // start-up (wrows rows) is amortised
+    int gx = 148 / nblk > 0 ? 148 / nblk : 1;
+    if (gx > (nchunks + 3) / 4) gx = (nchunks + 3) / 4;
+    if (gx < 1) gx = 1;
+    gx = (nchunks + ((nchunks + gx - 1) / gx) - 1) / ((nchunks + gx - 1) / gx);        // no empty CTAs
     wgrad_mma_kernel<<<dim3(gx, nblk), kWgWarps * 32, smem, st>>>(q);
     return 0;
 }
@@ -967,7 +1052,7 @@ void launch_conv_strided_backward(const ConvParams& p, const __half* x, const __
     if (dw) {
         const int taps = p.kz * p.kp * p.kr;
         const int nblk = ((p.Cin_total + 31) / 32) * (p.Cout / 32);
-        int split = (148 * 4) / (taps * nblk);
+        int split = (148 * 8) / (taps * nblk);
         if (split < 1) split = 1;
         conv_strided_wgrad_kernel<<<dim3(taps, nblk, split), 256, 0, st>>>(p, x, dy, dw, Cin_real, master_transposed);
     }

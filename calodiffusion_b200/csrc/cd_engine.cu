@@ -71,6 +71,7 @@ struct TapeOp {
     std::vector<int> srcs; int dst = -1;
     float* w = nullptr; __half* wmma = nullptr;              // forward layouts (refreshed from the master after every optimizer step)
     float* wd[2] = {nullptr, nullptr}; __half* wdm[2] = {nullptr, nullptr};   // data-gradient layouts, one per source
+    __half* wgat = nullptr; __half* wgat_d = nullptr;        // gather-tcgen05 layouts: forward, and the data gradient (opposite conv kind)
     bool need_dgrad = true, bias_via_gn = false;
     // GroupNorm
     std::string gname, betaname;
@@ -245,7 +246,7 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
-    if (want_gather && !h->train && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {   // training: the SIMT form (fp32 weights refreshed in place)
+    if (want_gather && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {   // (training re-derives it on the device: repack modes 4 / 5)
         const bool pairT = transposed && kr == 4;     // transposed convs use the merged output-pair taps
         std::vector<__half> hp(pairT ? gather_packed_elems_pairT(Cin_pad, Cout, kz, kp) : gather_packed_elems(Cin_pad, Cout, taps));
         if (pairT) gather_pack_weights_pairT(pk.data(), Cin_pad, Cout, kz, kp, kr, hp.data());
@@ -294,7 +295,7 @@ struct Builder {
             TapeOp t;
             t.kind = 0; t.wname = t_wname; t.bname = t_bname; t.Cin_real = t_cin_real ? t_cin_real : w.Cin; t.Cin_pad = w.Cin; t.Cout = w.Cout;
             t.kz = w.kz; t.kp = w.kp; t.kr = w.kr; t.stride = stride; t.transposed = w.transposed; t.level_in = level_in; t.level_out = level_out;
-            t.pz = pz; t.cp = cp; t.pr = pr; t.srcs = srcs; t.dst = dst; t.w = w.w; t.wmma = w.wmma;
+            t.pz = pz; t.cp = cp; t.pr = pr; t.srcs = srcs; t.dst = dst; t.w = w.w; t.wmma = w.wmma; t.wgat = w.wgat;
             hh->tape.push_back(t);
             t_wname.clear(); t_bname.clear(); t_cin_real = 0;
         }

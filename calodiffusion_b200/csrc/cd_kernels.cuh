@@ -175,6 +175,9 @@ struct EmbedBwdLayout { int stride, cvec, dt3, t2, dc3, c2, dt2, t1, dt1, t0, dc
 struct RepackParams {
     const float* master; float* out_f; __half* out_h;
     long long n; int mode, taps, Cin_real, Cin_pad, Cout, transposed, CB, ci_lo, n_out;
+    // modes 4 / 5 (gather-tcgen05 layouts): pk = the fp32 [tap][Cin_pad][Cout] array of mode 0; swap: pack the convolution with
+    // the channel roles exchanged (the data gradient of a strided / transposed conv is the opposite kind with the same taps)
+    const float* pk; int swap, kz, kp, kr;
 };
 
 void launch_loss_backward(const LossBwdParams& p, int B, cudaStream_t st);

@@ -40,6 +40,21 @@ static void train_refresh_weights(cd_unet* h, cudaStream_t st) {
             r.mode = 1; r.out_h = t.wmma; r.CB = mma_pick_cb(t.Cout, taps);
             launch_repack_conv(r, st);
         }
+        if (t.wgat || t.wgat_d) {
+            r.pk = t.w; r.kz = t.kz; r.kp = t.kp; r.kr = t.kr;
+            if (t.wgat) {       // forward: pack_conv's choice (merged pairs for the transposed conv with kr == 4)
+                const bool pairT = t.transposed && t.kr == 4;
+                r.mode = pairT ? 5 : 4; r.swap = 0; r.out_h = t.wgat;
+                r.n = (long long)(pairT ? gather_packed_elems_pairT(t.Cin_pad, t.Cout, t.kz, t.kp) : gather_packed_elems(t.Cin_pad, t.Cout, taps));
+                launch_repack_conv(r, st);
+            }
+            if (t.wgat_d) {     // data gradient: strided conv <-> transposed conv with the channel roles exchanged, same taps
+                const bool pairT = !t.transposed;
+                r.mode = pairT ? 5 : 4; r.swap = 1; r.out_h = t.wgat_d;
+                r.n = (long long)(pairT ? gather_packed_elems_pairT(t.Cout, t.Cin_pad, t.kz, t.kp) : gather_packed_elems(t.Cout, t.Cin_pad, taps));
+                launch_repack_conv(r, st);
+            }
+        }
         int lo = 0;
         for (size_t s = 0; s < t.srcs.size() && s < 2; ++s) {
             const int Cs = h->bufs[t.srcs[s]].C;
@@ -68,6 +83,16 @@ static int train_setup(cd_unet* h) {
         if (t.kind != 0) continue;
         if (!h->pptr(t.wname)) return fail("training: conv weight %s has no master copy", t.wname.c_str());
         const int taps = t.kz * t.kp * t.kr;
+        // strided <-> transposed conv as each other's adjoint holds on the circular axis only when the fine grid has exactly twice
+        // the coarse phi bins (an odd fine P gets its last bin from output_padding / the wrap, which are not adjoint to each other)
+        const int fineP = t.transposed ? h->geom[t.level_out].P : h->geom[t.level_in].P;
+        const int coarseP = t.transposed ? h->geom[t.level_in].P : h->geom[t.level_out].P;
+        if ((t.stride == 2 || t.transposed) && t.need_dgrad && t.srcs.size() == 1 && gather_conv_supported(t.Cout, t.Cin_pad) && taps <= 64 &&
+            fineP == 2 * coarseP && (t.transposed || (t.kr == 4 && t.pr == 1 && 2 * t.Cin_pad <= 256))) {
+            const size_t ne = t.transposed ? gather_packed_elems(t.Cout, t.Cin_pad, taps) : gather_packed_elems_pairT(t.Cout, t.Cin_pad, t.kz, t.kp);
+            t.wgat_d = h->dalloc<__half>(ne, true);
+            if (!t.wgat_d) return fail("out of device memory for the data-gradient weights");
+        }
         if (t.stride == 1 && !t.transposed && t.need_dgrad) {
             for (size_t s = 0; s < t.srcs.size() && s < 2; ++s) {
                 const int Cs = h->bufs[t.srcs[s]].C;
@@ -254,10 +279,24 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
                         mark(t.wdm[s] && h->conv_backend == 0 ? "dgrad_mma" : "dgrad_simt", &t, t.level_in, t.Cout, Cs, cflops * Cs / t.Cin_pad);
                     }
                 } else {
-                    launch_conv_strided_backward(p, nullptr, h->bufs[t.dst].grad, h->bufs[t.srcs[0]].grad, ginit[t.srcs[0]], nullptr, t.Cin_real,
-                                                 t.transposed, st);
+                    bool ddone = false;
+                    if (t.wgat_d && h->conv_backend == 0) {
+                        // the adjoint of a strided conv is the transposed conv with the same taps (and vice versa): the gather
+                        // tcgen05 kernel on dY, whose halo rows are re-derived first (its producer may have left them stale)
+                        launch_plcp_accumulate(go, h->bufs[t.dst].grad, h->bufs[t.dst].grad, t.Cout, 0, B, st);
+                        ConvParams q = p;
+                        q.gin = go; q.gout = gi; q.nsrc = 1; q.Cin_total = t.Cout;
+                        q.src[0].base = h->bufs[t.dst].grad; q.src[0].C = t.Cout; q.src[1].base = nullptr; q.src[1].C = 0;
+                        q.Cout = t.Cin_pad; q.w = nullptr; q.bias = nullptr; q.transposed = !t.transposed; q.write_halo = 1;
+                        q.dst = ginit[t.srcs[0]] ? tmp[t.level_in] : h->bufs[t.srcs[0]].grad;
+                        ddone = launch_conv_gather(q, t.wgat_d, st) == 0;
+                        if (ddone && ginit[t.srcs[0]]) launch_plcp_accumulate(gi, tmp[t.level_in], h->bufs[t.srcs[0]].grad, t.Cin_pad, 1, B, st);
+                    }
+                    if (!ddone)
+                        launch_conv_strided_backward(p, nullptr, h->bufs[t.dst].grad, h->bufs[t.srcs[0]].grad, ginit[t.srcs[0]], nullptr, t.Cin_real,
+                                                     t.transposed, st);
                     ginit[t.srcs[0]] = 1;
-                    mark("dgrad_simt", &t, t.level_in, t.Cout, t.Cin_pad, cflops);
+                    mark(ddone ? "dgrad_gather" : "dgrad_simt", &t, t.level_in, t.Cout, t.Cin_pad, cflops);
                 }
             }
         }
