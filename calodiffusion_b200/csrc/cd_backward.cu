@@ -110,6 +110,18 @@ __device__ __forceinline__ void gn_group_stats(const double* stats, int b, int C
     rstd = rsqrtf(var + 1e-5f);
 }
 
+// one block per sample: mean / rstd of every channel's group from the forward pass's fp64 sums (once, instead of in every
+// block of the two streaming passes), and the accumulators cleared
+__global__ void __launch_bounds__(128) gn_bwd_prep_kernel(GnBwdParams p) {
+    const int b = blockIdx.x;
+    for (int c = threadIdx.x; c < p.C; c += blockDim.x) {
+        float mean, rstd;
+        gn_group_stats(p.stats, b, p.C, p.groups, c, p.count_per_channel, mean, rstd);
+        *reinterpret_cast<float2*>(p.mr + ((long long)b * p.C + c) * 2) = make_float2(mean, rstd);
+        *reinterpret_cast<float4*>(p.acc + ((long long)b * p.C + c) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
 // grid (row chunks, B); thread layout: chunk-major so that a warp reads 512 contiguous bytes of one chunk plane
 __global__ void __launch_bounds__(kGbThreads) gn_bwd_reduce_kernel(GnBwdParams p) {
     __shared__ float s_mean[kBwdMaxC], s_rstd[kBwdMaxC], s_gamma[kBwdMaxC], s_beta[kBwdMaxC];
@@ -117,7 +129,8 @@ __global__ void __launch_bounds__(kGbThreads) gn_bwd_reduce_kernel(GnBwdParams p
     const int b = blockIdx.y, C = p.C, nch = C >> 3;
     const Geom& g = p.g;
     for (int c = threadIdx.x; c < C; c += kGbThreads) {
-        gn_group_stats(p.stats, b, C, p.groups, c, p.count_per_channel, s_mean[c], s_rstd[c]);
+        const float2 mr = *reinterpret_cast<const float2*>(p.mr + ((long long)b * C + c) * 2);
+        s_mean[c] = mr.x; s_rstd[c] = mr.y;
         s_gamma[c] = p.gamma[c]; s_beta[c] = p.beta[c];
         s_acc[c][0] = s_acc[c][1] = s_acc[c][2] = s_acc[c][3] = 0.f;
     }
@@ -150,10 +163,20 @@ __global__ void __launch_bounds__(kGbThreads) gn_bwd_reduce_kernel(GnBwdParams p
                 A[j] = fmaf(dz, xh, A[j]); Bc[j] += dz; D[j] += dy[j]; X[j] += xh;
             }
         }
+    }
+    // lanes of one chunk plane are contiguous (tpc is 8, 16, 32, 64 ...): butterfly over min(32, tpc) lanes, then one lane per
+    // group adds to the block's accumulators (all lanes take part in the shuffles, also those with k >= nch)
+    const int span = tpc < 32 ? tpc : 32;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            atomicAdd(&s_acc[k * 8 + j][0], A[j]); atomicAdd(&s_acc[k * 8 + j][1], Bc[j]);
-            atomicAdd(&s_acc[k * 8 + j][2], D[j]); atomicAdd(&s_acc[k * 8 + j][3], X[j]);
+    for (int j = 0; j < 8; ++j) {
+        float a = A[j], bsum = Bc[j], d = D[j], x = X[j];
+        for (int o = span >> 1; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o); bsum += __shfl_xor_sync(0xffffffffu, bsum, o);
+            d += __shfl_xor_sync(0xffffffffu, d, o); x += __shfl_xor_sync(0xffffffffu, x, o);
+        }
+        if (k < nch && (threadIdx.x & (span - 1)) == 0) {
+            atomicAdd(&s_acc[k * 8 + j][0], a); atomicAdd(&s_acc[k * 8 + j][1], bsum);
+            atomicAdd(&s_acc[k * 8 + j][2], d); atomicAdd(&s_acc[k * 8 + j][3], x);
         }
     }
     __syncthreads();
@@ -185,8 +208,7 @@ __global__ void __launch_bounds__(256) gn_bwd_finalize_kernel(GnBwdParams p) {
         atomicAdd(p.dbeta + c, acc[1]);
         if (p.daddvec) p.daddvec[(long long)b * p.addvec_stride + c] += acc[2];     // one block per sample: no race
         if (p.dbias) {
-            float mean, rstd;
-            gn_group_stats(p.stats, b, C, p.groups, c, p.count_per_channel, mean, rstd);
+            const float rstd = p.mr[((long long)b * C + c) * 2 + 1];
             const int gi = c / cpg;
             atomicAdd(p.dbias + c, rstd * (p.gamma[c] * acc[1] - V * s_m1[gi] - s_m2[gi] * acc[3]));
         }
@@ -199,7 +221,8 @@ __global__ void __launch_bounds__(kGbThreads) gn_bwd_apply_kernel(GnBwdParams p)
     const int b = blockIdx.y, C = p.C, nch = C >> 3, cpg = C / p.groups;
     const Geom& g = p.g;
     for (int c = threadIdx.x; c < C; c += kGbThreads) {
-        gn_group_stats(p.stats, b, C, p.groups, c, p.count_per_channel, s_mean[c], s_rstd[c]);
+        const float2 mr = *reinterpret_cast<const float2*>(p.mr + ((long long)b * C + c) * 2);
+        s_mean[c] = mr.x; s_rstd[c] = mr.y;
         s_gamma[c] = p.gamma[c]; s_beta[c] = p.beta[c];
         s_m1[c] = p.m12[((long long)b * p.groups + c / cpg) * 2];
         s_m2[c] = p.m12[((long long)b * p.groups + c / cpg) * 2 + 1];
@@ -616,31 +639,36 @@ __device__ __forceinline__ float ord2f_b(unsigned k) {
     return __uint_as_float(u);
 }
 
-// reduce pass: batches of 128 voxels; phase 1 (thread = voxel) leaves P, datt, att and dy in shared memory, phase 2 (thread = a
-// few matrix entries) contracts the batch into register accumulators; one set of global atomics per block at the end.
+// reduce pass: batches of 128 voxels; phase 1 (thread = voxel) leaves P, datt, att and dy in shared memory as fp16 chunk planes
+// ([8-channel chunk][voxel][8], the layout wgrad_mma_kernel stages), phase 2 contracts the batch on the tensor cores
+// (mma.sync m16n8k16, K = the 128 voxels): warps 0-1 dCx = P^T datt (16 d-rows each), warps 2-3 dWout = dy^T att (16-row
+// c tiles), accumulators in registers across the block's batches; one set of global atomics per block at the end.
 __global__ void __launch_bounds__(128) attn_bwd_reduce_kernel(AttnBwdParams p) {
     extern __shared__ __align__(16) float asm_[];
-    const int b = blockIdx.y, C = p.C;
+    const int b = blockIdx.y, C = p.C, ncc = C >> 3;
     const Geom& g = p.g;
-    float (*s_cx)[33] = reinterpret_cast<float (*)[33]>(asm_);                 // [32][33]
-    float (*s_P)[33] = s_cx + 32;                                               // [128][33]
-    float (*s_datt)[33] = s_P + 128;
-    float (*s_att)[33] = s_datt + 128;
-    float* s_wout = reinterpret_cast<float*>(s_att + 128);                      // [C][33]
-    float* s_dy = s_wout + C * 33;                                              // [128][C+1]
+    float (*s_cx)[32] = reinterpret_cast<float (*)[32]>(asm_);                 // [32][32] broadcast reads: unpadded, float4
+    float* s_wout = asm_ + 32 * 32;                                             // [C][32]
+    __half* h_P = reinterpret_cast<__half*>(s_wout + C * 32);                   // [4][128][8]
+    __half* h_datt = h_P + 4 * 128 * 8;
+    __half* h_att = h_datt + 4 * 128 * 8;
+    __half* h_dy = h_att + 4 * 128 * 8;                                         // [C/8][128][8]
     const float* ctx = p.ctx + (long long)b * 33 * 32;
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_cx[i >> 5][i & 31] = ctx[i] / ctx[32 * 32 + (i >> 5)];
-    for (int i = threadIdx.x; i < C * 32; i += blockDim.x) s_wout[(i >> 5) * 33 + (i & 31)] = p.wout[i];
+    for (int i = threadIdx.x; i < C * 32; i += blockDim.x) s_wout[i] = p.wout[i];
     __syncthreads();
     const float scale = 0.17677669529663687f;   // 32^-0.5
-    const int t = threadIdx.x;
-    const int dd = t >> 2, e0 = (t & 3) * 8;     // dCx entries [dd][e0..e0+8)
-    const int ee = t & 31, cq = t >> 5;          // dWout entries [cq + 4i][ee]
-    float a_dcx[8], a_dw[kBwdMaxC / 4], a_db = 0.f;
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int mi = lane >> 3, mr = lane & 7;
+    float acc[4][4][4];                          // [row tile][e 8-tile][frag]: warps 0-1 use tile 0 (dCx), warps 2-3 up to 4 c tiles
 #pragma unroll
-    for (int i = 0; i < 8; ++i) a_dcx[i] = 0.f;
+    for (int a = 0; a < 4; ++a)
 #pragma unroll
-    for (int i = 0; i < kBwdMaxC / 4; ++i) a_dw[i] = 0.f;
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[a][j][e] = 0.f;
+    float a_db = 0.f;
+    const int nct = C >> 4;                      // 16-row c tiles of dWout
     const uint32_t r0 = blockIdx.x * p.rows_per_block;
     uint32_t r1 = r0 + p.rows_per_block;
     if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
@@ -650,61 +678,117 @@ __global__ void __launch_bounds__(128) attn_bwd_reduce_kernel(AttnBwdParams p) {
         const long long row = (long long)b * g.rows_per_sample + rem;
         __syncthreads();
         if (interior) {
-            float q[32], P[32], datt[32];
+            float q[32], datt[32];
             for (int k = 0; k < 4; ++k) unpack8(load8(p.qkv + plcp_offset(g, k, row)), q + k * 8);
             float mx = q[0];
 #pragma unroll
             for (int d = 1; d < 32; ++d) mx = fmaxf(mx, q[d]);
             float sum = 0.f;
 #pragma unroll
-            for (int d = 0; d < 32; ++d) { P[d] = __expf(q[d] - mx); sum += P[d]; }
+            for (int d = 0; d < 32; ++d) { q[d] = __expf(q[d] - mx); sum += q[d]; }
             const float inv = 1.f / sum;
 #pragma unroll
+            for (int d = 0; d < 32; ++d) q[d] *= inv;                       // q holds P from here on
+#pragma unroll
             for (int e = 0; e < 32; ++e) datt[e] = 0.f;
-            for (int k = 0; k < (C >> 3); ++k) {
+            for (int k = 0; k < ncc; ++k) {
+                const Half8 raw = load8(p.dy + plcp_offset(g, k, row));
+                store8(h_dy + ((size_t)k * 128 + t) * 8, raw);
                 float dy[8];
-                unpack8(load8(p.dy + plcp_offset(g, k, row)), dy);
+                unpack8(raw, dy);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    s_dy[t * (C + 1) + k * 8 + j] = dy[j];
+                for (int j = 0; j < 8; ++j)
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) datt[e] = fmaf(s_wout[(k * 8 + j) * 33 + e], dy[j], datt[e]);
+                    for (int e4 = 0; e4 < 8; ++e4) {
+                        const float4 w = *reinterpret_cast<const float4*>(s_wout + (k * 8 + j) * 32 + e4 * 4);
+                        datt[e4 * 4] = fmaf(w.x, dy[j], datt[e4 * 4]); datt[e4 * 4 + 1] = fmaf(w.y, dy[j], datt[e4 * 4 + 1]);
+                        datt[e4 * 4 + 2] = fmaf(w.z, dy[j], datt[e4 * 4 + 2]); datt[e4 * 4 + 3] = fmaf(w.w, dy[j], datt[e4 * 4 + 3]);
+                    }
+            }
+#pragma unroll
+            for (int e = 0; e < 32; ++e) datt[e] *= scale;
+            for (int k = 0; k < 4; ++k) {
+                store8(h_P + ((size_t)k * 128 + t) * 8, pack8(q + k * 8));
+                store8(h_datt + ((size_t)k * 128 + t) * 8, pack8(datt + k * 8));
+            }
+#pragma unroll
+            for (int e = 0; e < 32; ++e) datt[e] = 0.f;                      // reuse as the att accumulator
+#pragma unroll
+            for (int d = 0; d < 32; ++d)
+#pragma unroll
+                for (int e4 = 0; e4 < 8; ++e4) {
+                    const float4 w = *reinterpret_cast<const float4*>(&s_cx[d][e4 * 4]);
+                    datt[e4 * 4] = fmaf(w.x, q[d], datt[e4 * 4]); datt[e4 * 4 + 1] = fmaf(w.y, q[d], datt[e4 * 4 + 1]);
+                    datt[e4 * 4 + 2] = fmaf(w.z, q[d], datt[e4 * 4 + 2]); datt[e4 * 4 + 3] = fmaf(w.w, q[d], datt[e4 * 4 + 3]);
                 }
-            }
 #pragma unroll
-            for (int d = 0; d < 32; ++d) { P[d] *= inv; s_P[t][d] = P[d]; }
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-                float a = 0.f;
-#pragma unroll
-                for (int d = 0; d < 32; ++d) a = fmaf(s_cx[d][e], P[d], a);
-                s_att[t][e] = a * scale;
-                s_datt[t][e] = datt[e] * scale;
-            }
+            for (int e = 0; e < 32; ++e) datt[e] *= scale;
+            for (int k = 0; k < 4; ++k) store8(h_att + ((size_t)k * 128 + t) * 8, pack8(datt + k * 8));
         } else {
-            for (int d = 0; d < 32; ++d) { s_P[t][d] = 0.f; s_att[t][d] = 0.f; s_datt[t][d] = 0.f; }
-            for (int c = 0; c < C; ++c) s_dy[t * (C + 1) + c] = 0.f;
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            for (int k = 0; k < 4; ++k) {
+                *reinterpret_cast<uint4*>(h_P + ((size_t)k * 128 + t) * 8) = z;
+                *reinterpret_cast<uint4*>(h_datt + ((size_t)k * 128 + t) * 8) = z;
+                *reinterpret_cast<uint4*>(h_att + ((size_t)k * 128 + t) * 8) = z;
+            }
+            for (int k = 0; k < ncc; ++k) *reinterpret_cast<uint4*>(h_dy + ((size_t)k * 128 + t) * 8) = z;
         }
         __syncthreads();
-        for (int n = 0; n < 128; ++n) {
-            const float pv = s_P[n][dd];
+        // phase 2: A = (P | dy)^T through ldmatrix.trans on the chunk planes, B = (datt | att) likewise (as wgrad_mma_kernel)
+        const __half* Am = warp < 2 ? h_P : h_dy;
+        const __half* Bm = warp < 2 ? h_datt : h_att;
+        const int ntile = warp < 2 ? 1 : (nct - (warp - 2) + 1) / 2;
+#pragma unroll 2
+        for (int k16 = 0; k16 < 8; ++k16) {
+            uint32_t bf[4][2];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a_dcx[i] = fmaf(pv, s_datt[n][e0 + i], a_dcx[i]);
-            const float av = s_att[n][ee];
-            for (int i = 0; i < (C >> 2); ++i) a_dw[i] = fmaf(s_dy[n * (C + 1) + cq + 4 * i], av, a_dw[i]);
-            if (t < C) a_db += s_dy[n * (C + 1) + t];
+            for (int jj = 0; jj < 2; ++jj) {
+                uint32_t r[4];
+                const int chunk = 2 * jj + (mi >> 1), krow = k16 * 16 + (mi & 1) * 8 + mr;
+                ldsm_x4_t(smem_u32(Bm + ((size_t)chunk * 128 + krow) * 8), r);
+                bf[2 * jj][0] = r[0]; bf[2 * jj][1] = r[1]; bf[2 * jj + 1][0] = r[2]; bf[2 * jj + 1][1] = r[3];
+            }
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                if (a >= ntile) break;
+                const int tile = warp < 2 ? warp : (warp - 2) + 2 * a;       // 16-row tile of d (dCx) or c (dWout)
+                uint32_t af[4];
+                const int chunk = 2 * tile + (mi & 1), krow = k16 * 16 + (mi >> 1) * 8 + mr;
+                ldsm_x4_t(smem_u32(Am + ((size_t)chunk * 128 + krow) * 8), af);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma16816(acc[a][j], af, bf[j][0], bf[j][1]);
+            }
+        }
+        if (t < C) {
+            const __half* col = h_dy + ((size_t)(t >> 3) * 128) * 8 + (t & 7);
+            float sdb = 0.f;
+            for (int n = 0; n < 128; ++n) sdb += __half2float(col[n * 8]);
+            a_db += sdb;
         }
     }
+    const int gq = lane >> 2, tq = lane & 3;
+    const int ntile = warp < 2 ? 1 : (nct - (warp - 2) + 1) / 2;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) atomicAdd(p.dcx + (long long)b * 1024 + dd * 32 + e0 + i, a_dcx[i]);
-    for (int i = 0; i < (C >> 2); ++i) atomicAdd(p.dwout + (cq + 4 * i) * 32 + ee, a_dw[i]);
+    for (int a = 0; a < 4; ++a) {
+        if (a >= ntile) break;
+        const int tile = warp < 2 ? warp : (warp - 2) + 2 * a;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int r = tile * 16 + gq + (e >> 1) * 8, c = j * 8 + tq * 2 + (e & 1);
+                if (warp < 2) atomicAdd(p.dcx + (long long)b * 1024 + r * 32 + c, acc[a][j][e]);
+                else atomicAdd(p.dwout + r * 32 + c, acc[a][j][e]);
+            }
+    }
     if (t < C) atomicAdd(p.dbout + t, a_db);
 }
 
 __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
-    __shared__ float s_cx[32][33];      // Cx[d][e]
-    __shared__ float s_dcx[32][33];     // dCx[d][e]
-    __shared__ float s_wout[kBwdMaxC][33];
+    // matrices every thread reads at the SAME address (broadcast): unpadded and 16-byte aligned so the e-loops read float4
+    __shared__ __align__(16) float s_cx[32][32];      // Cx[d][e]
+    __shared__ __align__(16) float s_dcx[32][32];     // dCx[d][e]
+    __shared__ __align__(16) float s_wout[kBwdMaxC][32];
     __shared__ float s_km[32], s_sinv[32], s_T[32];
     const int b = blockIdx.y, C = p.C;
     const Geom& g = p.g;
@@ -758,7 +842,11 @@ __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
 #pragma unroll
             for (int j = 0; j < 8; ++j)
 #pragma unroll
-                for (int e = 0; e < 32; ++e) datt[e] = fmaf(s_wout[k * 8 + j][e], dy[j], datt[e]);
+                for (int e4 = 0; e4 < 8; ++e4) {
+                    const float4 w = *reinterpret_cast<const float4*>(&s_wout[k * 8 + j][e4 * 4]);
+                    datt[e4 * 4] = fmaf(w.x, dy[j], datt[e4 * 4]); datt[e4 * 4 + 1] = fmaf(w.y, dy[j], datt[e4 * 4 + 1]);
+                    datt[e4 * 4 + 2] = fmaf(w.z, dy[j], datt[e4 * 4 + 2]); datt[e4 * 4 + 3] = fmaf(w.w, dy[j], datt[e4 * 4 + 3]);
+                }
         }
         float kv[32], vv[32];
         for (int k = 0; k < 4; ++k) unpack8(load8(p.qkv + plcp_offset(g, 4 + k, row)), kv + k * 8);
@@ -769,7 +857,10 @@ __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
         for (int d = 0; d < 32; ++d) {
             float t = 0.f;
 #pragma unroll
-            for (int e = 0; e < 32; ++e) t = fmaf(s_cx[d][e], datt[e], t);
+            for (int e4 = 0; e4 < 8; ++e4) {
+                const float4 w = *reinterpret_cast<const float4*>(&s_cx[d][e4 * 4]);
+                t = fmaf(w.x, datt[e4 * 4], t); t = fmaf(w.y, datt[e4 * 4 + 1], t); t = fmaf(w.z, datt[e4 * 4 + 2], t); t = fmaf(w.w, datt[e4 * 4 + 3], t);
+            }
             dP[d] = scale * t;
             dot = fmaf(P[d], dP[d], dot);
         }
@@ -785,25 +876,28 @@ __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
                 const int d = k * 8 + j;
                 float t = 0.f;
 #pragma unroll
-                for (int e = 0; e < 32; ++e) t = fmaf(s_dcx[d][e], vv[e], t);
+                for (int e4 = 0; e4 < 8; ++e4) {
+                    const float4 w = *reinterpret_cast<const float4*>(&s_dcx[d][e4 * 4]);
+                    t = fmaf(w.x, vv[e4 * 4], t); t = fmaf(w.y, vv[e4 * 4 + 1], t); t = fmaf(w.z, vv[e4 * 4 + 2], t); t = fmaf(w.w, vv[e4 * 4 + 3], t);
+                }
                 const float K = __expf(kv[d] - s_km[d]) * s_sinv[d];
                 out[j] = K * (t - s_T[d]);
                 kv[d] = K;                          // keep K for dv
             }
             store8(p.dqkv + plcp_offset(g, 4 + k, row), pack8(out));
         }
-        // dv[e] = sum_d K[d] dCx[d][e]
-        for (int k = 0; k < 4; ++k) {
+        // dv[e] = sum_d K[d] dCx[d][e]   (vv is dead: reuse it as the accumulator; d outer so the e-loop reads float4)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int e = k * 8 + j;
-                float t = 0.f;
+        for (int e = 0; e < 32; ++e) vv[e] = 0.f;
 #pragma unroll
-                for (int d = 0; d < 32; ++d) t = fmaf(kv[d], s_dcx[d][e], t);
-                out[j] = t;
+        for (int d = 0; d < 32; ++d)
+#pragma unroll
+            for (int e4 = 0; e4 < 8; ++e4) {
+                const float4 w = *reinterpret_cast<const float4*>(&s_dcx[d][e4 * 4]);
+                vv[e4 * 4] = fmaf(kv[d], w.x, vv[e4 * 4]); vv[e4 * 4 + 1] = fmaf(kv[d], w.y, vv[e4 * 4 + 1]);
+                vv[e4 * 4 + 2] = fmaf(kv[d], w.z, vv[e4 * 4 + 2]); vv[e4 * 4 + 3] = fmaf(kv[d], w.w, vv[e4 * 4 + 3]);
             }
-            store8(p.dqkv + plcp_offset(g, 8 + k, row), pack8(out));
-        }
+        for (int k = 0; k < 4; ++k) store8(p.dqkv + plcp_offset(g, 8 + k, row), pack8(vv + k * 8));
     }
 }
 
@@ -1005,7 +1099,7 @@ void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st) {
     const Geom& g = p.g;
     const int nch = p.C >> 3;
     if (kGbThreads % nch != 0 || p.C > kBwdMaxC) return;     // checked by the caller (C in {16,32,64,96,128})
-    fill_zero_kernel<<<(unsigned)(((long long)B * p.C * 4 + 255) / 256), 256, 0, st>>>(p.acc, (long long)B * p.C * 4);
+    gn_bwd_prep_kernel<<<B, 128, 0, st>>>(p);
     p.rows_per_block = 2048;
     dim3 grid1((g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);
     gn_bwd_reduce_kernel<<<grid1, kGbThreads, 0, st>>>(p);
@@ -1073,7 +1167,8 @@ int launch_attn_backward(AttnBwdParams p, int B, cudaStream_t st) {
     fill_zero_kernel<<<(unsigned)(((long long)B * 1024 + 255) / 256), 256, 0, st>>>(p.dcx, (long long)B * 1024);
     p.rows_per_block = 2048;
     dim3 grid((p.g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);
-    const size_t smem = ((size_t)(32 + 3 * 128) * 33 + (size_t)p.C * 33 + (size_t)128 * (p.C + 1)) * sizeof(float);
+    if (p.C % 16) return 1;
+    const size_t smem = ((size_t)32 * 32 + (size_t)p.C * 32) * sizeof(float) + ((size_t)3 * 4 + p.C / 8) * 128 * 8 * sizeof(__half);
     static size_t configured = 0;
     if (smem > configured) {
         if (cudaFuncSetAttribute(attn_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;

@@ -144,6 +144,7 @@ struct GnBwdParams {
     int C, groups, act; double count_per_channel;
     float* acc;                             // scratch [B][C][4]
     float* m12;                             // scratch [B][groups][2]
+    float* mr;                              // scratch [B][C][2]: mean, rstd of the channel's group
     float* dgamma; float* dbeta; float* dbias;      // parameter gradients (dbias: bias of the convolution that produced x, or null)
     float* daddvec; int addvec_stride;      // gradient of the additive conditioning (already offset to this block), or null
     __half* dx; int dx_accumulate;

@@ -104,7 +104,7 @@ static int train_setup(cd_unet* h) {
     }
     const int V = h->voxels();
     h->gn_acc = h->dalloc<float>((size_t)maxB * kBwdMaxC * 4, true);
-    h->gn_m12 = h->dalloc<float>((size_t)maxB * kBwdMaxC * 2, true);
+    h->gn_m12 = h->dalloc<float>((size_t)maxB * kBwdMaxC * 4, true);     // m1/m2 per group, then mean/rstd per channel
     h->attn_dcx = h->dalloc<float>((size_t)maxB * 1024, true);
     h->daddvec = h->dalloc<float>((size_t)maxB * (h->addvec_stride > 0 ? h->addvec_stride : 1), true);
     h->x_noisy = h->dalloc<float>((size_t)maxB * V, true);
@@ -206,7 +206,7 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
             p.g = g; p.x = h->bufs[t.src].ptr; p.dy = h->bufs[t.dst].grad;
             p.stats = (const double*)(h->scratch + t.stats_off * B); p.gamma = h->pptr(t.gname); p.beta = h->pptr(t.betaname);
             p.C = t.C; p.groups = t.groups; p.act = t.act; p.count_per_channel = (double)g.Z * g.P * g.R;
-            p.acc = h->gn_acc; p.m12 = h->gn_m12; p.dgamma = h->gptr(t.gname); p.dbeta = h->gptr(t.betaname);
+            p.acc = h->gn_acc; p.m12 = h->gn_m12; p.mr = h->gn_m12 + (size_t)h->d.max_batch * kBwdMaxC * 2; p.dgamma = h->gptr(t.gname); p.dbeta = h->gptr(t.betaname);
             if (t.conv_of_src >= 0 && !h->tape[t.conv_of_src].bname.empty()) p.dbias = h->gptr(h->tape[t.conv_of_src].bname);
             if (t.addvec_off >= 0) { p.daddvec = h->daddvec + t.addvec_off; p.addvec_stride = h->addvec_stride; }
             p.dx = h->bufs[t.src].grad; p.dx_accumulate = ginit[t.src];
