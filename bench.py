@@ -131,7 +131,7 @@ REF_CONFIGS = {"ds2": ("config_dataset2.json", None), "ds3": ("config_dataset3.j
                "ds1": ("config_dataset1_photon.json", {"BIN_FILE": "{REF_ROOT}/CaloChallenge/code/binning_dataset_1_photons.xml"})}
 
 
-def config_block(wl, B, steps, world):
+def config_block(wl, B, steps, world, strong=False):
     """The `config` object of the JSON line: identical on both arms (the driver compares them)."""
     if wl.get("train"):
         return {"workload": wl["name"], "batch_per_gpu": B, "optimizer": f"Adam lr {TRAIN_LR}",
@@ -139,6 +139,11 @@ def config_block(wl, B, steps, world):
                 "l2": "activations saved for the backward pass (GBs) exceed the 126 MB L2; no explicit flush",
                 "weights": "random init (seed 0)"}
     evals = wl["evals_per_shower"] * steps / wl["steps"]
+    if strong:      # B = the whole job's showers, split over the GPUs
+        return {"workload": wl["name"], "batch_total": B, "sampler": wl["sampler"], "sampling_steps": steps,
+                "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards of ONE batch, final all_gather)",
+                "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
+                "weights": "random init (seed 0)"}
     return {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
             "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
             "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
@@ -425,7 +430,12 @@ def run_gpu_arm(args, wl):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
+    from calodiffusion_b200 import distributed as D
     cfg, B, steps = dict(wl["cfg"]), int(args.batch or wl["batch"]), int(args.sampling_steps or wl["steps"])
+    strong = args.scaling == "strong"
+    n_total = B if strong else B * world                   # showers of the whole job per step
+    lo, hi = D.shard_range(n_total, rank, world)
+    B = hi - lo                                            # this rank's slice
     if wl.get("binning"):
         _binning(wl, cfg)
     torch.manual_seed(0)                                   # identical random-init weights on every rank
@@ -433,17 +443,17 @@ def run_gpu_arm(args, wl):
     if os.environ.get("CD_NO_GRAPH"):
         model.use_graph = False                            # diagnostics: eager launches instead of one CUDA graph
     sampler = model.sampler_algorithm
-    sampler.shower_offset = rank * B                       # global shower index keys the Philox stream
+    sampler.shower_offset = lo                             # global shower index keys the Philox stream
     if wl["sampler"] == "Heun":
         sampler.last_step_euler = True                     # finite showers; 2 evals on all other steps
     vox = int(np.prod(_data_shape(cfg)))
-    g = torch.Generator().manual_seed(1 + rank)
-    E_host = torch.rand(B, wl.get("cond_e", 1), generator=g).pin_memory()
-    L_host = torch.randn(B, wl["n_layers"], generator=g).pin_memory() if wl["n_layers"] else None
+    g = torch.Generator().manual_seed(1)                   # the job's full conditioning, identical on every rank
+    E_all = torch.rand(n_total, wl.get("cond_e", 1), generator=g).pin_memory()
+    L_all = torch.randn(n_total, wl["n_layers"], generator=g).pin_memory() if wl["n_layers"] else None
+    E_host, L_host = E_all[lo:hi], (L_all[lo:hi] if L_all is not None else None)
     E_dev = E_host.to(dev)
     L_dev = L_host.to(dev) if L_host is not None else None
     start_dev = torch.randn([B] + _data_shape(cfg), device=dev, generator=torch.Generator(device=dev).manual_seed(2 + rank))
-    gathered = torch.empty(world * B, vox, device=dev) if world > 1 else None
 
     def barrier():
         if world > 1:
@@ -453,12 +463,20 @@ def run_gpu_arm(args, wl):
     def device_step():
         x, _, _ = sampler(model, start_dev, E_dev, L_dev, steps, 0, False)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, x.reshape(B, vox))   # the one collective of the path
+            D.gather_showers(x.reshape(B, vox), n_total)        # the one collective of the path
         return x
 
+    seeds = iter(range(1000, 100000))
+
     def api_step():
-        out = model.sample(E_host, L_host, num_steps=steps)     # numpy on host (models/diffusion.py:77-104)
-        return out
+        if world == 1:
+            return model.sample(E_host, L_host, num_steps=steps)    # numpy on host (models/diffusion.py:77-104)
+        # several GPUs: the public entry is distributed.sample_sharded - full conditioning from pinned host memory on every
+        # rank, each samples its slice, one all-gather; rank 0 reads the whole job's showers back to the host
+        e = E_all.to(dev, non_blocking=True)
+        l = L_all.to(dev, non_blocking=True) if L_all is not None else None
+        out = D.sample_sharded(model, e, l, num_steps=steps, seed=next(seeds))
+        return out.cpu().numpy() if rank == 0 else out[lo:hi].cpu().numpy()
 
     for _ in range(args.warmup):
         x = device_step()
@@ -487,17 +505,17 @@ def run_gpu_arm(args, wl):
         out = api_step()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    assert out.shape[0] == B and np.isfinite(out).all()
+    assert out.shape[0] == (B if world == 1 or rank else n_total) and np.isfinite(out).all()
 
     t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(t[0]), float(t[1])
-    total_showers = world * B * args.steps
+    total_showers = n_total * args.steps
     value = total_showers / (ms * 1e-3)
     e2e = total_showers / (e2e_ms * 1e-3)
-    h2d = 4 * B * (wl.get("cond_e", 1) + wl["n_layers"])
-    d2h = 4 * B * vox
+    h2d = 4 * (B if world == 1 else n_total) * (wl.get("cond_e", 1) + wl["n_layers"])    # per rank
+    d2h = 4 * (B if world == 1 else n_total) * vox                                          # rank 0
 
     if rank == 0:
         peaks = _peaks()
@@ -520,9 +538,9 @@ def run_gpu_arm(args, wl):
         evals = wl["evals_per_shower"] * steps / wl["steps"]
         line = {
             "metric": "showers/sec sampled", "value": value, "unit": "showers/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": config_block(wl, B, steps, world),
+            "config": config_block(wl, n_total if strong else B, steps, world, strong),
             "e2e": {"value": e2e, "unit": "showers/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -686,6 +704,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override showers per GPU (diagnostics only)")
     ap.add_argument("--sampling-steps", type=int, default=0, help="override sampler steps (diagnostics only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the workload's batch on EVERY GPU; strong: the workload's batch in total, split over the GPUs")
     args = ap.parse_args()
     if args.impl == "reference":
         os.environ["CUDA_VISIBLE_DEVICES"] = ""      # the reference picks cuda when it sees one (utils.get_device)

@@ -12,6 +12,7 @@
 // PreNorm's GroupNorm(1,C) is folded as in the conv:  W(gamma*(x-mean)*rstd+beta) = rstd*(W')x + (W beta - mean*rstd*rowsum(W')),
 // W' = W diag(gamma) in fp16.  The x fragments are loaded straight from global memory: in the PLCP layout one 8-row x
 // 8-channel fragment is 128 contiguous bytes, so every warp-level load is one fully used 128-byte line.
+#include <cstdlib>
 #include "cd_kernels.cuh"
 
 namespace cd {
@@ -669,8 +670,19 @@ template <int KS>
 void launch_fused_t(const Geom& g, const __half* x, const __half* wf, const float* wsum, const float* wb, const double* pn_stats,
                     float inv_count, unsigned* kmax, float* ctx, float* part, __half* fold, const float* wout, const float* bout,
                     __half* dst, double* stats, int B, cudaStream_t st) {
-    int rows = 2048;
-    while (rows > 512 && (long long)B * ((g.rows_per_sample + rows - 1) / rows) < 592) rows >>= 1;
+    // rows per block: as many as leaves >= ~4 waves of blocks (2 x 148 resident): the per-block set-up (weights, per-sample
+    // scalars, partial write-out) is amortised over the block's rows.  CD_ATTN_ROWS / CD_ATTN_OROWS override (diagnostics).
+    auto pick = [&](int minrows, const char* env) {
+        if (const char* e = getenv(env)) { const int v = atoi(e); if (v >= 256) return (v + 255) / 256 * 256; }
+        int rows = (g.rows_per_sample + 255) / 256 * 256;
+        while (rows > minrows && (long long)B * ((g.rows_per_sample + rows - 1) / rows) < 1184) {
+            int half = (rows / 2 + 255) / 256 * 256;
+            if (half >= rows) break;
+            rows = half < minrows ? minrows : half;
+        }
+        return rows;
+    };
+    int rows = pick(512, "CD_ATTN_ROWS");
     // the online form merges at most kAttnMaxBlocks partials per sample
     while ((g.rows_per_sample + rows - 1) / rows > kAttnMaxBlocks) rows += 32 * kWarps;
     const int nblk = (g.rows_per_sample + rows - 1) / rows;
@@ -683,7 +695,7 @@ void launch_fused_t(const Geom& g, const __half* x, const __half* wf, const floa
         fa_ctx_kernel<KS><<<grid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, kmax, ctx, rows, nblk > 1 ? 1 : 0);
         fa_fold_kernel<<<B, 256, 0, st>>>(ctx, wout, fold, 16 * KS);
     }
-    const int orows = 1024;
+    const int orows = pick(512, "CD_ATTN_OROWS");
     dim3 ogrid((g.rows_per_sample + orows - 1) / orows, B);
     fa_out_kernel<KS, 2 * KS><<<ogrid, 256, 0, st>>>(g, x, wf, wsum, wb, pn_stats, inv_count, fold, bout, dst, stats, orows);
 }
