@@ -507,12 +507,15 @@ __global__ void conv_strided_dgrad_kernel(ConvParams p, const __half* __restrict
     store8(o, pack8(acc));
 }
 
-// block: 32 (co) x 8 (ci quads) threads; grid (taps, ci blocks * co blocks, row splits).  The walk is over the COARSE grid, so
-// every staged (voxel, tap) pair is a real product: output voxels of a strided conv; (circularly padded) input voxels of a
-// transposed conv, whose tap (a,b,c) lands on output (2z+a-pz, 2q+b-(kp-1), 2r+c-pr).
+// Weight gradient of a strided / transposed conv on the tensor cores.  grid (taps, ci blocks * co blocks, splits); the block
+// walks 128-voxel tiles of the COARSE grid (output voxels of a strided conv; circularly padded input voxels of a transposed
+// conv, whose tap (a,b,c) lands on output (2z+a-pz, 2q+b-(kp-1), 2r+c-pr)), so every staged (voxel, tap) pair is a real
+// product.  Thread pair = one voxel: one thread gathers its 4 dY chunks, the other its 4 X chunks (cp.async, zero fill where
+// the pair does not exist) into fp16 chunk planes [chunk][voxel][8], double-buffered; then dW[32 ci][32 co] += X^T dY with
+// mma.sync m16n8k16 (K = the 128 voxels, one k16 step per warp; operands through ldmatrix.trans as in wgrad_mma_kernel).
 __global__ void __launch_bounds__(256) conv_strided_wgrad_kernel(ConvParams p, const __half* __restrict__ x, const __half* __restrict__ dy,
                                                                  float* __restrict__ dw, int Cin_real, int master_transposed) {
-    __shared__ float xs[32][33], ys[32][33];
+    __shared__ __align__(16) __half sx[2][4 * 128 * 8], sy[2][4 * 128 * 8];
     const int tap = blockIdx.x;
     const int ncob = p.Cout / 32;
     const int cib = blockIdx.y / ncob, cob = blockIdx.y - cib * ncob;
@@ -522,59 +525,91 @@ __global__ void __launch_bounds__(256) conv_strided_wgrad_kernel(ConvParams p, c
     const int wZ = p.transposed ? gi.Z : go.Z, wP = p.transposed ? gi.P + 2 * p.cp : go.P, wR = p.transposed ? gi.R : go.R;
     const int vps = wZ * wP * wR;
     const long long nvox = (long long)p.B * vps;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (long long v0 = (long long)blockIdx.z * 32; v0 < nvox; v0 += (long long)gridDim.z * 32) {
-        __syncthreads();
-        // stage 32 walk voxels: dY[out][co block] and X[in][ci block] of this tap (0 where the pair does not exist)
-        for (int i = threadIdx.x; i < 32 * 8; i += 256) {
-            const int r = i >> 3, k = i & 7;            // voxel r, chunk k (0-3: dY co chunks, 4-7: X ci chunks)
-            const long long v = v0 + r;
-            float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            if (v < nvox) {
-                const int b = (int)(v / vps);
-                int rem = (int)(v - (long long)b * vps);
-                const int wz = rem / (wP * wR); rem -= wz * wP * wR;
-                const int wp = rem / wR, wr = rem - wp * wR;
-                int zo, po, ro, zi, pin, rin;
-                if (!p.transposed) {
-                    zo = wz; po = wp; ro = wr;
-                    zi = zo * p.sz + a - p.pz; rin = ro * p.sr + c - p.pr; pin = po * p.sp + bq - p.cp;
-                } else {
-                    zi = wz; rin = wr; pin = wp - p.cp;
-                    zo = zi * p.sz + a - p.pz; ro = rin * p.sr + c - p.pr; po = wp * p.sp + bq - (p.kp - 1);
-                }
-                pin %= gi.P; if (pin < 0) pin += gi.P;
-                const bool ok = zi >= 0 && zi < gi.Z && rin >= 0 && rin < gi.R && zo >= 0 && zo < go.Z && po >= 0 && po < go.P &&
-                                ro >= 0 && ro < go.R;
-                if (ok) {
-                    if (k < 4) unpack8(load8(dy + plcp_offset(go, cob * 4 + k, interior_row(go, b, zo, po, ro))), f);
-                    else if ((cib * 4 + (k - 4)) < (p.Cin_total >> 3))          // a 16-channel input has two chunk planes only
-                        unpack8(load8(x + plcp_offset(gi, cib * 4 + (k - 4), interior_row(gi, b, zi, pin, rin))), f);
-                }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, mi = lane >> 3, mr = lane & 7;
+    const int sv = threadIdx.x >> 1, sh = threadIdx.x & 1;          // staging role: voxel of the tile, 0 = dY / 1 = X
+    const int xavail = (p.Cin_total >> 3) - cib * 4;                // X chunk planes that exist in this ci block
+    auto stage = [&](int buf, long long v0) {
+        const long long v = v0 + sv;
+        bool ok = v < nvox;
+        long long row = 0;
+        if (ok) {
+            const int b = (int)(v / vps);
+            int rem = (int)(v - (long long)b * vps);
+            const int wz = rem / (wP * wR); rem -= wz * wP * wR;
+            const int wp = rem / wR, wr = rem - wp * wR;
+            int zo, po, ro, zi, pin, rin;
+            if (!p.transposed) {
+                zo = wz; po = wp; ro = wr;
+                zi = zo * p.sz + a - p.pz; rin = ro * p.sr + c - p.pr; pin = po * p.sp + bq - p.cp;
+            } else {
+                zi = wz; rin = wr; pin = wp - p.cp;
+                zo = zi * p.sz + a - p.pz; ro = rin * p.sr + c - p.pr; po = wp * p.sp + bq - (p.kp - 1);
             }
-            float (*dst)[33] = k < 4 ? ys : xs;
+            pin %= gi.P; if (pin < 0) pin += gi.P;
+            ok = zi >= 0 && zi < gi.Z && rin >= 0 && rin < gi.R && zo >= 0 && zo < go.Z && po >= 0 && po < go.P && ro >= 0 && ro < go.R;
+            if (ok) row = sh ? interior_row(gi, b, zi, pin, rin) : interior_row(go, b, zo, po, ro);
+        }
+        __half* dstp = (sh ? sx[buf] : sy[buf]) + sv * 8;
+        const __half* srcp = sh ? x : dy;
+        const Geom& gs = sh ? gi : go;
+        const int k0 = sh ? cib * 4 : cob * 4;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dst[r][(k & 3) * 8 + j] = f[j];
+        for (int k = 0; k < 4; ++k) {
+            const bool okk = ok && (!sh || k < xavail);
+            cp_async16_zfill(dstp + k * 128 * 8, okk ? (const void*)(srcp + plcp_offset(gs, k0 + k, row)) : (const void*)srcp, okk);
+        }
+    };
+    float acc[2][4][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+    const long long stride = (long long)gridDim.z * 128;
+    long long v0 = (long long)blockIdx.z * 128;
+    if (v0 < nvox) stage(0, v0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (int it = 0; v0 < nvox; v0 += stride, ++it) {
+        if (v0 + stride < nvox) stage((it + 1) & 1, v0 + stride);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncthreads();
+        const __half* xb = sx[it & 1];
+        const __half* yb = sy[it & 1];
+        uint32_t bf[4][2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            uint32_t r[4];
+            const int chunk = 2 * jj + (mi >> 1), krow = warp * 16 + (mi & 1) * 8 + mr;
+            ldsm_x4_t(smem_u32(yb + ((size_t)chunk * 128 + krow) * 8), r);
+            bf[2 * jj][0] = r[0]; bf[2 * jj][1] = r[1]; bf[2 * jj + 1][0] = r[2]; bf[2 * jj + 1][1] = r[3];
+        }
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            uint32_t af[4];
+            const int chunk = 2 * t + (mi & 1), krow = warp * 16 + (mi >> 1) * 8 + mr;
+            ldsm_x4_t(smem_u32(xb + ((size_t)chunk * 128 + krow) * 8), af);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mma16816(acc[t][j], af, bf[j][0], bf[j][1]);
         }
         __syncthreads();
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-            const float yv = ys[r][tx];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[i] = fmaf(xs[r][ty * 4 + i], yv, acc[i]);
-        }
     }
-    const int co = cob * 32 + tx;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const int gq = lane >> 2, tq = lane & 3;
+    const int taps = p.kz * p.kp * p.kr;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int ci = cib * 32 + ty * 4 + i;
-        if (ci >= Cin_real || acc[i] == 0.f) continue;
-        const int taps = p.kz * p.kp * p.kr;
-        // master layouts: Conv3d [co][ci][tap]; ConvTranspose3d [ci][co][tap]
-        const long long idx = master_transposed ? ((long long)ci * p.Cout + co) * taps + tap : ((long long)co * Cin_real + ci) * taps + tap;
-        atomicAdd(dw + idx, acc[i]);
-    }
+    for (int t = 0; t < 2; ++t)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int ci = cib * 32 + t * 16 + gq + (e >> 1) * 8, co = cob * 32 + j * 8 + tq * 2 + (e & 1);
+                if (ci >= Cin_real || acc[t][j][e] == 0.f) continue;
+                // master layouts: Conv3d [co][ci][tap]; ConvTranspose3d [ci][co][tap]
+                const long long idx = master_transposed ? ((long long)ci * p.Cout + co) * taps + tap : ((long long)co * Cin_real + ci) * taps + tap;
+                atomicAdd(dw + idx, acc[t][j][e]);
+            }
 }
 
 // per-channel sum over interior rows of a PLCP tensor (bias gradient of convolutions that are not followed by a GroupNorm)
