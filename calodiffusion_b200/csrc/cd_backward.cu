@@ -299,8 +299,8 @@ __device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b
 }
 
 constexpr int kWgRows = 128;          // rows per chunk (K of the MMAs: 8 k16 steps)
-constexpr int kWgWarps = 8;
-constexpr int kWgMaxTapsPerWarp = 4;  // 27 taps over 8 warps
+constexpr int kWgWarps = 28;
+constexpr int kWgMaxTapsPerWarp = 1;  // 27 taps over 28 warps (one spare)
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
     const uint32_t n = valid ? 16u : 0u;       // src-size 0: the 16 bytes are zero-filled, the source is not read
@@ -1058,9 +1058,20 @@ __global__ void adam_kernel(float* __restrict__ w, float* __restrict__ m, float*
 //   4: gather-tcgen05 layout [tap][kc][co][8] (gather_pack_weights); 5: the merged output-pair layout of the stride-2 transposed
 //   conv [(a*kp+b)*3+dr+1][kc][2*Cout][8] (gather_pack_weights_pairT); both read the mode-0 array `pk`, optionally with the
 //   channel roles swapped.
+__device__ __forceinline__ void repack_one(const RepackParams& p, long long i);
 __global__ void repack_conv_kernel(RepackParams p) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.n) return;
+    if (i < p.n) repack_one(p, i);
+}
+// all jobs of a handle in one launch: grid (blocks of the largest job, jobs)
+__global__ void repack_table_kernel(const RepackParams* __restrict__ table) {
+    __shared__ RepackParams p;
+    if (threadIdx.x == 0) p = table[blockIdx.y];
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.n) repack_one(p, i);
+}
+__device__ __forceinline__ void repack_one(const RepackParams& p, long long i) {
     if (p.mode >= 4) {
         const int Cg_in = p.swap ? p.Cout : p.Cin_pad, Cg_out = p.swap ? p.Cin_pad : p.Cout;
         const int nkc = (Cg_in + 15) / 16 * 2;
@@ -1085,8 +1096,12 @@ __global__ void repack_conv_kernel(RepackParams p) {
         }
         const int ci = kc * 8 + j;
         float v = 0.f;
-        if (live && ci < Cg_in)
-            v = p.swap ? p.pk[((long long)tap * p.Cin_pad + co) * p.Cout + ci] : p.pk[((long long)tap * p.Cin_pad + ci) * p.Cout + co];
+        if (live && ci < Cg_in) {
+            // straight from the master (not from the mode-0 array: all jobs of a handle run in ONE launch, unordered)
+            const int fci = p.swap ? co : ci, fco = p.swap ? ci : co;          // forward conv's input / output channel
+            if (fci < p.Cin_real)
+                v = p.transposed ? p.master[((long long)fci * p.Cout + fco) * p.taps + tap] : p.master[((long long)fco * p.Cin_real + fci) * p.taps + tap];
+        }
         p.out_h[i] = __float2half_rn(v);
         return;
     }
@@ -1219,6 +1234,30 @@ void launch_embed_backward(const EmbedParams& p, const EmbedBwdLayout& L, const 
     embed_backward_kernel<<<B, 256, 0, st>>>(p, L, sigma, cond, daddvec, rec);
 }
 
+// all Linear weight gradients of a step in one launch: grid (blocks of the largest job, jobs), B passed per launch
+__global__ void linear_wgrad_table_kernel(const LinearJob* __restrict__ table, int B) {
+    const LinearJob j = table[blockIdx.y];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= j.n_out * (j.n_in + 1)) return;
+    const int o = idx / (j.n_in + 1), i = idx - o * (j.n_in + 1);
+    float a0 = 0.f, a1 = 0.f;
+    if (i < j.n_in) {
+        int b = 0;
+        for (; b + 1 < B; b += 2) {           // two independent chains: the loop is load-latency bound
+            a0 = fmaf(j.dY[b * j.sy + o], j.X[b * j.sx + i], a0);
+            a1 = fmaf(j.dY[(b + 1) * j.sy + o], j.X[(b + 1) * j.sx + i], a1);
+        }
+        if (b < B) a0 = fmaf(j.dY[b * j.sy + o], j.X[b * j.sx + i], a0);
+        j.dW[(long long)o * j.n_in + i] += a0 + a1;
+    } else {
+        for (int b = 0; b < B; ++b) a0 += j.dY[b * j.sy + o];
+        j.dbias[o] += a0;
+    }
+}
+void launch_linear_wgrad_table(const LinearJob* table_dev, int njobs, int max_n, int B, cudaStream_t st) {
+    if (njobs < 1) return;
+    linear_wgrad_table_kernel<<<dim3((max_n + 127) / 128, njobs), 128, 0, st>>>(table_dev, B);
+}
 void launch_linear_wgrad(const float* dY, long long sy, const float* X, long long sx, int B, int n_out, int n_in, float* dW, float* dbias,
                          cudaStream_t st) {
     const int n = n_out * (n_in + 1);
@@ -1231,6 +1270,10 @@ void launch_adam(float* w, float* m, float* v, float* g, long long n, float lr, 
     adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w, m, v, g, n, lr, beta1, beta2, eps, bc1, bc2, inv_scale);
 }
 
+void launch_repack_table(const RepackParams* table_dev, int njobs, long long max_n, cudaStream_t st) {
+    if (njobs < 1) return;
+    repack_table_kernel<<<dim3((unsigned)((max_n + 255) / 256), njobs), 256, 0, st>>>(table_dev);
+}
 void launch_repack_conv(const RepackParams& p, cudaStream_t st) {
     repack_conv_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, st>>>(p);
 }

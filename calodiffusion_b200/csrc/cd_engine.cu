@@ -123,6 +123,8 @@ struct cd_unet {
     float* gn_acc = nullptr; float* gn_m12 = nullptr; float* attn_dcx = nullptr; float* daddvec = nullptr; float* embed_rec = nullptr;
     float* x_noisy = nullptr; float* x0_buf = nullptr; float* coef = nullptr; double* loss_dev = nullptr;
     cd::EmbedBwdLayout embed_layout = {};
+    cd::LinearJob* linear_tab = nullptr; int linear_jobs = 0, linear_max_n = 0;                 // device table of the Linear weight-gradient jobs
+    cd::RepackParams* repack_tab = nullptr; int repack_jobs = 0; long long repack_max_n = 0;   // device table of weight re-layout jobs
     std::vector<__half*> bwd_tmp;  // per level: scratch gradient tensor for data gradients accumulated outside the conv epilogue
     int tin_buf_index = -1;
     std::vector<std::string> proj_names;        // state-dict prefix of every conditioned block's Linear (e.g. model.downs.0.0.mlp.1)

@@ -181,6 +181,9 @@ struct RepackParams {
     const float* pk; int swap, kz, kp, kr;
 };
 
+struct LinearJob { const float* dY; const float* X; float* dW; float* dbias; long long sy, sx; int n_out, n_in; };
+void launch_linear_wgrad_table(const LinearJob* table_dev, int njobs, int max_n, int B, cudaStream_t st);
+void launch_repack_table(const RepackParams* table_dev, int njobs, long long max_n, cudaStream_t st);
 void launch_loss_backward(const LossBwdParams& p, int B, cudaStream_t st);
 void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st);
 int launch_wgrad_mma(const WgradParams& p, cudaStream_t st);

@@ -27,7 +27,12 @@ __global__ void loss_coef_kernel(const float* __restrict__ sigma, int B, double 
     }
 }
 
+// Every kernel weight layout is a pure function of the flat master buffer; the list of re-layout jobs is fixed once the plan is
+// built, so it lives in a device table and one launch (grid.y = job) refreshes all of them after an optimizer step.
 static void train_refresh_weights(cd_unet* h, cudaStream_t st) {
+    if (h->repack_tab) { launch_repack_table(h->repack_tab, h->repack_jobs, h->repack_max_n, st); return; }
+    std::vector<RepackParams> jobs;
+    auto launch_repack_conv = [&jobs](const RepackParams& r, cudaStream_t) { jobs.push_back(r); };
     for (const TapeOp& t : h->tape) {
         if (t.kind != 0) continue;
         const int taps = t.kz * t.kp * t.kr;
@@ -69,6 +74,14 @@ static void train_refresh_weights(cd_unet* h, cudaStream_t st) {
             lo += Cs;
         }
     }
+    long long mx = 1;
+    for (const RepackParams& r : jobs) if (r.n > mx) mx = r.n;
+    h->repack_tab = h->dalloc<RepackParams>(jobs.size() ? jobs.size() : 1, false);
+    if (h->repack_tab && !jobs.empty())
+        cudaMemcpyAsync(h->repack_tab, jobs.data(), jobs.size() * sizeof(RepackParams), cudaMemcpyHostToDevice, st);
+    cudaStreamSynchronize(st);          // `jobs` is pageable host memory: the copy must be done before it goes out of scope
+    h->repack_jobs = (int)jobs.size(); h->repack_max_n = mx;
+    if (h->repack_tab) launch_repack_table(h->repack_tab, h->repack_jobs, h->repack_max_n, st);
 }
 
 static int train_setup(cd_unet* h) {
@@ -305,24 +318,35 @@ static int run_backward(cd_unet* h, int B, const float* data, const float* sigma
     const EmbedParams& e = h->embed;
     const EmbedBwdLayout& L = h->embed_layout;
     launch_embed_backward(e, L, sigma, cond, h->daddvec, h->embed_rec, B, st);
-    const int half = e.cond_dim / 2, h2 = half / 2;
-    const std::string M = "model.";
-    struct Lin { const char* name; int dy, x, n_out, n_in; };
-    const Lin lins[6] = {{"time_mlp.5", L.dt3, L.t2, half, half}, {"time_mlp.3", L.dt2, L.t1, half, h2}, {"time_mlp.1", L.dt1, L.t0, h2, 1},
-                         {"cond_mlp.4", L.dc3, L.c2, half, half}, {"cond_mlp.2", L.dc2, L.c1, half, e.cond_hidden},
-                         {"cond_mlp.0", L.dc1, L.c0, e.cond_hidden, e.cond_size}};
-    for (const Lin& l : lins) {
-        float* dW = h->gptr(M + l.name + ".weight");
-        float* db = h->gptr(M + l.name + ".bias");
-        if (!dW || !db) return fail("training: %s has no gradient slot", l.name);
-        launch_linear_wgrad(h->embed_rec + l.dy, L.stride, h->embed_rec + l.x, L.stride, B, l.n_out, l.n_in, dW, db, st);
+    if (!h->linear_tab) {       // the jobs are fixed once the plan is built (all pointers are the handle's own buffers)
+        const int half = e.cond_dim / 2, h2 = half / 2;
+        const std::string M = "model.";
+        struct Lin { const char* name; int dy, x, n_out, n_in; };
+        const Lin lins[6] = {{"time_mlp.5", L.dt3, L.t2, half, half}, {"time_mlp.3", L.dt2, L.t1, half, h2}, {"time_mlp.1", L.dt1, L.t0, h2, 1},
+                             {"cond_mlp.4", L.dc3, L.c2, half, half}, {"cond_mlp.2", L.dc2, L.c1, half, e.cond_hidden},
+                             {"cond_mlp.0", L.dc1, L.c0, e.cond_hidden, e.cond_size}};
+        std::vector<LinearJob> jobs;
+        for (const Lin& l : lins) {
+            float* dW = h->gptr(M + l.name + ".weight");
+            float* db = h->gptr(M + l.name + ".bias");
+            if (!dW || !db) return fail("training: %s has no gradient slot", l.name);
+            jobs.push_back({h->embed_rec + l.dy, h->embed_rec + l.x, dW, db, (long long)L.stride, (long long)L.stride, l.n_out, l.n_in});
+        }
+        for (int k = 0; k < e.n_proj; ++k) {
+            float* dW = h->gptr(h->proj_names[k] + ".weight");
+            float* db = h->gptr(h->proj_names[k] + ".bias");
+            if (!dW || !db) return fail("training: projection %d has no gradient slot", k);
+            jobs.push_back({h->daddvec + e.poff[k], h->embed_rec + L.cvec, dW, db, (long long)h->addvec_stride, (long long)L.stride, e.pC[k], e.cond_dim});
+        }
+        int mx = 1;
+        for (const LinearJob& j : jobs) mx = std::max(mx, j.n_out * (j.n_in + 1));
+        h->linear_tab = h->dalloc<LinearJob>(jobs.size(), false);
+        if (!h->linear_tab) return fail("out of device memory for the training tables");
+        cudaMemcpyAsync(h->linear_tab, jobs.data(), jobs.size() * sizeof(LinearJob), cudaMemcpyHostToDevice, st);
+        cudaStreamSynchronize(st);
+        h->linear_jobs = (int)jobs.size(); h->linear_max_n = mx;
     }
-    for (int k = 0; k < e.n_proj; ++k) {
-        float* dW = h->gptr(h->proj_names[k] + ".weight");
-        float* db = h->gptr(h->proj_names[k] + ".bias");
-        if (!dW || !db) return fail("training: projection %d has no gradient slot", k);
-        launch_linear_wgrad(h->daddvec + e.poff[k], h->addvec_stride, h->embed_rec + L.cvec, L.stride, B, e.pC[k], e.cond_dim, dW, db, st);
-    }
+    launch_linear_wgrad_table(h->linear_tab, h->linear_jobs, h->linear_max_n, B, st);
     mark("embed_mlps", nullptr, 0, e.cond_dim, 0, 0.0);
     if (h->profile && nev > 1) {
         cudaEventSynchronize(h->prof_evs[nev - 1]);
