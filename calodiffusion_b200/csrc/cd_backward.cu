@@ -299,8 +299,8 @@ __device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b
 }
 
 constexpr int kWgRows = 128;          // rows per chunk (K of the MMAs: 8 k16 steps)
-constexpr int kWgWarps = 28;
-constexpr int kWgMaxTapsPerWarp = 1;  // 27 taps over 28 warps (one spare)
+constexpr int kWgWarps = 16;
+constexpr int kWgMaxTapsPerWarp = 2;  // 27 taps over 16 warps (8 warps x 4 taps: 150 TFLOP/s, 16 x 2: 198, 28 x 1: 167 at DS2 L0)
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
     const uint32_t n = valid ? 16u : 0u;       // src-size 0: the 16 bytes are zero-filled, the source is not read
@@ -1150,7 +1150,7 @@ void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st) {
     const int nch = p.C >> 3;
     if (kGbThreads % nch != 0 || p.C > kBwdMaxC) return;     // checked by the caller (C in {16,32,64,96,128})
     gn_bwd_prep_kernel<<<B, 128, 0, st>>>(p);
-    p.rows_per_block = 2048;
+    p.rows_per_block = 1024;     // 2048 left the last of 5 blocks per DS2 sample with 88 rows and one ragged wave (ncu: 30 % warps active)
     dim3 grid1((g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);
     gn_bwd_reduce_kernel<<<grid1, kGbThreads, 0, st>>>(p);
     gn_bwd_finalize_kernel<<<B, 256, 0, st>>>(p);
