@@ -9,6 +9,7 @@
 //     weight gradient = wgrad_mma_kernel below (mma.sync m16n8k16, K = voxels x batch).
 //   * strided / transposed convolutions (4 per network, 5 % of the FLOPs): exact adjoints by inverse index enumeration (SIMT).
 //   * GroupNorm + SiLU + conditioning + residual, linear attention, the conditioning MLPs, the final 1x1x1 conv + loss.
+#include <cstdlib>
 #include "cd_kernels.cuh"
 
 namespace cd {
@@ -936,6 +937,227 @@ __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// apply pass on the tensor cores (C a multiple of 16).  A warp owns 32 consecutive rows (two m16 tiles); the four per-voxel
+// 32x32 matvecs of the SIMT form become mma.sync m16n8k16 GEMMs chained through registers, the accumulator fragment of one
+// being repacked (fp16) as the A fragment of the next, as fa_out_kernel does in the forward pass:
+//   datt = dy Wout (K = C)  ->  dP = s datt Cx^T  ->  dq = P (dP - <P,dP>)          P = softmax_d(q), in accumulator layout
+//   dKpre = v dCx^T  ->  dk = K (dKpre - T)   ;   dv = K dCx                          K = exp(k - kmax) / S
+// q / k are read from global memory directly in the accumulator layout, dy / v directly as A fragments (in PLCP one 8-row x
+// 8-channel fragment is 128 contiguous bytes); the small matrices sit in shared memory as fp16 B operands (dCx scaled by
+// 1/16 to stay well inside fp16 range).  Halo / guard rows of dqkv are written as zeros (whole 32-byte sectors).
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm_x4_n(uint32_t addr, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t pack2h(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float2 unpack2h(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+
+constexpr int kAbStr = 80;            // bytes per row of the 32-wide fp16 matrices (conflict-free ldmatrix)
+constexpr float kDcxScale = 0.0625f;
+
+__global__ void __launch_bounds__(128) attn_bwd_apply_mma_kernel(AttnBwdParams p) {
+    extern __shared__ __align__(16) unsigned char abs_[];
+    const int b = blockIdx.y, C = p.C, KS = C >> 4, wstr = C * 2 + 16;
+    const Geom& g = p.g;
+    unsigned char* s_cx = abs_;                          // Cx[d][e] fp16, rows of kAbStr bytes
+    unsigned char* s_dcx = s_cx + 32 * kAbStr;           // dCx[d][e] / 16
+    unsigned char* s_wt = s_dcx + 32 * kAbStr;           // Wout^T[e][c], rows of wstr bytes
+    float* s_km = reinterpret_cast<float*>(s_wt + 32 * wstr);
+    float* s_sinv = s_km + 32;
+    float* s_T = s_sinv + 32;
+    const float* ctx = p.ctx + (long long)b * 33 * 32;
+    for (int i = threadIdx.x; i < 32; i += blockDim.x) { s_km[i] = ord2f_b(p.kmax[b * 32 + i]); s_sinv[i] = 1.f / ctx[32 * 32 + i]; }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+        const int d = i >> 5, e = i & 31;
+        *reinterpret_cast<__half*>(s_cx + d * kAbStr + e * 2) = __float2half_rn(ctx[i] * s_sinv[d]);
+        *reinterpret_cast<__half*>(s_dcx + d * kAbStr + e * 2) = __float2half_rn(p.dcx[(long long)b * 1024 + i] * kDcxScale);
+    }
+    for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
+        const int c = i >> 5, e = i & 31;
+        *reinterpret_cast<__half*>(s_wt + e * wstr + c * 2) = __float2half_rn(p.wout[i]);
+    }
+    if (threadIdx.x < 32) {                               // T[d] = sum_e dCx[d][e] Cx[d][e]  (fp32, from the fp32 sources)
+        const int d = threadIdx.x;
+        float t = 0.f;
+        for (int e = 0; e < 32; ++e) t = fmaf(p.dcx[(long long)b * 1024 + d * 32 + e], ctx[d * 32 + e] * s_sinv[d], t);
+        s_T[d] = t;
+    }
+    __syncthreads();
+    const float scale = 0.17677669529663687f;   // 32^-0.5
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gq = lane >> 2, tq = lane & 3;
+    const uint32_t r0 = blockIdx.x * p.rows_per_block;
+    uint32_t r1 = r0 + p.rows_per_block;
+    if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const long long srow0 = (long long)b * g.rows_per_sample;
+    const long long cs = g.chunk_stride * 8;
+    const __half* qb = p.qkv + plcp_offset(g, 0, srow0);
+    const __half* dyb = p.dy + plcp_offset(g, 0, srow0);
+    __half* ob = p.dqkv + plcp_offset(g, 0, srow0);
+    for (uint32_t base = r0 + warp * 32; base < r1; base += 4 * 32) {
+        const uint32_t rem = base + lane;
+        const bool inb = rem < r1;
+        const unsigned vmask = __ballot_sync(0xffffffffu, inb && decode_subrow(g, rem).kind == 0);
+        const unsigned imask = __ballot_sync(0xffffffffu, inb);
+        if (vmask == 0u) {          // nothing to differentiate in this group: zero rows
+            if (inb) {
+                const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+                for (int k = 0; k < 12; ++k) *reinterpret_cast<uint4*>(ob + (long long)rem * 8 + k * cs) = z;
+            }
+            continue;
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            const uint32_t rA = base + mt * 16 + gq, rB = rA + 8;         // this lane's two rows of the m tile
+            const bool ldA = rA < r1, ldB = rB < r1;
+            const bool vA = (vmask >> (mt * 16 + gq)) & 1u, vB = (vmask >> (mt * 16 + gq + 8)) & 1u;
+            const bool sA = (imask >> (mt * 16 + gq)) & 1u, sB = (imask >> (mt * 16 + gq + 8)) & 1u;
+            const long long oA = (long long)rA * 8 + 2 * tq, oB = (long long)rB * 8 + 2 * tq;
+            // ---- P = softmax_d(q) in accumulator layout: P[j][0,1] = row A cols 8j+2t,+1 ; [2,3] = row B
+            float P[4][4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 a = unpack2h(ldA ? __ldg(reinterpret_cast<const unsigned*>(qb + oA + j * cs)) : 0u);
+                const float2 c = unpack2h(ldB ? __ldg(reinterpret_cast<const unsigned*>(qb + oB + j * cs)) : 0u);
+                P[j][0] = a.x; P[j][1] = a.y; P[j][2] = c.x; P[j][3] = c.y;
+            }
+            float m0 = P[0][0], m1 = P[0][2];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { m0 = fmaxf(m0, fmaxf(P[j][0], P[j][1])); m1 = fmaxf(m1, fmaxf(P[j][2], P[j][3])); }
+            m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                P[j][0] = __expf(P[j][0] - m0); P[j][1] = __expf(P[j][1] - m0); s0 += P[j][0] + P[j][1];
+                P[j][2] = __expf(P[j][2] - m1); P[j][3] = __expf(P[j][3] - m1); s1 += P[j][2] + P[j][3];
+            }
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 1); s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+            const float i0 = 1.f / s0, i1 = 1.f / s1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { P[j][0] *= i0; P[j][1] *= i0; P[j][2] *= i1; P[j][3] *= i1; }
+            // ---- datt = dy Wout : A = dy fragments from global, B = Wout^T rows (e) x k (c)
+            float acc[4][4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            for (int sp = 0; sp < KS; sp += 2) {            // two k16 steps (32 channels of dy) per ldmatrix.x4
+                uint32_t a[2][4];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int s = sp + u;
+                    const bool have = s < KS;
+                    a[u][0] = (have && ldA) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oA + (2 * s) * cs)) : 0u;
+                    a[u][1] = (have && ldB) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oB + (2 * s) * cs)) : 0u;
+                    a[u][2] = (have && ldA) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oA + (2 * s + 1) * cs)) : 0u;
+                    a[u][3] = (have && ldB) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oB + (2 * s + 1) * cs)) : 0u;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t bw[4];
+                    ldsm_x4_n(smem_u32(s_wt) + (j * 8 + (lane & 7)) * wstr + sp * 32 + (lane >> 3) * 16, bw);
+                    mma16816(acc[j], a[0], bw[0], bw[1]);
+                    if (sp + 1 < KS) mma16816(acc[j], a[1], bw[2], bw[3]);
+                }
+            }
+            // ---- dP = s datt Cx^T ; dq = P (dP - <P, dP>)
+            uint32_t af[2][4];
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+                af[ks][0] = pack2h(acc[2 * ks][0], acc[2 * ks][1]); af[ks][1] = pack2h(acc[2 * ks][2], acc[2 * ks][3]);
+                af[ks][2] = pack2h(acc[2 * ks + 1][0], acc[2 * ks + 1][1]); af[ks][3] = pack2h(acc[2 * ks + 1][2], acc[2 * ks + 1][3]);
+            }
+            float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint32_t bc[4];
+                ldsm_x4_n(smem_u32(s_cx) + (j * 8 + (lane & 7)) * kAbStr + (lane >> 3) * 16, bc);
+                acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+                mma16816(acc[j], af[0], bc[0], bc[1]);
+                mma16816(acc[j], af[1], bc[2], bc[3]);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc[j][e] *= scale;               // dP = 32^-1/2 Cx datt
+                d0 = fmaf(P[j][0], acc[j][0], fmaf(P[j][1], acc[j][1], d0));
+                d1 = fmaf(P[j][2], acc[j][2], fmaf(P[j][3], acc[j][3], d1));
+            }
+            d0 += __shfl_xor_sync(0xffffffffu, d0, 1); d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
+            d1 += __shfl_xor_sync(0xffffffffu, d1, 1); d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float q0 = vA ? P[j][0] * (acc[j][0] - d0) : 0.f, q1 = vA ? P[j][1] * (acc[j][1] - d0) : 0.f;
+                const float q2 = vB ? P[j][2] * (acc[j][2] - d1) : 0.f, q3 = vB ? P[j][3] * (acc[j][3] - d1) : 0.f;
+                if (sA) *reinterpret_cast<unsigned*>(ob + oA + j * cs) = pack2h(q0, q1);
+                if (sB) *reinterpret_cast<unsigned*>(ob + oB + j * cs) = pack2h(q2, q3);
+            }
+            // ---- K = exp(k - kmax) / S (accumulator layout, reusing P) ; v as A fragments
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 a = unpack2h(ldA ? __ldg(reinterpret_cast<const unsigned*>(qb + oA + (4 + j) * cs)) : 0u);
+                const float2 c = unpack2h(ldB ? __ldg(reinterpret_cast<const unsigned*>(qb + oB + (4 + j) * cs)) : 0u);
+                const int dcol = j * 8 + 2 * tq;
+                const float k0 = s_km[dcol], k1 = s_km[dcol + 1], v0 = s_sinv[dcol], v1 = s_sinv[dcol + 1];
+                P[j][0] = __expf(a.x - k0) * v0; P[j][1] = __expf(a.y - k1) * v1;
+                P[j][2] = __expf(c.x - k0) * v0; P[j][3] = __expf(c.y - k1) * v1;
+            }
+            uint32_t av[2][4];
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+                av[ks][0] = ldA ? __ldg(reinterpret_cast<const unsigned*>(qb + oA + (8 + 2 * ks) * cs)) : 0u;
+                av[ks][1] = ldB ? __ldg(reinterpret_cast<const unsigned*>(qb + oB + (8 + 2 * ks) * cs)) : 0u;
+                av[ks][2] = ldA ? __ldg(reinterpret_cast<const unsigned*>(qb + oA + (8 + 2 * ks + 1) * cs)) : 0u;
+                av[ks][3] = ldB ? __ldg(reinterpret_cast<const unsigned*>(qb + oB + (8 + 2 * ks + 1) * cs)) : 0u;
+            }
+            // ---- dk = K (v dCx^T - T)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint32_t bd[4];
+                ldsm_x4_n(smem_u32(s_dcx) + (j * 8 + (lane & 7)) * kAbStr + (lane >> 3) * 16, bd);
+                acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+                mma16816(acc[j], av[0], bd[0], bd[1]);
+                mma16816(acc[j], av[1], bd[2], bd[3]);
+                const int dcol = j * 8 + 2 * tq;
+                const float t0 = s_T[dcol], t1 = s_T[dcol + 1];
+                const float inv = 1.f / kDcxScale;
+                const float q0 = vA ? P[j][0] * (acc[j][0] * inv - t0) : 0.f, q1 = vA ? P[j][1] * (acc[j][1] * inv - t1) : 0.f;
+                const float q2 = vB ? P[j][2] * (acc[j][2] * inv - t0) : 0.f, q3 = vB ? P[j][3] * (acc[j][3] * inv - t1) : 0.f;
+                if (sA) *reinterpret_cast<unsigned*>(ob + oA + (4 + j) * cs) = pack2h(q0, q1);
+                if (sB) *reinterpret_cast<unsigned*>(ob + oB + (4 + j) * cs) = pack2h(q2, q3);
+            }
+            // ---- dv = K dCx : A = K repacked, B[k = d][n = e] = dCx[d][e] through ldmatrix.trans
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+                af[ks][0] = pack2h(P[2 * ks][0], P[2 * ks][1]); af[ks][1] = pack2h(P[2 * ks][2], P[2 * ks][3]);
+                af[ks][2] = pack2h(P[2 * ks + 1][0], P[2 * ks + 1][1]); af[ks][3] = pack2h(P[2 * ks + 1][2], P[2 * ks + 1][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                for (int jj = 0; jj < 2; ++jj) {
+                    uint32_t bt[4];
+                    // matrices: (k 0-7, n tile 2jj) (k 8-15, n tile 2jj) (k 0-7, n tile 2jj+1) (k 8-15, n tile 2jj+1)
+                    const int mi = lane >> 3, mr = lane & 7;
+                    ldsm_x4_t(smem_u32(s_dcx) + (ks * 16 + (mi & 1) * 8 + mr) * kAbStr + (2 * jj + (mi >> 1)) * 16, bt);
+                    mma16816(acc[2 * jj], af[ks], bt[0], bt[1]);
+                    mma16816(acc[2 * jj + 1], af[ks], bt[2], bt[3]);
+                }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float inv = 1.f / kDcxScale;
+                const float q0 = vA ? acc[j][0] * inv : 0.f, q1 = vA ? acc[j][1] * inv : 0.f;
+                const float q2 = vB ? acc[j][2] * inv : 0.f, q3 = vB ? acc[j][3] * inv : 0.f;
+                if (sA) *reinterpret_cast<unsigned*>(ob + oA + (8 + j) * cs) = pack2h(q0, q1);
+                if (sB) *reinterpret_cast<unsigned*>(ob + oB + (8 + j) * cs) = pack2h(q2, q3);
+            }
+        }
+    }
+}
+
 // =================================================================================================
 // Conditioning MLPs backward (models.py:575-608, 176-178): one block per sample recomputes the forward (as embed_kernel),
 // back-propagates the gradient of the additive conditioning vectors through the per-block projections, the SiLU and both
@@ -1225,7 +1447,12 @@ int launch_attn_backward(AttnBwdParams p, int B, cudaStream_t st) {
         configured = smem;
     }
     attn_bwd_reduce_kernel<<<grid, 128, smem, st>>>(p);
-    attn_bwd_apply_kernel<<<grid, 128, 0, st>>>(p);
+    static const bool simt_apply = getenv("CD_ATTN_BWD_SIMT") != nullptr;       // diagnostics: the per-voxel SIMT form
+    if (simt_apply) { attn_bwd_apply_kernel<<<grid, 128, 0, st>>>(p); return 0; }
+    const size_t asmem = (size_t)2 * 32 * kAbStr + (size_t)32 * (p.C * 2 + 16) + 3 * 32 * sizeof(float);
+    p.rows_per_block = 1024;
+    dim3 agrid((p.g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);
+    attn_bwd_apply_mma_kernel<<<agrid, 128, asmem, st>>>(p);
     return 0;
 }
 
