@@ -252,8 +252,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     // accumulator slot of sub-tile n: even sub-tiles (issuer 0 / epilogue group 0) and odd ones (issuer 1 / group 1)
     // own disjoint halves of the slot ring, so every slot's full/empty chain has one producer and one consumer
     const uint32_t hacc = (uint32_t)p.nacc >> 1;
-    auto slot_of = [&](uint32_t n) { return 2u * ((n >> 1) % hacc) + (n & 1u); };
-    auto phase_of = [&](uint32_t n) { return ((n >> 1) / hacc) & 1u; };
+    // (runtime integer divisions cost ~25 instructions and a MUFU round trip each; these run once per sub-tile in every role.
+    //  hacc is 1, 2 or 4 for every shape in use: mask / shift, with the division kept for the odd case)
+    const bool hacc_p2 = (hacc & (hacc - 1u)) == 0u;
+    const uint32_t hacc_log = 31u - (uint32_t)__clz((int)hacc);
+    auto slot_of = [&](uint32_t n) { const uint32_t h = n >> 1; return 2u * (hacc_p2 ? (h & (hacc - 1u)) : (h % hacc)) + (n & 1u); };
+    auto phase_of = [&](uint32_t n) { const uint32_t h = n >> 1; return (hacc_p2 ? (h >> hacc_log) : (h / hacc)) & 1u; };
 
     const int cb = blockIdx.x % p.ncb;
     const int cta = blockIdx.x / p.ncb;
@@ -276,12 +280,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     bulk_g2s(wbuf_s + off, wsrc + off, n, smem_u32(&ctl->w_res));
                 }
             }
-            uint32_t wcount = 0;
-            for (int item = 0; item < my_tiles * p.ksplit; ++item) {
-                const int it = item / p.ksplit, kgi = item - it * p.ksplit;
+            uint32_t ws = 0, wph = 0;                 // weight-ring stage / phase (counters instead of % and /)
+            int it = 0, kgi = 0, stage = 0;
+            uint32_t ph = 0;
+            for (int item = 0; item < my_tiles * p.ksplit; ++item,
+                     kgi = (kgi + 1 == p.ksplit) ? 0 : kgi + 1, it += (kgi == 0), stage = (stage + 1 == p.astages) ? 0 : stage + 1,
+                     ph ^= (uint32_t)(stage == 0)) {
                 const int tile = tile_begin + it;
-                const int stage = item % p.astages;
-                const uint32_t ph = (item / p.astages) & 1;
                 const long long d0 = (long long)tile * p.tile_rows + p.d_lead;
                 mbar_wait_relaxed(smem_u32(&ctl->a_empty[stage]), ph ^ 1);
                 const bool stale = DBG_MODE(2) && item >= p.astages;      // debug: reuse the windows already in shared memory
@@ -300,8 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 }
                 if (!p.resident) {
                     for (int s = 0; s < p.nshift; ++s) {
-                        for (int kg = 0; kg < nkg; ++kg, ++wcount) {
-                            const uint32_t ws = wcount % p.nwstages, wph = (wcount / p.nwstages) & 1;
+                        for (int kg = 0; kg < nkg; ++kg, ws = (ws + 1 == (uint32_t)p.nwstages) ? 0u : ws + 1, wph ^= (uint32_t)(ws == 0)) {
                             const int kc0 = kg * p.kgroup_chunks;
                             const int kcn = (p.nchunks - kc0) < p.kgroup_chunks ? (p.nchunks - kc0) : p.kgroup_chunks;
                             const uint32_t bytes = (uint32_t)kcn * N * 16u;
@@ -341,7 +345,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             const uint32_t qstep = (2u * chunk_bytes) >> 4, bstep = (2u * N * 16u) >> 4;
             const uint32_t jstep = ((uint32_t)p.sub_stride * 16u) >> 4;
             const int nq = p.nchunks >> 1;
-            uint32_t cnt = 0, wcount = 0;
+            uint32_t cnt = 0;
+            uint32_t ws = 0, wph = 0;                 // weight-ring stage / phase
+            int astage = 0;                           // activation-ring stage / phase of the next item
+            uint32_t aph = 0;
+            auto next_astage = [&]() { astage = (astage + 1 == p.astages) ? 0 : astage + 1; aph ^= (uint32_t)(astage == 0); };
             if (p.resident) mbar_wait(smem_u32(&ctl->w_res), 0);
             const int gq = p.gchunks >> 1;                       // K16 steps per staged K group
             const uint32_t bshift = (uint32_t)p.nchunks * N;     // weight offset (16-byte units) between (dz,dp) shifts
@@ -362,10 +370,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             for (int it = 0; it < my_tiles; ++it) {
                 if (p.resident) {
                     // a tile's K range arrives in ksplit stages; every sub-tile accumulator stays open until the last one
-                    for (int kgi = 0; kgi < p.ksplit; ++kgi) {
-                        const int item = it * p.ksplit + kgi;
-                        const int stage = item % p.astages;
-                        const uint32_t ph = (item / p.astages) & 1;
+                    for (int kgi = 0; kgi < p.ksplit; ++kgi, next_astage()) {
+                        const int stage = astage;
+                        const uint32_t ph = aph;
                         const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
                         const uint32_t b_kg = (uint32_t)(kgi * p.gchunks) * N;
                         const uint32_t b_lo0 = (wbuf_s >> 4) + b_kg;
@@ -417,8 +424,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     continue;
                 }
                 if (!leader) { cnt += p.MT; continue; }      // streamed-weight form: the elected lane walks alone
-                const int stage = it % p.astages;
-                const uint32_t ph = (it / p.astages) & 1;
+                const int stage = astage;
+                const uint32_t ph = aph;
+                next_astage();
                 const uint32_t a_lo0 = (abuf_s + stage * p.a_stage_bytes) >> 4;
                 mbar_wait(smem_u32(&ctl->a_full[stage]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -431,8 +439,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                     for (int s = 0; s < NS; ++s) {
-                        for (int kg = 0; kg < nkg; ++kg, ++wcount) {
-                            const uint32_t ws = wcount % p.nwstages, wph = (wcount / p.nwstages) & 1;
+                        for (int kg = 0; kg < nkg; ++kg, ws = (ws + 1 == (uint32_t)p.nwstages) ? 0u : ws + 1, wph ^= (uint32_t)(ws == 0)) {
                             const int kc0 = kg * p.kgroup_chunks;
                             const int kcn = (p.nchunks - kc0) < p.kgroup_chunks ? (p.nchunks - kc0) : p.kgroup_chunks;
                             mbar_wait(smem_u32(&ctl->w_full[ws]), wph);
@@ -501,8 +508,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
         };
         const int halo_delta = g.P * g.Rp;
         const int total_sub = half < HALVES ? my_tiles * p.MT : 0;     // CB not a multiple of 32: the second half idles
+        int e_tile = tile_begin + group / p.MT, e_j = group % p.MT;     // sub-tile n = (tile, j), advanced by 2 per iteration
         for (int n = group; n < total_sub; n += 2) {
-            const int tile = tile_begin + n / p.MT, j = n % p.MT;
+            const int tile = e_tile, j = e_j;
+            e_j += 2;
+            while (e_j >= p.MT) { e_j -= p.MT; ++e_tile; }
             const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
             const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
             // which output row is this?  (fast division by the level's constant extents)
