@@ -309,8 +309,9 @@ struct Builder {
             char nm[96];
             snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : ""), w.Cin, w.Cout,
                      level_out, (w.wmma && stride == 1 && !w.transposed) ? "_mma" : (w.wgat ? "_gather" : "_simt"));
-            // FLOP = 2*MAC over output voxels as the reference executes them; bytes = fp16 in + out
-            hh->op_info.push_back({nm, 2.0 * mo * w.Cin * w.Cout * taps, 2.0 * (mi * w.Cin + mo * w.Cout)});
+            // FLOP = 2*MAC as executed: every output voxel x all taps for a (strided) conv; every INPUT voxel x all
+            // taps for a transposed conv (an output voxel of a stride-2 transposed conv receives 1/8 of the taps); bytes = fp16 in + out
+            hh->op_info.push_back({nm, 2.0 * (w.transposed ? mi : mo) * w.Cin * w.Cout * taps, 2.0 * (mi * w.Cin + mo * w.Cout)});
         }
         hh->ops.push_back([=](Run& r) {
             ConvParams p;
@@ -622,8 +623,12 @@ struct Builder {
             double m = (double)g.Z * g.P * g.R;
             char nm[96];
             snprintf(nm, sizeof(nm), "attention_L%d", level);
-            // two 32x32xn einsums + the to_out 1x1x1 conv; bytes: k read twice, v and q once, C channels written
-            hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m + 2.0 * 32 * C * m, 2.0 * m * (32 * 4 + C)});
+            // two 32x32xn einsums + the to_out 1x1x1 conv (+ the three projections the fused form recomputes).  Bytes: the fused
+            // form moves the C-channel tensor three times (x read by the context pass and by the output pass, y written) =
+            // 192 B/voxel at C = 32; the unfused form reads k twice, v and q once from the 96-channel tensor and writes C channels
+            const bool fused_form = can_fuse && !hh->no_fused_attention;
+            hh->op_info.push_back({nm, 2.0 * 2.0 * 32 * 32 * m + 2.0 * 32 * C * m + (fused_form ? 2.0 * (64 + 32) * C * m : 0.0),
+                                   fused_form ? 2.0 * m * 3 * C : 2.0 * m * (32 * 4 + C)});
         }
         // attention + to_out conv -> xn reused as the raw output (+ its GroupNorm(1,C) statistics), then GN(1) + residual x
         hh->ops.push_back([=](Run& r) {
