@@ -7,7 +7,7 @@ from calodiffusion_b200.calodiffusion import CaloDiffusion
 key = sys.argv[1] if len(sys.argv) > 1 else "ds2"
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 wl = WORKLOADS[key]
-B = wl["batch"]
+B = int(sys.argv[3]) if len(sys.argv) > 3 else wl["batch"]
 cfg = dict(wl["cfg"])
 torch.manual_seed(0)
 m = CaloDiffusion(cfg, n_steps=400, loss_type="l2", max_batch=B)
