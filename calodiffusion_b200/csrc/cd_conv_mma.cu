@@ -845,6 +845,8 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.kgroup_chunks = p.nchunks < 8 ? p.nchunks : 8;
     p.wstage_bytes = p.kgroup_chunks * p.N * 16;
     p.nwstages = 3;
+    if (const char* e = getenv("CD_MMA_WSTAGES")) { const int v = atoi(e); if (v >= 2 && v <= kMaxWStages) p.nwstages = v; }   // diagnostics
+    const int nwstages_plan = p.nwstages;
     p.nrows = (long long)cp.B * g.rows_per_sample;
     if (p.nrows + 4096 >= (1LL << 31)) return 1;
 
@@ -890,7 +892,7 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         found = accept(0, 1, mt, 2);
     }
     // 3) single-stage forms
-    p.nwstages = 3;
+    p.nwstages = nwstages_plan;
     for (int resident = 1; resident >= 0 && !found; --resident)
         for (int mt = 4; mt >= 1 && !found; --mt) {
             if (!resident && mt > p.nacc) continue;

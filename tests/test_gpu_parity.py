@@ -149,6 +149,21 @@ def test_tcgen05_conv_many_tiles_per_cta():
     assert max(errs.values()) < TOL_LAYER, errs
 
 
+def test_tcgen05_conv_two_stage_weight_ring(monkeypatch):
+    """The streamed-weight form with a 2-stage weight ring (CD_MMA_WSTAGES, read per launch).  Round 1 parked this
+    configuration after an illegal address on multi-tile CTAs; with the ring bookkeeping rewritten as counters it runs clean
+    (it is no faster than 3 stages, which stays the default) - kept under test so the protocol is exercised at both depths."""
+    monkeypatch.setenv("CD_MMA_WSTAGES", "2")
+    m, c = _model("ds2", max_batch=48)
+    lib = m._lib
+    errs = {}
+    errs["k3_l1_128_32_stream"] = _conv_case(m, lib, 1, 1, 128, 32, (3, 3, 3), (1, 1, 1), False, 0, B=48)
+    errs["k3_l1_64_64_stream"] = _conv_case(m, lib, 1, 1, 64, 64, (3, 3, 3), (1, 1, 1), False, 0, B=48)
+    errs["k3_l2_192_64_stream"] = _conv_case(m, lib, 2, 2, 192, 64, (3, 3, 3), (1, 1, 1), False, 0, B=48)
+    print({k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
 @pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
 def test_denoise_generic_backend(models, case):
     """Same golden check with the SIMT convolution everywhere (conv_backend=1)."""
