@@ -660,8 +660,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         if (!keep) h = Half8{};
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
                         if (do_store && !DBG_MODE(8)) store8(o, h);
-                        if (halo_up) store8(o + (long long)halo_delta * 8, h);
-                        if (halo_dn) store8(o - (long long)halo_delta * 8, h);
+                        if (p.write_halo) {      // uniform branch: the resblock convs (no halo copies) skip the address arithmetic too
+                            if (halo_up) store8(o + (long long)halo_delta * 8, h);
+                            if (halo_dn) store8(o - (long long)halo_delta * 8, h);
+                        }
                     }
                     if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(12, DBG_T() - tE1);
                     if (p.stats && valid && !DBG_MODE(16)) {
@@ -724,8 +726,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         if (!keep) h = Half8{};
                         __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
                         if (do_store) store8(o, h);
-                        if (halo_up) store8(o + (long long)halo_delta * 8, h);
-                        if (halo_dn) store8(o - (long long)halo_delta * 8, h);
+                        if (p.write_halo) {
+                            if (halo_up) store8(o + (long long)halo_delta * 8, h);
+                            if (halo_dn) store8(o - (long long)halo_delta * 8, h);
+                        }
                     }
                 }
             }
