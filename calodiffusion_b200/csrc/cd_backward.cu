@@ -675,27 +675,45 @@ __device__ __forceinline__ float ord2f_b(unsigned k) {
     return __uint_as_float(u);
 }
 
+__device__ __forceinline__ void ldsm_x4_n(uint32_t addr, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t pack2h(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float2 unpack2h(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+
+constexpr int kAbStr = 80;            // bytes per row of the 32-wide fp16 matrices (conflict-free ldmatrix)
+constexpr float kDcxScale = 0.0625f;
+
 // reduce pass: batches of 128 voxels; phase 1 (thread = voxel) leaves P, datt, att and dy in shared memory as fp16 chunk planes
 // ([8-channel chunk][voxel][8], the layout wgrad_mma_kernel stages), phase 2 contracts the batch on the tensor cores
 // (mma.sync m16n8k16, K = the 128 voxels): warps 0-1 dCx = P^T datt (16 d-rows each), warps 2-3 dWout = dy^T att (16-row
 // c tiles), accumulators in registers across the block's batches; one set of global atomics per block at the end.
 __global__ void __launch_bounds__(128) attn_bwd_reduce_kernel(AttnBwdParams p) {
-    extern __shared__ __align__(16) float asm_[];
-    const int b = blockIdx.y, C = p.C, ncc = C >> 3;
+    extern __shared__ __align__(16) unsigned char arsm_[];
+    const int b = blockIdx.y, C = p.C, ncc = C >> 3, KS = C >> 4, wstr = C * 2 + 16;
     const Geom& g = p.g;
-    float (*s_cx)[32] = reinterpret_cast<float (*)[32]>(asm_);                 // [32][32] broadcast reads: unpadded, float4
-    float* s_wout = asm_ + 32 * 32;                                             // [C][32]
-    __half* h_P = reinterpret_cast<__half*>(s_wout + C * 32);                   // [4][128][8]
+    unsigned char* s_cx = arsm_;                                   // Cx[d][e] fp16, rows of kAbStr bytes (B operand, k = d through .trans)
+    unsigned char* s_wt = s_cx + 32 * kAbStr;                       // Wout^T[e][c] fp16, rows of wstr bytes
+    __half* h_P = reinterpret_cast<__half*>(s_wt + 32 * wstr);      // [4][128][8]
     __half* h_datt = h_P + 4 * 128 * 8;
     __half* h_att = h_datt + 4 * 128 * 8;
-    __half* h_dy = h_att + 4 * 128 * 8;                                         // [C/8][128][8]
+    __half* h_dy = h_att + 4 * 128 * 8;                             // [C/8][128][8]
     const float* ctx = p.ctx + (long long)b * 33 * 32;
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_cx[i >> 5][i & 31] = ctx[i] / ctx[32 * 32 + (i >> 5)];
-    for (int i = threadIdx.x; i < C * 32; i += blockDim.x) s_wout[i] = p.wout[i];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+        const int d = i >> 5, e = i & 31;
+        *reinterpret_cast<__half*>(s_cx + d * kAbStr + e * 2) = __float2half_rn(ctx[i] / ctx[32 * 32 + d]);
+    }
+    for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
+        const int c = i >> 5, e = i & 31;
+        *reinterpret_cast<__half*>(s_wt + e * wstr + c * 2) = __float2half_rn(p.wout[i]);
+    }
     __syncthreads();
     const float scale = 0.17677669529663687f;   // 32^-0.5
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int mi = lane >> 3, mr = lane & 7;
+    const int mi = lane >> 3, mr = lane & 7, gq = lane >> 2, tq = lane & 3;
     float acc[4][4][4];                          // [row tile][e 8-tile][frag]: warps 0-1 use tile 0 (dCx), warps 2-3 up to 4 c tiles
 #pragma unroll
     for (int a = 0; a < 4; ++a)
@@ -708,66 +726,105 @@ __global__ void __launch_bounds__(128) attn_bwd_reduce_kernel(AttnBwdParams p) {
     const uint32_t r0 = blockIdx.x * p.rows_per_block;
     uint32_t r1 = r0 + p.rows_per_block;
     if (r1 > (uint32_t)g.rows_per_sample) r1 = g.rows_per_sample;
+    const long long srow0 = (long long)b * g.rows_per_sample;
+    const long long cs = g.chunk_stride * 8;
+    const __half* qb = p.qkv + plcp_offset(g, 0, srow0);
+    const __half* dyb = p.dy + plcp_offset(g, 0, srow0);
     for (uint32_t rem0 = r0; rem0 < r1; rem0 += 128) {
-        const uint32_t rem = rem0 + t;
-        const bool interior = rem < r1 && decode_subrow(g, rem).kind == 0;
-        const long long row = (long long)b * g.rows_per_sample + rem;
         __syncthreads();
-        if (interior) {
-            float q[32], datt[32];
-            for (int k = 0; k < 4; ++k) unpack8(load8(p.qkv + plcp_offset(g, k, row)), q + k * 8);
-            float mx = q[0];
+        // phase 1: the warp's 32 rows as two m16 tiles; P, datt = s dy Wout, att = s P Cx in accumulator layout, written to the
+        // chunk planes as half2 (rows that are not interior voxels contribute zeros)
+        {
+            const uint32_t base = rem0 + warp * 32;
+            const uint32_t rem = base + lane;
+            const unsigned vmask = __ballot_sync(0xffffffffu, rem < r1 && decode_subrow(g, rem).kind == 0);
 #pragma unroll
-            for (int d = 1; d < 32; ++d) mx = fmaxf(mx, q[d]);
-            float sum = 0.f;
+            for (int mt = 0; mt < 2; ++mt) {
+                const int lA = warp * 32 + mt * 16 + gq, lB = lA + 8;               // rows within the 128-row batch
+                const uint32_t rA = rem0 + lA, rB = rem0 + lB;
+                const bool vA = (vmask >> (mt * 16 + gq)) & 1u, vB = (vmask >> (mt * 16 + gq + 8)) & 1u;
+                const long long oA = (long long)rA * 8 + 2 * tq, oB = (long long)rB * 8 + 2 * tq;
+                float P[4][4];
 #pragma unroll
-            for (int d = 0; d < 32; ++d) { q[d] = __expf(q[d] - mx); sum += q[d]; }
-            const float inv = 1.f / sum;
+                for (int j = 0; j < 4; ++j) {
+                    const float2 a = unpack2h(vA ? __ldg(reinterpret_cast<const unsigned*>(qb + oA + j * cs)) : 0u);
+                    const float2 c = unpack2h(vB ? __ldg(reinterpret_cast<const unsigned*>(qb + oB + j * cs)) : 0u);
+                    P[j][0] = a.x; P[j][1] = a.y; P[j][2] = c.x; P[j][3] = c.y;
+                }
+                float m0 = P[0][0], m1 = P[0][2];
 #pragma unroll
-            for (int d = 0; d < 32; ++d) q[d] *= inv;                       // q holds P from here on
+                for (int j = 0; j < 4; ++j) { m0 = fmaxf(m0, fmaxf(P[j][0], P[j][1])); m1 = fmaxf(m1, fmaxf(P[j][2], P[j][3])); }
+                m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+                m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+                float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-            for (int e = 0; e < 32; ++e) datt[e] = 0.f;
-            for (int k = 0; k < ncc; ++k) {
-                const Half8 raw = load8(p.dy + plcp_offset(g, k, row));
-                store8(h_dy + ((size_t)k * 128 + t) * 8, raw);
-                float dy[8];
-                unpack8(raw, dy);
+                for (int j = 0; j < 4; ++j) {
+                    P[j][0] = __expf(P[j][0] - m0); P[j][1] = __expf(P[j][1] - m0); s0 += P[j][0] + P[j][1];
+                    P[j][2] = __expf(P[j][2] - m1); P[j][3] = __expf(P[j][3] - m1); s1 += P[j][2] + P[j][3];
+                }
+                s0 += __shfl_xor_sync(0xffffffffu, s0, 1); s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
+                s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+                const float i0 = vA ? 1.f / s0 : 0.f, i1 = vB ? 1.f / s1 : 0.f;          // P = 0 on rows that do not count
+                uint32_t pa[2][4];
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t hA = pack2h(P[j][0] * i0, P[j][1] * i0), hB = pack2h(P[j][2] * i1, P[j][3] * i1);
+                    *reinterpret_cast<unsigned*>(h_P + ((size_t)j * 128 + lA) * 8 + 2 * tq) = hA;
+                    *reinterpret_cast<unsigned*>(h_P + ((size_t)j * 128 + lB) * 8 + 2 * tq) = hB;
+                    pa[j >> 1][(j & 1) * 2] = hA; pa[j >> 1][(j & 1) * 2 + 1] = hB;       // A fragment of P for att
+                }
+                // datt = s dy Wout  (dy fragments from global, copied to the dy chunk planes on the way)
+                float dt[4][4];
 #pragma unroll
-                    for (int e4 = 0; e4 < 8; ++e4) {
-                        const float4 w = *reinterpret_cast<const float4*>(s_wout + (k * 8 + j) * 32 + e4 * 4);
-                        datt[e4 * 4] = fmaf(w.x, dy[j], datt[e4 * 4]); datt[e4 * 4 + 1] = fmaf(w.y, dy[j], datt[e4 * 4 + 1]);
-                        datt[e4 * 4 + 2] = fmaf(w.z, dy[j], datt[e4 * 4 + 2]); datt[e4 * 4 + 3] = fmaf(w.w, dy[j], datt[e4 * 4 + 3]);
+                for (int j = 0; j < 4; ++j) dt[j][0] = dt[j][1] = dt[j][2] = dt[j][3] = 0.f;
+                for (int sp = 0; sp < KS; sp += 2) {
+                    uint32_t a[2][4];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const int s = sp + u;
+                        const bool have = s < KS;
+                        a[u][0] = (have && vA) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oA + (2 * s) * cs)) : 0u;
+                        a[u][1] = (have && vB) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oB + (2 * s) * cs)) : 0u;
+                        a[u][2] = (have && vA) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oA + (2 * s + 1) * cs)) : 0u;
+                        a[u][3] = (have && vB) ? __ldg(reinterpret_cast<const unsigned*>(dyb + oB + (2 * s + 1) * cs)) : 0u;
+                        if (have) {
+                            *reinterpret_cast<unsigned*>(h_dy + ((size_t)(2 * s) * 128 + lA) * 8 + 2 * tq) = a[u][0];
+                            *reinterpret_cast<unsigned*>(h_dy + ((size_t)(2 * s) * 128 + lB) * 8 + 2 * tq) = a[u][1];
+                            *reinterpret_cast<unsigned*>(h_dy + ((size_t)(2 * s + 1) * 128 + lA) * 8 + 2 * tq) = a[u][2];
+                            *reinterpret_cast<unsigned*>(h_dy + ((size_t)(2 * s + 1) * 128 + lB) * 8 + 2 * tq) = a[u][3];
+                        }
                     }
-            }
 #pragma unroll
-            for (int e = 0; e < 32; ++e) datt[e] *= scale;
-            for (int k = 0; k < 4; ++k) {
-                store8(h_P + ((size_t)k * 128 + t) * 8, pack8(q + k * 8));
-                store8(h_datt + ((size_t)k * 128 + t) * 8, pack8(datt + k * 8));
-            }
-#pragma unroll
-            for (int e = 0; e < 32; ++e) datt[e] = 0.f;                      // reuse as the att accumulator
-#pragma unroll
-            for (int d = 0; d < 32; ++d)
-#pragma unroll
-                for (int e4 = 0; e4 < 8; ++e4) {
-                    const float4 w = *reinterpret_cast<const float4*>(&s_cx[d][e4 * 4]);
-                    datt[e4 * 4] = fmaf(w.x, q[d], datt[e4 * 4]); datt[e4 * 4 + 1] = fmaf(w.y, q[d], datt[e4 * 4 + 1]);
-                    datt[e4 * 4 + 2] = fmaf(w.z, q[d], datt[e4 * 4 + 2]); datt[e4 * 4 + 3] = fmaf(w.w, q[d], datt[e4 * 4 + 3]);
+                    for (int j = 0; j < 4; ++j) {
+                        uint32_t bw[4];
+                        ldsm_x4_n(smem_u32(s_wt) + (j * 8 + (lane & 7)) * wstr + sp * 32 + (lane >> 3) * 16, bw);
+                        mma16816(dt[j], a[0], bw[0], bw[1]);
+                        if (sp + 1 < KS) mma16816(dt[j], a[1], bw[2], bw[3]);
+                    }
                 }
 #pragma unroll
-            for (int e = 0; e < 32; ++e) datt[e] *= scale;
-            for (int k = 0; k < 4; ++k) store8(h_att + ((size_t)k * 128 + t) * 8, pack8(datt + k * 8));
-        } else {
-            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-            for (int k = 0; k < 4; ++k) {
-                *reinterpret_cast<uint4*>(h_P + ((size_t)k * 128 + t) * 8) = z;
-                *reinterpret_cast<uint4*>(h_datt + ((size_t)k * 128 + t) * 8) = z;
-                *reinterpret_cast<uint4*>(h_att + ((size_t)k * 128 + t) * 8) = z;
+                for (int j = 0; j < 4; ++j) {
+                    *reinterpret_cast<unsigned*>(h_datt + ((size_t)j * 128 + lA) * 8 + 2 * tq) = pack2h(dt[j][0] * scale, dt[j][1] * scale);
+                    *reinterpret_cast<unsigned*>(h_datt + ((size_t)j * 128 + lB) * 8 + 2 * tq) = pack2h(dt[j][2] * scale, dt[j][3] * scale);
+                }
+                // att = s P Cx : A = P (k = d), B[k = d][n = e] = Cx[d][e] through ldmatrix.trans
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dt[j][0] = dt[j][1] = dt[j][2] = dt[j][3] = 0.f;
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                    for (int jj = 0; jj < 2; ++jj) {
+                        uint32_t bt[4];
+                        ldsm_x4_t(smem_u32(s_cx) + (ks * 16 + (mi & 1) * 8 + mr) * kAbStr + (2 * jj + (mi >> 1)) * 16, bt);
+                        mma16816(dt[2 * jj], pa[ks], bt[0], bt[1]);
+                        mma16816(dt[2 * jj + 1], pa[ks], bt[2], bt[3]);
+                    }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    *reinterpret_cast<unsigned*>(h_att + ((size_t)j * 128 + lA) * 8 + 2 * tq) = pack2h(dt[j][0] * scale, dt[j][1] * scale);
+                    *reinterpret_cast<unsigned*>(h_att + ((size_t)j * 128 + lB) * 8 + 2 * tq) = pack2h(dt[j][2] * scale, dt[j][3] * scale);
+                }
             }
-            for (int k = 0; k < ncc; ++k) *reinterpret_cast<uint4*>(h_dy + ((size_t)k * 128 + t) * 8) = z;
         }
         __syncthreads();
         // phase 2: A = (P | dy)^T through ldmatrix.trans on the chunk planes, B = (datt | att) likewise (as wgrad_mma_kernel)
@@ -802,7 +859,6 @@ __global__ void __launch_bounds__(128) attn_bwd_reduce_kernel(AttnBwdParams p) {
             a_db += sdb;
         }
     }
-    const int gq = lane >> 2, tq = lane & 3;
     const int ntile = warp < 2 ? 1 : (nct - (warp - 2) + 1) / 2;
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
@@ -947,17 +1003,6 @@ __global__ void __launch_bounds__(128) attn_bwd_apply_kernel(AttnBwdParams p) {
 // 8-channel fragment is 128 contiguous bytes); the small matrices sit in shared memory as fp16 B operands (dCx scaled by
 // 1/16 to stay well inside fp16 range).  Halo / guard rows of dqkv are written as zeros (whole 32-byte sectors).
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void ldsm_x4_n(uint32_t addr, uint32_t* r) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ uint32_t pack2h(float a, float b) {
-    __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
-__device__ __forceinline__ float2 unpack2h(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
-
-constexpr int kAbStr = 80;            // bytes per row of the 32-wide fp16 matrices (conflict-free ldmatrix)
-constexpr float kDcxScale = 0.0625f;
 
 __global__ void __launch_bounds__(128) attn_bwd_apply_mma_kernel(AttnBwdParams p) {
     extern __shared__ __align__(16) unsigned char abs_[];
@@ -1440,7 +1485,7 @@ int launch_attn_backward(AttnBwdParams p, int B, cudaStream_t st) {
     p.rows_per_block = 2048;
     dim3 grid((p.g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);
     if (p.C % 16) return 1;
-    const size_t smem = ((size_t)32 * 32 + (size_t)p.C * 32) * sizeof(float) + ((size_t)3 * 4 + p.C / 8) * 128 * 8 * sizeof(__half);
+    const size_t smem = (size_t)32 * kAbStr + (size_t)32 * (p.C * 2 + 16) + ((size_t)3 * 4 + p.C / 8) * 128 * 8 * sizeof(__half);
     static size_t configured = 0;
     if (smem > configured) {
         if (cudaFuncSetAttribute(attn_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;
