@@ -366,19 +366,41 @@ void launch_gn_apply(const Geom& g, const __half* src, const double* stats, cons
 // time input = do_time_embed(sigma) (calodiffusion.py:144-155).
 // =================================================================================================
 // out[o] = act(bias[o] + sum_i W[o][i] in[i]): one warp per output row so the weight reads are coalesced
+// The kernel is a chain of small matrix-vector products, one block per shower: what it costs is the number of dependent
+// global-load round trips, so a warp works on FOUR output rows at a time (four independent load streams and reductions).
+__device__ __forceinline__ void warp_rows4(const float* __restrict__ W, const float* in, int n_in, int n_out, int o0, int stride,
+                                           float (&a)[4]) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] = 0.f;
+    for (int i = lane; i < n_in; i += 32) {
+        const float x = in[i];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int o = o0 + u * stride;
+            if (o < n_out) a[u] = fmaf(__ldg(W + (long long)o * n_in + i), x, a[u]);
+        }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) a[u] += __shfl_xor_sync(0xffffffffu, a[u], s);
+}
 __device__ void dense_layer(const float* __restrict__ W, const float* __restrict__ bias, const float* in, float* out,
                             int n_in, int n_out, int act) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    for (int o = warp; o < n_out; o += nwarps) {
-        const float* w = W + (long long)o * n_in;
-        float a = 0.f;
-        for (int i = lane; i < n_in; i += 32) a = fmaf(__ldg(w + i), in[i], a);
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) a += __shfl_xor_sync(0xffffffffu, a, s);
+    for (int o0 = warp; o0 < n_out; o0 += 4 * nwarps) {
+        float a[4];
+        warp_rows4(W, in, n_in, n_out, o0, nwarps, a);
         if (lane == 0) {
-            a += bias ? bias[o] : 0.f;
-            if (act == 1) a = gelu_erf(a);
-            out[o] = a;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int o = o0 + u * nwarps;
+                if (o >= n_out) break;
+                float v = a[u] + (bias ? bias[o] : 0.f);
+                if (act == 1) v = gelu_erf(v);
+                out[o] = v;
+            }
         }
     }
     __syncthreads();
@@ -411,13 +433,16 @@ __global__ void __launch_bounds__(256) embed_kernel(EmbedParams p, const float* 
         const float* bias = p.pb[k];
         const int C = p.pC[k];
         float* out = addvec + (long long)b * p.addvec_stride + p.poff[k];
-        for (int o = warp; o < C; o += nwarps) {
-            const float* w = W + (long long)o * p.cond_dim;
-            float a = 0.f;
-            for (int i = lane; i < p.cond_dim; i += 32) a = fmaf(__ldg(w + i), cvec[i], a);
+        for (int o0 = warp; o0 < C; o0 += 4 * nwarps) {
+            float a[4];
+            warp_rows4(W, cvec, p.cond_dim, C, o0, nwarps, a);
+            if (lane == 0) {
 #pragma unroll
-            for (int s = 16; s > 0; s >>= 1) a += __shfl_xor_sync(0xffffffffu, a, s);
-            if (lane == 0) out[o] = a + bias[o];
+                for (int u = 0; u < 4; ++u) {
+                    const int o = o0 + u * nwarps;
+                    if (o < C) out[o] = a[u] + bias[o];
+                }
+            }
         }
     }
 }
