@@ -144,10 +144,14 @@ def config_block(wl, B, steps, world, strong=False):
                 "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards of ONE batch, final all_gather)",
                 "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
                 "weights": "random init (seed 0)"}
-    return {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
-            "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
-            "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
-            "weights": "random init (seed 0)"}
+    cfg = {"workload": wl["name"], "batch_per_gpu": B, "sampler": wl["sampler"], "sampling_steps": steps,
+           "denoiser_evals_per_shower": evals, "parallelism": f"dp{world} (event-batch shards, final all_gather)",
+           "l2": "working set per evaluation (GBs of activations) exceeds the 126 MB L2; no explicit flush",
+           "weights": "random init (seed 0)"}
+    if wl["sampler"] == "Heun":   # same key on both arms (the driver compares the blocks)
+        cfg["sampler_note"] = ("the B200 arm takes the last step (t_next = 0) as an Euler step (SAMPLER_OPTIONS LAST_STEP_EULER: finite "
+                               "showers); the unmodified reference divides by zero there - same number of denoiser evaluations")
+    return cfg
 
 
 def reference_leg(key, budget_s=10.0, batch=None):
