@@ -150,7 +150,7 @@ def config_block(wl, B, steps, world, strong=False):
            "weights": "random init (seed 0)"}
     if wl["sampler"] == "Heun":   # same key on both arms (the driver compares the blocks)
         cfg["sampler_note"] = ("the B200 arm takes the last step (t_next = 0) as an Euler step (SAMPLER_OPTIONS LAST_STEP_EULER: finite "
-                               "showers); the unmodified reference divides by zero there - same number of denoiser evaluations")
+                               "showers, 2*steps - 1 evaluations); the unmodified reference divides by zero there (2*steps evaluations)")
     return cfg
 
 
