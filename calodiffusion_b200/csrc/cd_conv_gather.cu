@@ -13,6 +13,7 @@
 // halo copies) into the output PLCP tensor.
 #include <cuda.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "cd_kernels.cuh"
@@ -105,6 +106,18 @@ __device__ __forceinline__ void g_umma_f16(uint32_t tmem_d, uint64_t adesc, uint
         "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
 }
+// warp-convergent forms (every lane executes the call, one elected lane performs the operation): with the issue loop walked by
+// all 32 lanes the descriptor arithmetic stays in the uniform datapath; issued from divergent single-lane code every MMA costs a
+// ~20-instruction R2UR waterfall (measured in cd_conv_mma.cu: 164 clk per MMA against a 44-56 clk tensor-pipe slot)
+__device__ __forceinline__ void g_umma_f16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n.reg .pred p, e;\nelect.sync _|e, 0xffffffff;\nsetp.ne.b32 p, %4, 0;\n@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void g_umma_commit_elect(uint32_t bar) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}"
+                 ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void g_umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -180,12 +193,11 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
     if (warp == 0) {
         // ===================== weight taps: cp.async.bulk into the stage ring =====================
         if (lane == 0) {
-            uint32_t n = 0;
+            uint32_t slot = 0, ph = 0;
             for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
                 const GClass& c = p.cls[find_class(p, tile)];
                 const int nst = (c.ntaps + G - 1) / G;
-                for (int st = 0; st < nst; ++st, ++n) {
-                    const uint32_t slot = n % p.nstages, ph = (n / p.nstages) & 1;
+                for (int st = 0; st < nst; ++st, slot = (slot + 1 == (uint32_t)p.nstages) ? 0u : slot + 1, ph ^= (uint32_t)(slot == 0)) {
                     const int t0 = st * G;
                     const int nt = c.ntaps - t0 < G ? c.ntaps - t0 : G;
                     g_mbar_wait(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
@@ -198,9 +210,9 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            uint32_t n = 0, tcount = 0;
+        // ===================== MMA issuer (all lanes walk the loop, the elected lane issues) =====================
+        {
+            uint32_t slot = 0, ph = 0, tcount = 0;              // stage ring position as counters (no runtime % and /)
             const uint64_t adesc_hi = g_make_desc(0, 2048u, 128u);
             const uint64_t bdesc_hi = g_make_desc(0, (uint32_t)N * 16u, 128u);
             const uint32_t bstep = (2u * N * 16u) >> 4;
@@ -212,8 +224,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                 g_mbar_wait(g_smem_u32(&ctl->t_empty[acc]), aph ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 uint32_t accum = 0;
-                for (int st = 0; st < nst; ++st, ++n) {
-                    const uint32_t slot = n % p.nstages, ph = (n / p.nstages) & 1;
+                for (int st = 0; st < nst; ++st) {
                     const int t0 = st * G;
                     const int nt = c.ntaps - t0 < G ? c.ntaps - t0 : G;
                     g_mbar_wait(g_smem_u32(&ctl->full[slot]), ph);
@@ -222,12 +233,14 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint32_t al = (abuf_s + slot * p.a_stage_bytes) >> 4, bl = (wbuf_s + slot * p.w_stage_bytes) >> 4;
                     for (int e = 0; e < nt * (NCH / 2); ++e, al += 256u, bl += bstep) {   // stage layouts are contiguous in (tap, k16)
-                        g_umma_f16(dcol, adesc_hi | al, bdesc_hi | bl, p.idesc, accum);
+                        g_umma_f16_elect(dcol, adesc_hi | al, bdesc_hi | bl, p.idesc, accum);
                         accum = 1;
                     }
-                    g_umma_commit(g_smem_u32(&ctl->empty[slot]));
+                    g_umma_commit_elect(g_smem_u32(&ctl->empty[slot]));
+                    slot = (slot + 1 == (uint32_t)p.nstages) ? 0u : slot + 1;
+                    ph ^= (uint32_t)(slot == 0);
                 }
-                g_umma_commit(g_smem_u32(&ctl->t_full[acc]));
+                g_umma_commit_elect(g_smem_u32(&ctl->t_full[acc]));
             }
         }
     } else if (warp < 6) {
@@ -280,7 +293,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
         // ===================== gather producers: two groups of 128 threads alternate stages =====================
         const int pg = (warp - 6) >> 2;
         const int i = ((warp - 6) & 3) * 32 + lane;
-        uint32_t n = 0;
+        uint32_t n = 0, rslot = 0, rph = 0;          // stage counter and its ring position (counters: no runtime % and /)
         for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
             const GClass& c = p.cls[find_class(p, tile)];
             const int nst = (c.ntaps + G - 1) / G;
@@ -292,9 +305,9 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
             const uint4* bp0 = reinterpret_cast<const uint4*>(p.src + plcp_offset(p.gin, 0, 0));   // always-valid address for zero fills
             const int wrap = p.gin.P * p.gin.Rp;
             const long long cs = p.gin.chunk_stride;     // uint4 units between chunk planes
-            for (int st = 0; st < nst; ++st, ++n) {
+            for (int st = 0; st < nst; ++st, ++n, rslot = (rslot + 1 == (uint32_t)p.nstages) ? 0u : rslot + 1, rph ^= (uint32_t)(rslot == 0)) {
                 if ((int)(n & 1) != pg) continue;
-                const uint32_t slot = n % p.nstages, ph = (n / p.nstages) & 1;
+                const uint32_t slot = rslot, ph = rph;
                 const int t0 = st * G;
                 // asynchronous 16-byte gathers straight into the operand tile (zero-filled when the tap falls in the zero
                 // padding): nothing is staged in registers, so a thread keeps as many stages in flight as the ring is deep
@@ -477,6 +490,11 @@ int launch_conv_gather(const ConvParams& cp, const __half* packed_w, cudaStream_
     p.w_stage_bytes = p.G * p.w_tap_bytes;
     int stages = (max_smem - kGCtlBytes - 256) / (p.a_stage_bytes + p.w_stage_bytes);
     if (stages > kGMaxStages) stages = kGMaxStages;
+    // The strided conv fetches every input piece ~6 times (once per (output, tap) pair that reads it) with cp.async.ca: a ring of
+    // 4 stages instead of 6 leaves ~70 KB more of the SM's L1 for those repeats (DS2 L0->L1: 0.489 -> 0.296 ms, DS3 0.644 -> 0.552;
+    // 5 stages: no gain - the shared-memory carve-out moves in steps; the transposed form is neutral to slightly faster)
+    if (stages > 4) stages = 4;
+    if (const char* e = getenv("CD_GATHER_STAGES")) { const int v = atoi(e); if (v >= 2 && v < stages) stages = v; }   // diagnostics
     if (stages < 2) return 1;
     p.nstages = stages;
     const size_t smem = kGCtlBytes + (size_t)stages * (p.a_stage_bytes + p.w_stage_bytes) + 128;
