@@ -51,7 +51,9 @@ def test_gradients_match_oracle(case):
     # measured on B200: ds2 total 2.5e-3, worst tensor 6.1e-3; ds3 total 3.4e-4, worst 2.2e-3; loss 5e-5
     assert e_loss < 5e-4
     assert total < (6e-3 if case == "ds2" else 1.5e-3)
-    assert max(errs.values()) < 1e-2, worst
+    # worst single tensor over ten runs of this round: 6.1e-3 ... 7.7e-3 (ds2, a 32-element bias deep in the network; the
+    # accumulation order of the atomics varies run to run), 2.4e-3 (ds3): gate at 2x the largest measured
+    assert max(errs.values()) < 1.5e-2, worst
 
 
 def test_fused_adam_matches_torch_adam():
