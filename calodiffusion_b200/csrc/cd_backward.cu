@@ -167,7 +167,9 @@ __global__ void __launch_bounds__(kGbThreads) gn_bwd_reduce_kernel(GnBwdParams p
     }
     // lanes of one chunk plane are contiguous (tpc is 8, 16, 32, 64 ...): butterfly over min(32, tpc) lanes, then one lane per
     // group adds to the block's accumulators (all lanes take part in the shuffles, also those with k >= nch)
-    const int span = tpc < 32 ? tpc : 32;
+    // (a width whose chunk count does not divide the block - 96 channels: 21 threads per plane - has no lane-aligned groups:
+    //  span 1, every thread adds its own partial sums)
+    const int span = (tpc & (tpc - 1)) != 0 ? 1 : (tpc < 32 ? tpc : 32);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         float a = A[j], bsum = Bc[j], d = D[j], x = X[j];
@@ -1415,7 +1417,7 @@ void launch_loss_backward(const LossBwdParams& p, int B, cudaStream_t st) {
 void launch_gn_backward(GnBwdParams p, int B, cudaStream_t st) {
     const Geom& g = p.g;
     const int nch = p.C >> 3;
-    if (kGbThreads % nch != 0 || p.C > kBwdMaxC) return;     // checked by the caller (C in {16,32,64,96,128})
+    if (nch < 1 || nch > kGbThreads / 8 || p.C > kBwdMaxC) return;     // checked by the caller
     gn_bwd_prep_kernel<<<B, 128, 0, st>>>(p);
     p.rows_per_block = 1024;     // 2048 left the last of 5 blocks per DS2 sample with 88 rows and one ragged wave (ncu: 30 % warps active)
     dim3 grid1((g.rows_per_sample + p.rows_per_block - 1) / p.rows_per_block, B);

@@ -90,7 +90,7 @@ static int train_setup(cd_unet* h) {
     int gmax = 1;
     for (TapeOp& t : h->tape) {
         if (t.kind == 1) {
-            if (t.C > kBwdMaxC || 256 % (t.C / 8) != 0) return fail("training: GroupNorm over %d channels is not supported", t.C);
+            if (t.C > kBwdMaxC || t.C % 8) return fail("training: GroupNorm over %d channels is not supported", t.C);
             if (t.groups > gmax) gmax = t.groups;
         }
         if (t.kind != 0) continue;

@@ -29,7 +29,7 @@ def _oracle(c, E, layers, data, noise, rnd, time):
     return loss_and_grads(c["cfg"], c["sd"], data, E, layers, noise, sigma_for(c["cfg"], rnd, time))
 
 
-@pytest.mark.parametrize("case", ["ds2", "ds3"])
+@pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
 def test_gradients_match_oracle(case):
     m, c = _model(case)
     E, layers, data, noise, rnd, time = train_inputs(c["shape"], 2, c["meta"]["cond_e"], c["meta"]["cond_layers"])
@@ -48,9 +48,10 @@ def test_gradients_match_oracle(case):
                    np.concatenate([grads_ref["model." + n].numpy().ravel() for n, _ in m.model.named_parameters()]))
     print(f"{case}: loss rel.err {e_loss:.2e}; all-parameter gradient rel-L2 {total:.2e}; worst tensors: " +
           ", ".join(f"{k} {v:.2e}" for k, v in worst))
-    # measured on B200: ds2 total 2.5e-3, worst tensor 6.1e-3; ds3 total 3.4e-4, worst 2.2e-3; loss 5e-5
+    # measured on B200: ds2 total 2.5e-3, worst tensor 6.1e-3; ds3 total 3.4e-4, worst 2.2e-3; hgcal shape (96-channel level,
+    # PHI_INPUT, 32 conditioning inputs) total 4.7e-4, worst 3.4e-3; loss 5e-5 (hgcal 1.3e-4)
     assert e_loss < 5e-4
-    assert total < (6e-3 if case == "ds2" else 1.5e-3)
+    assert total < {"ds2": 6e-3, "ds3": 1.5e-3, "hgcal": 1.5e-3}[case]      # measured 2.6e-3 / 3.4e-4 / 4.7e-4
     # worst single tensor over ten runs of this round: 6.1e-3 ... 7.7e-3 (ds2, a 32-element bias deep in the network; the
     # accumulation order of the atomics varies run to run), 2.4e-3 (ds3): gate at 2x the largest measured
     assert max(errs.values()) < 1.5e-2, worst
