@@ -81,6 +81,16 @@ __device__ __forceinline__ void g_mbar_wait(uint32_t bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000LL) { printf("cd_conv_gather: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
     }
 }
+// waits of the warps that are not on the MMA issue path (weights, gather producers, epilogue): back off between polls.  The
+// tight form costs ~10 instructions per poll on every lane; ncu showed a third of this kernel's issue slots going to such loops.
+__device__ __forceinline__ void g_mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+    if (g_mbar_try(bar, parity)) return;
+    long long t0 = clock64();
+    while (!g_mbar_try(bar, parity)) {
+        __nanosleep(64);
+        if (clock64() - t0 > 4000000000LL) { printf("cd_conv_gather: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
+    }
+}
 __device__ __forceinline__ void g_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
@@ -200,7 +210,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                 for (int st = 0; st < nst; ++st, slot = (slot + 1 == (uint32_t)p.nstages) ? 0u : slot + 1, ph ^= (uint32_t)(slot == 0)) {
                     const int t0 = st * G;
                     const int nt = c.ntaps - t0 < G ? c.ntaps - t0 : G;
-                    g_mbar_wait(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
+                    g_mbar_wait_relaxed(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
                     g_mbar_expect_tx(g_smem_u32(&ctl->full[slot]), (uint32_t)nt * p.w_tap_bytes);
                     for (int gi = 0; gi < nt; ++gi)
                         g_bulk_g2s(wbuf_s + slot * p.w_stage_bytes + gi * p.w_tap_bytes,
@@ -261,7 +271,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
             // P == 1: p = 0 is both edges; the single phi row mirrors to both halo rows
             const long long mirror2 = (p.write_halo && p.gout.P == 1) ? row - (long long)p.gout.Rp : -1;
             const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
-            g_mbar_wait(g_smem_u32(&ctl->t_full[acc]), aph);
+            g_mbar_wait_relaxed(g_smem_u32(&ctl->t_full[acc]), aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * 256;
             const bool ok2 = rc.ok && p.pair_r && (ro + 1 < p.gout.R);     // second voxel of the pair exists (odd R: last one does not)
@@ -311,7 +321,7 @@ __global__ void __launch_bounds__(kGThreads, 1) conv_gather_kernel(const __grid_
                 const int t0 = st * G;
                 // asynchronous 16-byte gathers straight into the operand tile (zero-filled when the tap falls in the zero
                 // padding): nothing is staged in registers, so a thread keeps as many stages in flight as the ring is deep
-                g_mbar_wait(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
+                g_mbar_wait_relaxed(g_smem_u32(&ctl->empty[slot]), ph ^ 1);
                 const uint32_t dst_s = abuf_s + slot * p.a_stage_bytes + (uint32_t)i * 16u;
 #pragma unroll
                 for (int gi = 0; gi < G; ++gi) {
