@@ -134,6 +134,9 @@ struct ConvParams {
     // Optional C_out-channel PLCP tensor added to the result before rounding / statistics (3x3x3 tcgen05 form only): lets a
     // convolution over a wide concatenated input run as two resident-weight convolutions, the second accumulating onto the first.
     const __half* addsrc = nullptr;
+    // channels per sample of the statistics array when this launch produces only a slice of the output channels (a 64 -> 64 conv
+    // run as two 64 -> 32 halves: `dst`, `bias` and `stats` point at the slice, the per-sample stride stays the full width); 0: Cout
+    int stats_C = 0;
     int B;
 };
 

@@ -72,6 +72,7 @@ struct MmaParams {
     const float* bias;
     __half* dst;
     double* stats;
+    int stats_C;            // channels per sample of the statistics array (>= Cout: this launch may produce a channel slice)
     int Cout, CB, ncb;      // output channels, channels per block, blocks
     int N;                  // GEMM N = 3*CB (3x3x3) or CB (1x1x1)
     int nshift;             // 9 or 1
@@ -498,7 +499,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) { s_tot += __shfl_xor_sync(0xffffffffu, s_tot, o); q_tot += __shfl_xor_sync(0xffffffffu, q_tot, o); }
                     if (lane == 0) {
-                        double* d = p.stats + ((long long)cur_b * p.Cout + cb * CB + half * CH + i * CPG) * 2;
+                        double* d = p.stats + ((long long)cur_b * p.stats_C + cb * CB + half * CH + i * CPG) * 2;
                         atomicAdd(d, (double)s_tot);
                         atomicAdd(d + 1, (double)q_tot);
                     }
@@ -674,7 +675,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             // the warp's 32 rows straddle two samples (once per sample boundary): direct atomics
 #pragma unroll
                             for (int k = 0; k < W; ++k) {
-                                double* d = p.stats + ((long long)sample * p.Cout + cb * CB + ((c0 + k) / CPG) * CPG) * 2;
+                                double* d = p.stats + ((long long)sample * p.stats_C + cb * CB + ((c0 + k) / CPG) * CPG) * 2;
                                 atomicAdd(d, (double)acc[k]);
                                 atomicAdd(d + 1, (double)(acc[k] * acc[k]));
                             }
@@ -826,6 +827,7 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.pn_stats = cp.pn_stats; p.pn_wsum = cp.pn_wsum; p.pn_wb = cp.pn_wb; p.pn_C = cp.pn_C;
     p.pn_inv_count = cp.pn_stats ? (float)(1.0 / cp.pn_count) : 0.f;
     p.Cout = cp.Cout; p.CB = pick_cb(cp.Cout, taps); p.ncb = cp.Cout / p.CB;
+    p.stats_C = cp.stats_C > 0 ? cp.stats_C : cp.Cout;
     // statistics are accumulated per GroupNorm group: the group size must match an instantiated (CB, CPG) pair
     int cpg = 0;
     if (k3) {
@@ -833,7 +835,7 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         cpg = def_cpg[p.CB / 16 - 1];
         if (cp.stats) {
             cpg = cp.stats_cpg;
-            const bool ok = (p.CB == 16 && cpg == 2) || (p.CB == 32 && cpg == 4) || (p.CB == 48 && (cpg == 6 || cpg == 12)) ||
+            const bool ok = (p.CB == 16 && cpg == 2) || (p.CB == 32 && (cpg == 4 || cpg == 8)) || (p.CB == 48 && (cpg == 6 || cpg == 12)) ||
                             (p.CB == 64 && (cpg == 8 || cpg == 16));
             if (!ok) return 1;
         }
@@ -921,6 +923,7 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         switch (p.CB * 100 + cpg) {
             case 1602: e = launch_inst<16, true, 2>(p, grid, smem_total, max_smem, st); break;
             case 3204: e = launch_inst<32, true, 4>(p, grid, smem_total, max_smem, st); break;
+            case 3208: e = launch_inst<32, true, 8>(p, grid, smem_total, max_smem, st); break;   // a 32-channel half of a 64-channel conv (8 per group)
             case 4806: e = launch_inst<48, true, 6>(p, grid, smem_total, max_smem, st); break;
             case 4812: e = launch_inst<48, true, 12>(p, grid, smem_total, max_smem, st); break;
             case 6408: e = launch_inst<64, true, 8>(p, grid, smem_total, max_smem, st); break;

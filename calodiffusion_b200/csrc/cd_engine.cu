@@ -43,6 +43,9 @@ struct ConvW {
     float* bias = nullptr;   // [co]
     __half* wmma = nullptr;  // fp16 blocks for the R-stacked tcgen05 kernel (stride-1 3x3x3 / 1x1x1 convs)
     __half* wgat = nullptr;  // fp16 [tap][kc][co][8] for the gather tcgen05 kernel (strided / transposed / thin-input convs)
+    // 64 -> 64 stride-1 3x3x3 conv as two 64 -> 32 halves (output channels 0-31 / 32-63): each half's 110 KB of weights stays
+    // resident in shared memory (K-staged form, 0.62 of peak) where the full 221 KB has to stream through the weight ring (0.39)
+    __half* wmma_lo = nullptr; __half* wmma_hi = nullptr; float* bias_hi = nullptr;
     int Cin = 0, Cout = 0, kz = 1, kp = 1, kr = 1;
     int transposed = 0;
 };
@@ -248,6 +251,23 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
+    // output-channel halves of a 64 -> 64 conv (see ConvW): not in training (the weight layouts are re-derived on the device there)
+    if (want_mma && !transposed && !h->train && taps == 27 && Cin_pad == 64 && Cout == 64 && out->wmma && out->bias &&
+        mma_conv_supported(Cin_pad, Cout / 2, taps) && !getenv("CD_NO_OSPLIT")) {
+        const int half = Cout / 2;
+        std::vector<float> ph((size_t)taps * Cin_pad * half);
+        std::vector<__half> hp(mma_packed_elems(Cin_pad, half, taps));
+        __half** dstp[2] = {&out->wmma_lo, &out->wmma_hi};
+        for (int part = 0; part < 2; ++part) {
+            for (size_t r = 0; r < (size_t)taps * Cin_pad; ++r)
+                for (int co = 0; co < half; ++co) ph[r * half + co] = pk[r * Cout + part * half + co];
+            mma_pack_weights(ph.data(), Cin_pad, half, taps, hp.data());
+            *dstp[part] = h->dalloc<__half>(hp.size(), false);
+            if (*dstp[part]) cudaMemcpy(*dstp[part], hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
+        }
+        out->bias_hi = out->bias + half;
+        if (!out->wmma_lo || !out->wmma_hi) { out->wmma_lo = out->wmma_hi = nullptr; }
+    }
     if (want_gather && gather_conv_supported(Cin_pad, Cout) && taps <= 64) {   // (training re-derives it on the device: repack modes 4 / 5)
         const bool pairT = transposed && kr == 4;     // transposed convs use the merged output-pair taps
         std::vector<__half> hp(pairT ? gather_packed_elems_pairT(Cin_pad, Cout, kz, kp) : gather_packed_elems(Cin_pad, Cout, taps));
@@ -334,6 +354,21 @@ struct Builder {
             p.pn_stats = nullptr; p.pn_wsum = nullptr; p.pn_wb = nullptr; p.pn_C = 0; p.pn_count = 1.0;
             p.B = r.B;
             hh->launches += 1;
+            // (measured: DS2 L1 at B = 1000, 1.2 M rows, 0.287 -> 0.263 ms; neutral at 0.3 M rows; slower on the 30 k rows of
+            //  the HGCal L2 level at B = 128, where the second launch's set-up is not amortised)
+            if (hh->conv_backend == 0 && w.wmma_lo && w.wmma_hi && stride == 1 && !w.transposed && p.nsrc == 1 &&
+                (long long)r.B * p.gout.rows_per_sample >= 500000) {
+                ConvParams lo = p, hi = p;
+                const int half = w.Cout / 2;
+                lo.Cout = hi.Cout = half; lo.stats_C = hi.stats_C = w.Cout;
+                hi.dst = p.dst + (long long)(half / 8) * p.gout.chunk_stride * 8;
+                hi.bias = w.bias_hi;
+                hi.stats = p.stats ? p.stats + (size_t)half * 2 : nullptr;
+                if (launch_conv_mma(lo, w.wmma_lo, r.st) == 0) {
+                    if (launch_conv_mma(hi, w.wmma_hi, r.st) == 0) { hh->launches += 1; return; }
+                    // (the first half is overwritten by whichever full-width form runs below)
+                }
+            }
             if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed) {
                 if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
             }
