@@ -489,9 +489,10 @@ struct Builder {
         bool split = false;
         // (criterion: resident weights + two activation windows of the full input width exceed what one CTA can hold, so the
         //  single conv would stream its weights or stage K in many small groups; measured on DS2 L1 128->32 and DS3 L0 64->32)
-        const Geom& gl = h->geom[level];
-        const size_t win_bytes = (size_t)(128 + 2 * (gl.Pp * gl.Rp + gl.Rp + 1)) * Cin * 2;
-        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 + 2 * win_bytes > (size_t)300 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT") && !h->train) {
+        // Round 2 re-measured the 64 -> 32 case after the ring bookkeeping rework: the single K-staged conv (110 KB of resident
+        // weights, K in four groups) is now the faster form (DS3 L0 1.39 vs 1.46-1.51 ms, HGCal L0 0.153 vs 0.176 ms), so the
+        // split is kept for inputs whose weights cannot stay resident at all (27*Cin*Cout fp16 > 160 KB: 128 -> 32 and wider).
+        if (srcs.size() == 2 && (size_t)27 * Cin * Cout * 2 > (size_t)160 * 1024 && c1.wmma && !getenv("CD_NO_SPLIT") && !h->train) {
             const int Ca = h->bufs[srcs[0]].C, Cb = h->bufs[srcs[1]].C;
             const HostTensor* wfull = find_w(h, pre + "block1.proj.conv.weight");
             if (wfull && Ca + Cb == Cin && mma_conv_supported(Ca, Cout, 27) && mma_conv_supported(Cb, Cout, 27)) {
