@@ -53,12 +53,25 @@ __device__ long long g_mma_dbg[16];
 namespace {
 
 #ifndef CD_EPI_SPLIT
-#define CD_EPI_SPLIT 1                          // 1: split a block's channels over two sets of epilogue warps
+#define CD_EPI_SPLIT 0                          // 1: split a block's channels over two sets of epilogue warps (measured slower than a third group, see below)
 #endif
-constexpr int kEpiWarps = CD_EPI_SPLIT ? 16 : 8;   // 2 groups x (1 or 2 channel halves) x 4 lane quarters
-constexpr int kIssuers = 2;                     // MMA-issuing warps (one elected thread each), alternating sub-tiles
-constexpr int kFirstEpiWarp = 1 + kIssuers;
-constexpr int kThreads = 32 * (kFirstEpiWarp + kEpiWarps);   // warp 0: loads, warps 1-2: MMA issue (warp 1 owns TMEM), warps 3..18: epilogue
+#ifndef CD_EPI_GROUPS
+#define CD_EPI_GROUPS 3                         // epilogue groups (sub-tiles in flight) of the narrow 3x3x3 forms: 2, 3 or 4
+#endif
+#ifndef CD_EPI_CW3
+#define CD_EPI_CW3 16                           // channels per epilogue pass of the three-group form (8: fewer live registers)
+#endif
+// Epilogue groups take sub-tiles round-robin.  A sub-tile's epilogue is a ~4000 clk dependent chain against ~1000 clk of MMAs
+// (N = 96), so the narrow 3x3x3 forms run three groups (27 warps, 72 registers per thread); N = 192 has two accumulator slots
+// and the 1x1x1 form is HBM-bound: two groups.
+template <int CB, bool K3> __host__ __device__ constexpr int kGroups() { return (K3 && CB <= 48) ? CD_EPI_GROUPS : 2; }
+template <int CB, bool K3> __host__ __device__ constexpr int kEpiWarps() { return kGroups<CB, K3>() * (CD_EPI_SPLIT ? 8 : 4); }   // groups x (1 or 2 channel halves) x 4 lane quarters
+// Sub-tile n belongs to class n % G: issued by MMA warp 1 + n % G (one elected thread each), finished by epilogue group n % G,
+// in TMEM accumulator slots that class owns.  One producer and one consumer per slot, each walking its uses in order, is what
+// makes the parity waits on t_full / t_empty safe (a shared ring lets a fast issuer lap a slow group by a whole phase).
+template <int CB, bool K3> __host__ __device__ constexpr int kFirstEpiWarp() { return 1 + kGroups<CB, K3>(); }
+template <int CB, bool K3> __host__ __device__ constexpr int kThreads() { return 32 * (kFirstEpiWarp<CB, K3>() + kEpiWarps<CB, K3>()); }   // warp 0: loads, warps 1..G: MMA issue (warp 1 owns TMEM), then the epilogue warps
+constexpr int kMaxGroups = CD_EPI_GROUPS > 2 ? CD_EPI_GROUPS : 2;
 constexpr int kMaxWStages = 4;
 constexpr int kAStages = 4;
 constexpr int kMaxAcc = 8;
@@ -199,7 +212,30 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t* r) {
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld8_issue(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr) : "memory");
+}
+template <int W> __device__ __forceinline__ void tmem_ldw_issue(uint32_t taddr, uint32_t* r) {
+    static_assert(W == 8 || W % 16 == 0, "pass width");
+    if constexpr (W == 8) tmem_ld8_issue(taddr, r);
+    else {
+#pragma unroll
+        for (int k = 0; k < W; k += 16) tmem_ld16_issue(taddr + k, r + k);
+    }
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// predicated 128-bit shared-memory accesses (no divergent branch: `if (lane == 31) {...}` compiles to BSSY / BSYNC regions)
+__device__ __forceinline__ void sts128_if(bool pred, uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %5, 0;\n@q st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n}"
+                 ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d), "r"((uint32_t)pred) : "memory");
+}
+__device__ __forceinline__ void lds128_if(bool pred, uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {   // a..d kept when !pred
+    asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %5, 0;\n@q ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n}"
+                 : "+r"(a), "+r"(b), "+r"(c), "+r"(d) : "r"(addr), "r"((uint32_t)pred) : "memory");
+}
 
 struct SmemCtl {
     uint64_t a_full[kAStages], a_empty[kAStages];
@@ -210,8 +246,8 @@ struct SmemCtl {
     uint32_t pad;
 };
 constexpr int kCtlBytes = 512;
-constexpr int kXchFloats = 2 /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64;
-constexpr int kXchBytes = kXchFloats * 4 + 1024;  // 8 KB exchange + 128 floats of bias + 128 floats of folded-PreNorm weight sums
+constexpr int kXchFloats = kMaxGroups /*group*/ * 2 /*parity*/ * 2 /*up,down*/ * 4 /*quarter*/ * 64;
+constexpr int kXchBytes = kXchFloats * 4 + 1024;  // 16 KB exchange + 128 floats of bias + 128 floats of folded-PreNorm weight sums
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
 // A sub-tile's epilogue is one long dependent instruction stream per warp (TMEM loads, exchange, 2 shuffles + 5 flops per
@@ -221,7 +257,7 @@ static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 template <int CB, bool K3> __host__ __device__ constexpr int kHalves() { return (CD_EPI_SPLIT && CB % 32 == 0) ? 2 : 1; }
 
 template <int CB, bool K3, int CPG>   // CPG: channels per GroupNorm group for the statistics (divides CB)
-__global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p) {
+__global__ void __launch_bounds__((kThreads<CB, K3>()), 1) conv_mma_kernel(const MmaParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem);
     float* xch = reinterpret_cast<float*>(smem + kCtlBytes);
@@ -233,12 +269,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     const int lane = threadIdx.x & 31;
     const Geom& g = p.g;
     constexpr int N = K3 ? 3 * CB : CB;
+    constexpr int G = kGroups<CB, K3>();
     DBG_DECL();
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), kIssuers); }
+        for (int s = 0; s < kAStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), G); }
         for (int s = 0; s < kMaxAcc; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 4 * kHalves<CB, K3>()); }
-        for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), kIssuers); }
+        for (int s = 0; s < kMaxWStages; ++s) { mbar_init(smem_u32(&ctl->w_full[s]), 1); mbar_init(smem_u32(&ctl->w_empty[s]), G); }
         mbar_init(smem_u32(&ctl->w_res), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -250,15 +287,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = ctl->tmem_base;
-    // accumulator slot of sub-tile n: even sub-tiles (issuer 0 / epilogue group 0) and odd ones (issuer 1 / group 1)
-    // own disjoint halves of the slot ring, so every slot's full/empty chain has one producer and one consumer
-    const uint32_t hacc = (uint32_t)p.nacc >> 1;
-    // (runtime integer divisions cost ~25 instructions and a MUFU round trip each; these run once per sub-tile in every role.
-    //  hacc is 1, 2 or 4 for every shape in use: mask / shift, with the division kept for the odd case)
-    const bool hacc_p2 = (hacc & (hacc - 1u)) == 0u;
-    const uint32_t hacc_log = 31u - (uint32_t)__clz((int)hacc);
-    auto slot_of = [&](uint32_t n) { const uint32_t h = n >> 1; return 2u * (hacc_p2 ? (h & (hacc - 1u)) : (h % hacc)) + (n & 1u); };
-    auto phase_of = [&](uint32_t n) { const uint32_t h = n >> 1; return (hacc_p2 ? (h >> hacc_log) : (h / hacc)) & 1u; };
+    // accumulator slots of class c (sub-tiles n = c, c + G, ...; h = n / G counts the class's sub-tiles): the nacc slots are dealt
+    // out as evenly as they go (N = 96, G = 3: 2 + 2 + 1); use h of a class is slot base + h % cnt with phase (h / cnt) & 1.
+    // (h / cnt by multiply-high: exact for h < 2^29, cnt <= 8.)
+    struct SlotRing { uint32_t base, cnt, magic; };
+    auto ring_of = [&](uint32_t c) {
+        const uint32_t lo = (uint32_t)p.nacc / (uint32_t)G, extra = (uint32_t)p.nacc - lo * (uint32_t)G;
+        SlotRing r;
+        r.cnt = lo + (c < extra ? 1u : 0u);
+        r.base = c * lo + (c < extra ? c : extra);
+        r.magic = 0xffffffffu / r.cnt + 1u;
+        return r;
+    };
+    auto lap_of = [](const SlotRing& r, uint32_t h) { return r.cnt == 1u ? h : __umulhi(h, r.magic); };   // (the magic number wraps to 0 for cnt = 1)
+    auto slot_of = [&](const SlotRing& r, uint32_t h) { return r.base + (h - lap_of(r, h) * r.cnt); };
+    auto phase_of = [&](const SlotRing& r, uint32_t h) { return lap_of(r, h) & 1u; };
 
     const int cb = blockIdx.x % p.ncb;
     const int cta = blockIdx.x / p.ncb;
@@ -319,7 +362,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 }
             }
         }
-    } else if (warp < kFirstEpiWarp) {
+    } else if (warp < kFirstEpiWarp<CB, K3>()) {
         // ===================== MMA issuers (one thread of each of two warps) =====================
         // A single thread cannot issue M128xN96xK16 MMAs with changing descriptors faster than one per ~105 clk
         // (measured, scripts/mma_microbench.cu: descriptor arithmetic -> R2UR -> UTCHMMA is a serial chain), while the
@@ -346,7 +389,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
             const uint32_t qstep = (2u * chunk_bytes) >> 4, bstep = (2u * N * 16u) >> 4;
             const uint32_t jstep = ((uint32_t)p.sub_stride * 16u) >> 4;
             const int nq = p.nchunks >> 1;
-            uint32_t cnt = 0;
+            // sub-tiles are numbered n = cnt + j; (tc, th) = (n % G, n / G) of the current tile's first sub-tile, kept as counters
+            uint32_t tc = 0, th = 0;
+            const SlotRing ring = ring_of(iw);
+            auto next_tile = [&]() { tc += (uint32_t)p.MT; while (tc >= (uint32_t)G) { tc -= (uint32_t)G; ++th; } };
+            // is sub-tile j of the current tile mine, and which use of my class is it
+            auto mine = [&](int j, uint32_t& h) { uint32_t c = tc + (uint32_t)j; h = th; while (c >= (uint32_t)G) { c -= (uint32_t)G; ++h; } return c == iw; };
             uint32_t ws = 0, wph = 0;                 // weight-ring stage / phase
             int astage = 0;                           // activation-ring stage / phase of the next item
             uint32_t aph = 0;
@@ -383,10 +431,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                         bool issued = false;
                         for (int j = 0; j < p.MT; ++j) {
-                            const uint32_t n = cnt + j;
-                            if ((DBG_MODE(64) ? 0u : (n & 1u)) != iw) continue;        // debug 64: issuer 0 issues every sub-tile
+                            uint32_t h;
+                            if (!mine(j, h)) continue;
                             const uint32_t a_lo = a_lo0 + (uint32_t)j * jstep;
-                            const uint32_t slot = slot_of(n), tph = phase_of(n);
+                            const uint32_t slot = slot_of(ring, h), tph = phase_of(ring, h);
                             const uint32_t dcol = tmem_base + slot * N;
                             const long long tB = DBG_T();
                             if (kgi == 0) {
@@ -421,10 +469,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         if (issued) umma_commit_elect(smem_u32(&ctl->a_empty[stage]));
                         else mbar_arrive_elect(smem_u32(&ctl->a_empty[stage]));
                     }
-                    cnt += p.MT;
+                    next_tile();
                     continue;
                 }
-                if (!leader) { cnt += p.MT; continue; }      // streamed-weight form: the elected lane walks alone
+                if (!leader) { next_tile(); continue; }      // streamed-weight form: the elected lane walks alone
                 const int stage = astage;
                 const uint32_t ph = aph;
                 next_astage();
@@ -434,8 +482,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                 bool issued = false;
                 {
                     for (int j = 0; j < p.MT; ++j) {
-                        const uint32_t n = cnt + j, slot = slot_of(n), tph = phase_of(n);
-                        if ((n & 1u) == iw) mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
+                        uint32_t h;
+                        if (mine(j, h)) mbar_wait(smem_u32(&ctl->t_empty[slot_of(ring, h)]), phase_of(ring, h) ^ 1);
                     }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
@@ -449,8 +497,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             const uint32_t a_lo1 = a_lo0 + soff[s] + (uint32_t)kc0 * (chunk_bytes >> 4);
                             bool used = false;
                             for (int j = 0; j < p.MT; ++j) {
-                                if (((cnt + j) & 1u) != iw) continue;
-                                const uint32_t dcol = tmem_base + slot_of(cnt + j) * N;
+                                uint32_t h;
+                                if (!mine(j, h)) continue;
+                                const uint32_t dcol = tmem_base + slot_of(ring, h) * N;
                                 uint32_t al = a_lo1 + (uint32_t)j * jstep, b_lo = b_lo0;
                                 for (int q = 0; q < (kcn >> 1); ++q, al += qstep, b_lo += bstep)
                                     umma_f16(dcol, adesc_hi | al, bdesc_hi | b_lo, p.idesc, (s | kg | q) != 0);
@@ -461,9 +510,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                             issued = issued || used;
                         }
                     }
-                    for (int j = 0; j < p.MT; ++j)
-                        if (((cnt + j) & 1u) == iw) umma_commit(smem_u32(&ctl->t_full[slot_of(cnt + j)]));
-                    cnt += p.MT;
+                    for (int j = 0; j < p.MT; ++j) {
+                        uint32_t h;
+                        if (mine(j, h)) umma_commit(smem_u32(&ctl->t_full[slot_of(ring, h)]));
+                    }
+                    next_tile();
                 }
                 if (issued) umma_commit(smem_u32(&ctl->a_empty[stage]));
                 else mbar_arrive(smem_u32(&ctl->a_empty[stage]));
@@ -472,19 +523,20 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
     } else {
         // ===================== epilogue: TMEM -> registers -> global (+ GroupNorm statistics) =====================
         const int q = warp & 3;                   // TMEM lane quarter this warp may read (warp id % 4)
-        const int eset = (warp - kFirstEpiWarp) >> 2;    // 4 sets of 4 warps; each set covers the four lane quarters
-        const int group = eset & 1;               // 0 / 1: the two groups alternate sub-tiles
-        const int half = eset >> 1;               // which half of the block's channels this warp handles (0 when not split)
+        constexpr int EW = kEpiWarps<CB, K3>();
+        const int eset = (warp - kFirstEpiWarp<CB, K3>()) >> 2;    // sets of 4 warps; each set covers the four lane quarters
+        const int group = eset % G;               // the groups take sub-tiles round-robin
+        const int half = eset / G;                // which half of the block's channels this warp handles (0 when not split)
         constexpr int HALVES = kHalves<CB, K3>();
         constexpr int CH = CB / HALVES;           // channels per half
         const int i_row = q * 32 + lane;          // row within the 128-row sub-tile
         float* sbias = xch + kXchFloats;          // bias of this channel block, broadcast-read from shared memory
         float* swsum = sbias + 128;              // folded PreNorm: sum_c W'[o][c]; sbias then holds sum_c W[o][c]*beta[c]
-        for (int c = threadIdx.x - 32 * kFirstEpiWarp; c < CB; c += 32 * kEpiWarps) {
+        for (int c = threadIdx.x - 32 * kFirstEpiWarp<CB, K3>(); c < CB; c += 32 * EW) {
             sbias[c] = p.pn_stats ? __ldg(p.pn_wb + cb * CB + c) : (p.bias ? __ldg(p.bias + cb * CB + c) : 0.f);
             swsum[c] = p.pn_stats ? __ldg(p.pn_wsum + cb * CB + c) : 0.f;
         }
-        asm volatile("bar.sync 5, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        asm volatile("bar.sync 15, %0;" ::"n"(32 * EW) : "memory");
         constexpr int NG = K3 ? CH / CPG : 1;     // statistics groups per half of the channel block
         static_assert(!K3 || CH % CPG == 0, "a GroupNorm group must not straddle the channel halves");
         float gs[NG], gq[NG];                     // this thread's running sum / sum of squares per group (sample cur_b)
@@ -509,34 +561,50 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
         };
         const int halo_delta = g.P * g.Rp;
         const int total_sub = half < HALVES ? my_tiles * p.MT : 0;     // CB not a multiple of 32: the second half idles
-        int e_tile = tile_begin + group / p.MT, e_j = group % p.MT;     // sub-tile n = (tile, j), advanced by 2 per iteration
-        for (int n = group; n < total_sub; n += 2) {
-            const int tile = e_tile, j = e_j;
-            e_j += 2;
-            while (e_j >= p.MT) { e_j -= p.MT; ++e_tile; }
-            const uint32_t slot = slot_of((uint32_t)n), tph = phase_of((uint32_t)n);
-            const long long row = (long long)tile * p.tile_rows + p.d_lead + (long long)j * p.sub_stride + i_row;
-            // which output row is this?  (fast division by the level's constant extents)
+        // Row of this thread in its group's sub-tile n: (tile_begin * MT + n) * sub_stride + d_lead + i_row, i.e. a constant stride of
+        // G * sub_stride rows per iteration.  Its decomposition (sample, z, pp, rr) is kept incrementally (add the decomposed
+        // stride, carry once per digit) instead of three divisions per sub-tile, and the store offset advances with it.
+        const long long cs8 = g.chunk_stride * 8;                        // halves between consecutive chunk planes
+        const long long obase = ((long long)(cb * (CB / 8)) * g.chunk_stride + g.guard) * 8;   // this channel block's first plane, row 0
+        const int e_stride = G * p.sub_stride;
+        int s_b, s_z, s_pp, s_rr;                                        // the stride, digit by digit
+        {
+            int t = e_stride;
+            s_b = t / g.rows_per_sample; t -= s_b * g.rows_per_sample;
+            s_z = t / g.plane; t -= s_z * g.plane;
+            s_pp = t / g.Rp; s_rr = t - s_pp * g.Rp;
+        }
+        int row = (tile_begin * p.MT + group) * p.sub_stride + p.d_lead + i_row - e_stride;   // advanced at the top of the loop
+        int c_b, c_z, c_pp, c_rr;                                        // digits of `row` (floor semantics for the rows before row 0)
+        {
+            int t = row;
+            c_b = t >= 0 ? t / g.rows_per_sample : -((-t + g.rows_per_sample - 1) / g.rows_per_sample);
+            t -= c_b * g.rows_per_sample;
+            c_z = t / g.plane; t -= c_z * g.plane;
+            c_pp = t / g.Rp; c_rr = t - c_pp * g.Rp;
+        }
+        int par = 1;                                                     // exchange-buffer parity of this group's current sub-tile
+        const SlotRing ring = ring_of((uint32_t)group);
+        uint32_t e_s = ring.cnt - 1u, e_ph = 1u;                         // slot index within the group's ring / phase (counters)
+        for (int n = group; n < total_sub; n += G) {
+            par ^= 1;
+            if (++e_s == ring.cnt) { e_s = 0u; e_ph ^= 1u; }
+            const uint32_t slot = ring.base + e_s, tph = e_ph;
+            row += e_stride;
+            c_rr += s_rr; c_pp += s_pp; c_z += s_z; c_b += s_b;
+            if (c_rr >= g.Rp) { c_rr -= g.Rp; ++c_pp; }
+            if (c_pp >= g.Pp) { c_pp -= g.Pp; ++c_z; }
+            if (c_z > g.Z) { c_z -= g.Z + 1; ++c_b; }
+            // which output row is this?
             // 1x1x1 stores cover every row of the sub-tile (whole 32-byte sectors, no read-modify-write in L2/HBM): interior rows
             // get the result, zero rows get zeros (the invariant every consumer relies on), phi halo rows get a don't-care value
             // (re-derived from the interior by whoever needs them) unless this launch maintains them (write_halo).
-            const bool inrange = row >= 0 && row < p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
-            bool valid = inrange, phi_halo = false;
-            int sample = -1;
-            uint32_t pp = 0;
-            if (inrange) {
-                const uint32_t ur = (uint32_t)row;
-                const uint32_t b = fdiv(g, 2, ur);
-                const uint32_t rem = ur - b * (uint32_t)g.rows_per_sample;
-                const uint32_t z = fdiv(g, 0, rem);
-                const uint32_t rem2 = rem - z * (uint32_t)g.plane;
-                pp = fdiv(g, 1, rem2);
-                const uint32_t rr = rem2 - pp * (uint32_t)g.Rp;
-                const bool nonzero_row = z < (uint32_t)g.Z && rr < (uint32_t)g.R;
-                valid = nonzero_row && pp >= 1u && pp <= (uint32_t)g.P;
-                phi_halo = nonzero_row && !valid;
-                sample = (int)b;
-            }
+            const bool inrange = row >= 0 && row < (int)p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
+            const bool nonzero_row = c_z < g.Z && c_rr < g.R;
+            const bool valid = inrange && nonzero_row && c_pp >= 1 && c_pp <= g.P;
+            const bool phi_halo = inrange && nonzero_row && !valid;
+            const int sample = inrange ? c_b : -1;
+            const uint32_t pp = (uint32_t)c_pp;
             // 1x1x1 (HBM-bound): whole-sector stores of every row.  3x3x3 (epilogue-bound): interior rows only, measured faster.
             const bool do_store = K3 ? valid : (inrange && !(p.write_halo && phi_halo));
             const bool keep = valid || (!K3 && phi_halo && !p.write_halo);
@@ -556,9 +624,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #endif
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + slot * N;
             if constexpr (K3) {
-                constexpr int CW = 16;                     // channels recombined per pass
-                static_assert(CH % CW == 0, "channel half must be a multiple of 16");
-                const int par = (n >> 1) & 1;
+                constexpr int CW = (G >= 3) ? CD_EPI_CW3 : 16;   // channels recombined per pass
+                static_assert(CH % CW == 0, "channel half must be a multiple of the pass width");
                 float* xup = xch + (size_t)(((group * 2 + par) * 2 + 0) * 4) * 64;
                 float* xdn = xch + (size_t)(((group * 2 + par) * 2 + 1) * 4) * 64;
                 // sample bookkeeping for the statistics (warp-uniform decisions)
@@ -580,17 +647,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     uint32_t r0[W], r1[W], r2[W];
 #pragma unroll
                     for (int k = 0; k < W; ++k) { r0[k] = 0; r1[k] = 0; r2[k] = 0; }
-                    if (!DBG_MODE(32))
-#pragma unroll
-                    for (int k = 0; k < W; k += 16) {
-                        if (k < w) {
-                            tmem_ld16_issue(taddr + CB + c0 + k, r1 + k);       // D_1 of row m
-                            tmem_ld16_issue(taddr + c0 + k, r0 + k);            // D_0 of row m   (wanted by lane + 1)
-                            tmem_ld16_issue(taddr + 2 * CB + c0 + k, r2 + k);   // D_2 of row m   (wanted by lane - 1)
-                        }
+                    if (!DBG_MODE(32)) {
+                        tmem_ldw_issue<W>(taddr + CB + c0, r1);       // D_1 of row m
+                        tmem_ldw_issue<W>(taddr + c0, r0);            // D_0 of row m   (wanted by lane + 1)
+                        tmem_ldw_issue<W>(taddr + 2 * CB + c0, r2);   // D_2 of row m   (wanted by lane - 1)
                     }
                     tmem_ld_wait();
-                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(9, DBG_T() - tE1);
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp<CB, K3>() && lane == 0) DBG_ADD(9, DBG_T() - tE1);
                     if (cr + CW >= CH) {
                         // this warp's last TMEM read of the sub-tile: the slot is free once all 4*HALVES warps have arrived
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -605,14 +668,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     // (A split-phase mbarrier with lanes 0 / 31 finished in a second pass measured slower: 0.64 vs 0.50 ms.)
                     const bool xchg = !DBG_MODE(4) && !DBG_MODE(1024);
                     if (xchg) {
-                        if (lane == 31) {
+                        const uint32_t up_s = smem_u32(xup + q * 64 + c0), dn_s = smem_u32(xdn + q * 64 + c0);
 #pragma unroll
-                            for (int k = 0; k < W; k += 4) *reinterpret_cast<uint4*>(xup + q * 64 + c0 + k) = make_uint4(r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
-                        }
-                        if (lane == 0) {
+                        for (int k = 0; k < W; k += 4) sts128_if(lane == 31, up_s + k * 4, r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
 #pragma unroll
-                            for (int k = 0; k < W; k += 4) *reinterpret_cast<uint4*>(xdn + q * 64 + c0 + k) = make_uint4(r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
-                        }
+                        for (int k = 0; k < W; k += 4) sts128_if(lane == 0, dn_s + k * 4, r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
                     }
                     const int src_up = (lane + 31) & 31, src_dn = (lane + 1) & 31;
                     float acc[W];
@@ -631,17 +691,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                     if (xchg) {
                         if (!DBG_MODE(512)) asm volatile("bar.sync %0, 128;" ::"r"(1 + eset) : "memory");
-                        if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(10, DBG_T() - tE1);
-                        if (lane == 0 && q > 0) {          // D_0 of the previous quarter's last row
-                            const float* src = xup + (q - 1) * 64 + c0;
+                        if (blockIdx.x == 0 && warp == kFirstEpiWarp<CB, K3>() && lane == 0) DBG_ADD(10, DBG_T() - tE1);
+                        // lane 0: D_0 of the previous quarter's last row; lane 31: D_2 of the next quarter's first row
+                        // (q = 0 / q = 3 keep a don't-care value: rows 0 and 127 of a sub-tile are never stored)
+                        const uint32_t up_s = smem_u32(xup + ((q + 3) & 3) * 64 + c0), dn_s = smem_u32(xdn + ((q + 1) & 3) * 64 + c0);
 #pragma unroll
-                            for (int k = 0; k < W; k += 4) { const uint4 t = *reinterpret_cast<const uint4*>(src + k); r0[k] = t.x; r0[k + 1] = t.y; r0[k + 2] = t.z; r0[k + 3] = t.w; }
-                        }
-                        if (lane == 31 && q < 3) {         // D_2 of the next quarter's first row
-                            const float* src = xdn + (q + 1) * 64 + c0;
+                        for (int k = 0; k < W; k += 4) lds128_if(lane == 0, up_s + k * 4, r0[k], r0[k + 1], r0[k + 2], r0[k + 3]);
 #pragma unroll
-                            for (int k = 0; k < W; k += 4) { const uint4 t = *reinterpret_cast<const uint4*>(src + k); r2[k] = t.x; r2[k + 1] = t.y; r2[k + 2] = t.z; r2[k + 3] = t.w; }
-                        }
+                        for (int k = 0; k < W; k += 4) lds128_if(lane == 31, dn_s + k * 4, r2[k], r2[k + 1], r2[k + 2], r2[k + 3]);
                     }
 #pragma unroll
                     for (int k = 0; k < W; ++k) acc[k] += __uint_as_float(r0[k]) + __uint_as_float(r2[k]);
@@ -649,24 +706,24 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
 #pragma unroll
                         for (int k = 0; k < W; k += 8) {
                             float f[8];
-                            unpack8(load8(p.addsrc + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row)), f);
+                            unpack8(load8(p.addsrc + obase + (long long)row * 8 + ((c0 + k) >> 3) * cs8), f);
 #pragma unroll
                             for (int e = 0; e < 8; ++e) acc[k + e] += f[e];
                         }
                     }
-                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(11, DBG_T() - tE1);
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp<CB, K3>() && lane == 0) DBG_ADD(11, DBG_T() - tE1);
 #pragma unroll
                     for (int k = 0; k < W; k += 8) {
                         Half8 h = pack8(acc + k);
                         if (!keep) h = Half8{};
-                        __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
+                        __half* o = p.dst + obase + (long long)row * 8 + ((c0 + k) >> 3) * cs8;
                         if (do_store && !DBG_MODE(8)) store8(o, h);
                         if (p.write_halo) {      // uniform branch: the resblock convs (no halo copies) skip the address arithmetic too
                             if (halo_up) store8(o + (long long)halo_delta * 8, h);
                             if (halo_dn) store8(o - (long long)halo_delta * 8, h);
                         }
                     }
-                    if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) DBG_ADD(12, DBG_T() - tE1);
+                    if (blockIdx.x == 0 && warp == kFirstEpiWarp<CB, K3>() && lane == 0) DBG_ADD(12, DBG_T() - tE1);
                     if (p.stats && valid && !DBG_MODE(16)) {
                         if (uniform) {
 #pragma unroll
@@ -725,7 +782,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                         }
                         Half8 h = pack8(acc);
                         if (!keep) h = Half8{};
-                        __half* o = p.dst + plcp_offset(g, cb * (CB / 8) + ((c0 + k) >> 3), row);
+                        __half* o = p.dst + obase + (long long)row * 8 + ((c0 + k) >> 3) * cs8;
                         if (do_store) store8(o, h);
                         if (p.write_halo) {
                             if (halo_up) store8(o + (long long)halo_delta * 8, h);
@@ -734,11 +791,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_mma_kernel(const MmaParams p
                     }
                 }
             }
-            if (blockIdx.x == 0 && warp == kFirstEpiWarp && lane == 0) { DBG_ADD(4, tE1 - tE0); DBG_ADD(5, DBG_T() - tE1); DBG_ADD(6, 1); }
+            if (blockIdx.x == 0 && warp == kFirstEpiWarp<CB, K3>() && lane == 0) { DBG_ADD(4, tE1 - tE0); DBG_ADD(5, DBG_T() - tE1); DBG_ADD(6, 1); }
         }
         if (K3 && p.stats) flush();
     }
-    DBG_FLUSH(blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == kFirstEpiWarp));
+    DBG_FLUSH(blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == kFirstEpiWarp<CB, K3>()));
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
@@ -790,7 +847,7 @@ static cudaError_t launch_inst(const MmaParams& p, int grid, size_t smem, int ma
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    conv_mma_kernel<CB, K3, CPG><<<grid, kThreads, smem, st>>>(p);
+    conv_mma_kernel<CB, K3, CPG><<<grid, kThreads<CB, K3>(), smem, st>>>(p);
     return cudaSuccess;
 }
 
@@ -845,8 +902,12 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     p.sub_stride = k3 ? 126 : 128;
     p.d_lead = k3 ? -1 : 0;
     p.nacc = 512 / p.N; if (p.nacc > kMaxAcc) p.nacc = kMaxAcc;
-    p.nacc &= ~1;          // even: the two issuer / epilogue-group pairs own disjoint halves
-    if (p.nacc < 2) return 1;
+    // classes (issuer + epilogue group pairs) of this shape's kernel and the slots every class is sure to own
+    const int groups = k3 ? (p.CB == 16 ? kGroups<16, true>() : p.CB == 32 ? kGroups<32, true>() : p.CB == 48 ? kGroups<48, true>() : kGroups<64, true>())
+                          : kGroups<32, false>();
+    const int class_slots = p.nacc / groups;
+    if (class_slots < 1) return 1;
+    const int mt_open = groups * class_slots < 4 ? groups * class_slots : 4;   // largest tile whose accumulators can all be open at once
     p.w_bytes_cb = p.nshift * cp.Cin_total * p.N * 2;
     p.kgroup_chunks = p.nchunks < 8 ? p.nchunks : 8;
     p.wstage_bytes = p.kgroup_chunks * p.N * 16;
@@ -886,22 +947,19 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
     //    With K staged in groups all of a tile's accumulators stay open together: keep one slot free for the epilogue.
     for (int ksplit = 1; ksplit <= 8 && !found; ksplit *= 2) {
         if (p.nchunks % ksplit != 0 || (p.nchunks / ksplit) % 2 != 0) continue;
-        int mt_max = ksplit > 1 ? (p.nacc - 1 < 4 ? p.nacc - 1 : 4) : 4;
+        int mt_max = ksplit > 1 ? (p.nacc - 1 < mt_open ? p.nacc - 1 : mt_open) : 4;
         if (const char* e = getenv("CD_MMA_MT")) { const int v = atoi(e); if (v >= 1 && v < mt_max) mt_max = v; }   // diagnostics
         for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
             for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
     }
     // 2) otherwise: weights streamed through the 3-stage ring (K unsplit), two activation stages, largest tile that fits
     //    (a 2-stage ring would admit larger tiles for 128-wide inputs but faulted on multi-tile CTAs: not used)
-    for (int mt = 4; mt >= 1 && !found; --mt) {
-        if (mt > p.nacc) continue;
-        found = accept(0, 1, mt, 2);
-    }
+    for (int mt = mt_open; mt >= 1 && !found; --mt) found = accept(0, 1, mt, 2);
     // 3) single-stage forms
     p.nwstages = nwstages_plan;
     for (int resident = 1; resident >= 0 && !found; --resident)
         for (int mt = 4; mt >= 1 && !found; --mt) {
-            if (!resident && mt > p.nacc) continue;
+            if (!resident && mt > mt_open) continue;
             if (resident && mt < 2 && k3) continue;   // a 1-sub-tile resident tile re-reads too much halo: stream instead
             found = accept(resident, 1, mt, 1);
         }
