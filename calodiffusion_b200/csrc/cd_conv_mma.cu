@@ -943,14 +943,21 @@ int launch_conv_mma(const ConvParams& cp, const __half* packed_w, cudaStream_t s
         smem_total = total;
         return true;
     };
-    // 1) weights resident, >= 2 activation stages; K staged in as few groups as fit; largest tile first (least halo re-read).
-    //    With K staged in groups all of a tile's accumulators stay open together: keep one slot free for the epilogue.
+    // 1) weights resident, >= 2 activation stages; K staged in as few groups as fit.  Unsplit K: deepest activation ring first, then
+    //    the largest tile (DS2 32 -> 32 at L0: 4 stages of 2 sub-tiles 0.423 ms, 3 x 3 0.436, 2 x 4 0.439 - a deeper ring hides the
+    //    window loads better than a larger tile saves halo re-reads).  With K staged in groups all of a tile's accumulators stay
+    //    open together (keep one slot free for the epilogue) and every stage is a fraction of a window: largest tile first.
     for (int ksplit = 1; ksplit <= 8 && !found; ksplit *= 2) {
         if (p.nchunks % ksplit != 0 || (p.nchunks / ksplit) % 2 != 0) continue;
         int mt_max = ksplit > 1 ? (p.nacc - 1 < mt_open ? p.nacc - 1 : mt_open) : 4;
         if (const char* e = getenv("CD_MMA_MT")) { const int v = atoi(e); if (v >= 1 && v < mt_max) mt_max = v; }   // diagnostics
-        for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
-            for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
+        if (ksplit == 1 && !getenv("CD_MMA_TILE_FIRST")) {
+            for (int astages = kAStages; astages >= 2 && !found; --astages)
+                for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt) found = accept(1, ksplit, mt, astages);
+        } else {
+            for (int mt = mt_max; mt >= (k3 ? 2 : 1) && !found; --mt)
+                for (int astages = kAStages; astages >= 2 && !found; --astages) found = accept(1, ksplit, mt, astages);
+        }
     }
     // 2) otherwise: weights streamed through the 3-stage ring (K unsplit), two activation stages, largest tile that fits
     //    (a 2-stage ring would admit larger tiles for 128-wide inputs but faulted on multi-tile CTAs: not used)
