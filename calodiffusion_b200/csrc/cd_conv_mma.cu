@@ -566,7 +566,11 @@ __global__ void __launch_bounds__((kThreads<CB, K3>()), 1) conv_mma_kernel(const
         // stride, carry once per digit) instead of three divisions per sub-tile, and the store offset advances with it.
         const long long cs8 = g.chunk_stride * 8;                        // halves between consecutive chunk planes
         const long long obase = ((long long)(cb * (CB / 8)) * g.chunk_stride + g.guard) * 8;   // this channel block's first plane, row 0
-        const int e_stride = G * p.sub_stride;
+        int e_stride = G * p.sub_stride;
+        // loop invariants pinned in registers (ptxas otherwise re-loads them from the parameter bank every sub-tile and the
+        // epilogue stalls on the constant-cache latency: 6 % of the kernel's stall samples)
+        int gRp = g.Rp, gPp = g.Pp, gZ = g.Z, gR = g.R, gP = g.P, nrows_i = (int)p.nrows;
+        asm volatile("" : "+r"(e_stride), "+r"(gRp), "+r"(gPp), "+r"(gZ), "+r"(gR), "+r"(gP), "+r"(nrows_i));
         int s_b, s_z, s_pp, s_rr;                                        // the stride, digit by digit
         {
             int t = e_stride;
@@ -592,16 +596,16 @@ __global__ void __launch_bounds__((kThreads<CB, K3>()), 1) conv_mma_kernel(const
             const uint32_t slot = ring.base + e_s, tph = e_ph;
             row += e_stride;
             c_rr += s_rr; c_pp += s_pp; c_z += s_z; c_b += s_b;
-            if (c_rr >= g.Rp) { c_rr -= g.Rp; ++c_pp; }
-            if (c_pp >= g.Pp) { c_pp -= g.Pp; ++c_z; }
-            if (c_z > g.Z) { c_z -= g.Z + 1; ++c_b; }
+            if (c_rr >= gRp) { c_rr -= gRp; ++c_pp; }
+            if (c_pp >= gPp) { c_pp -= gPp; ++c_z; }
+            if (c_z > gZ) { c_z -= gZ + 1; ++c_b; }
             // which output row is this?
             // 1x1x1 stores cover every row of the sub-tile (whole 32-byte sectors, no read-modify-write in L2/HBM): interior rows
             // get the result, zero rows get zeros (the invariant every consumer relies on), phi halo rows get a don't-care value
             // (re-derived from the interior by whoever needs them) unless this launch maintains them (write_halo).
-            const bool inrange = row >= 0 && row < (int)p.nrows && (!K3 || (i_row >= 1 && i_row <= 126));
-            const bool nonzero_row = c_z < g.Z && c_rr < g.R;
-            const bool valid = inrange && nonzero_row && c_pp >= 1 && c_pp <= g.P;
+            const bool inrange = row >= 0 && row < nrows_i && (!K3 || (i_row >= 1 && i_row <= 126));
+            const bool nonzero_row = c_z < gZ && c_rr < gR;
+            const bool valid = inrange && nonzero_row && c_pp >= 1 && c_pp <= gP;
             const bool phi_halo = inrange && nonzero_row && !valid;
             const int sample = inrange ? c_b : -1;
             const uint32_t pp = (uint32_t)c_pp;
@@ -609,7 +613,7 @@ __global__ void __launch_bounds__((kThreads<CB, K3>()), 1) conv_mma_kernel(const
             const bool do_store = K3 ? valid : (inrange && !(p.write_halo && phi_halo));
             const bool keep = valid || (!K3 && phi_halo && !p.write_halo);
             const bool halo_up = valid && p.write_halo && pp == 1u;               // copy to pp = P+1
-            const bool halo_dn = valid && p.write_halo && pp == (uint32_t)g.P;    // copy to pp = 0
+            const bool halo_dn = valid && p.write_halo && pp == (uint32_t)gP;     // copy to pp = 0
             const long long tE0 = DBG_T();
             mbar_wait_relaxed(smem_u32(&ctl->t_full[slot]), tph);
             const long long tE1 = DBG_T();
