@@ -46,6 +46,7 @@ struct ConvW {
     // 64 -> 64 stride-1 3x3x3 conv as two 64 -> 32 halves (output channels 0-31 / 32-63): each half's 110 KB of weights stays
     // resident in shared memory (K-staged form, 0.62 of peak) where the full 221 KB has to stream through the weight ring (0.39)
     __half* wmma_lo = nullptr; __half* wmma_hi = nullptr; float* bias_hi = nullptr;
+    __half* wz = nullptr;        // Z-stacked tcgen05 layout (cd_conv_zstack.cu): 3x3x3, C_out = 32, sampling handles only
     int Cin = 0, Cout = 0, kz = 1, kp = 1, kr = 1;
     int transposed = 0;
 };
@@ -251,6 +252,14 @@ static bool pack_conv(cd_unet* h, const std::string& wname, const std::string& b
         out->wmma = h->dalloc<__half>(hp.size(), false);
         if (out->wmma) cudaMemcpy(out->wmma, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
     }
+    // Z-stacked layout for the large-plane levels (taken per launch where the strip decomposition is row-efficient): not in
+    // training (the weight layouts are re-derived on the device there)
+    if (want_mma && !transposed && !h->train && zstack_conv_supported(Cin_pad, Cout, taps) && !getenv("CD_NO_ZSTACK")) {
+        std::vector<__half> hp(zstack_packed_elems(Cin_pad, Cout, taps));
+        zstack_pack_weights(pk.data(), Cin_pad, Cout, hp.data());
+        out->wz = h->dalloc<__half>(hp.size(), false);
+        if (out->wz) cudaMemcpy(out->wz, hp.data(), hp.size() * sizeof(__half), cudaMemcpyHostToDevice);
+    }
     // output-channel halves of a 64 -> 64 conv (see ConvW): not in training (the weight layouts are re-derived on the device there)
     if (want_mma && !transposed && !h->train && taps == 27 && Cin_pad == 64 && Cout == 64 && out->wmma && out->bias &&
         mma_conv_supported(Cin_pad, Cout / 2, taps) && !getenv("CD_NO_OSPLIT")) {
@@ -368,6 +377,9 @@ struct Builder {
                     if (launch_conv_mma(hi, w.wmma_hi, r.st) == 0) { hh->launches += 1; return; }
                     // (the first half is overwritten by whichever full-width form runs below)
                 }
+            }
+            if (hh->conv_backend == 0 && w.wz && stride == 1 && !w.transposed) {
+                if (launch_conv_zstack(p, w.wz, 0, r.st) == 0) return;
             }
             if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed) {
                 if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
@@ -1551,6 +1563,8 @@ extern "C" int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, in
     int rc = 0;
     if (backend == 0) {
         if (!cw.wmma || launch_conv_mma(p, cw.wmma, st) != 0) rc = fail("tcgen05 conv does not support this shape");
+    } else if (backend == 3) {
+        if (!cw.wz || launch_conv_zstack(p, cw.wz, 1, st) != 0) rc = fail("Z-stacked tcgen05 conv does not support this shape");
     } else if (backend == 2) {
         p.write_halo = 1;
         if (!cw.wgat || launch_conv_gather(p, cw.wgat, st) != 0) rc = fail("gather tcgen05 conv does not support this shape");

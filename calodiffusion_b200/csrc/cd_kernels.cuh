@@ -121,6 +121,11 @@ bool mma_conv_supported(int Cin, int Cout, int taps);
 size_t mma_packed_elems(int Cin, int Cout, int taps);
 // w: fp32 [tap][ci][co]; out: fp16 blocks in the layout the tcgen05 kernel streams (see cd_conv_mma.cu)
 void mma_pack_weights(const float* w, int Cin, int Cout, int taps, __half* out);
+// Z-stacked tcgen05 conv (cd_conv_zstack.cu): 3x3x3 stride 1, C_out = 32; force = 1 takes it whatever its row efficiency
+bool zstack_conv_supported(int Cin, int Cout, int taps);
+size_t zstack_packed_elems(int Cin, int Cout, int taps);
+void zstack_pack_weights(const float* w, int Cin, int Cout, __half* out);
+int launch_conv_zstack(const ConvParams& p, const __half* packed_w, int force, cudaStream_t st);
 
 
 // ---- training step (cd_backward.cu) ---------------------------------------------------------------

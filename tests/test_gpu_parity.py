@@ -134,6 +134,36 @@ def test_tcgen05_conv_variants(models, case):
     assert max(errs.values()) < TOL_LAYER, errs
 
 
+@pytest.mark.parametrize("case", ["ds2", "ds3", "hgcal"])
+def test_zstacked_tcgen05_conv_variants(models, case):
+    """The Z-stacked tcgen05 kernel (backend 3: three Z taps in GEMM-N, strips of 128 rows per plane, same-lane recombination)
+    vs torch fp32 on fp16-rounded operands, forced on whatever the level's row efficiency: 16 / 32 / 64 input channels, levels
+    whose plane is several strips (ds3 L0: 8), one strip and a bit (ds2 L0) and less than one strip (L1 / L2)."""
+    m, c = models(case)
+    lib = m._lib
+    errs = {}
+    errs["k3_l0_32_32"] = _conv_case(m, lib, 0, 0, 32, 32, (3, 3, 3), (1, 1, 1), False, 3)
+    errs["k3_l0_16_32"] = _conv_case(m, lib, 0, 0, 16, 32, (3, 3, 3), (1, 1, 1), False, 3)
+    errs["k3_l0_64_32"] = _conv_case(m, lib, 0, 0, 64, 32, (3, 3, 3), (1, 1, 1), False, 3)
+    errs["k3_l1_32_32"] = _conv_case(m, lib, 1, 1, 32, 32, (3, 3, 3), (1, 1, 1), False, 3)
+    errs["k3_l2_64_32"] = _conv_case(m, lib, 2, 2, 64, 32, (3, 3, 3), (1, 1, 1), False, 3)
+    print(case, {k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
+def test_zstacked_tcgen05_conv_many_planes_per_cta():
+    """Batches at which every CTA of the Z-stacked kernel walks many planes (accumulator-slot and window-ring wrap-around, sample
+    boundaries inside a CTA's range, ranges of unequal length)."""
+    m, c = _model("ds3", max_batch=40)
+    lib = m._lib
+    errs = {}
+    errs["ds3_l0_32_32_B40"] = _conv_case(m, lib, 0, 0, 32, 32, (3, 3, 3), (1, 1, 1), False, 3, B=40)
+    errs["ds3_l0_64_32_B7"] = _conv_case(m, lib, 0, 0, 64, 32, (3, 3, 3), (1, 1, 1), False, 3, B=7)
+    errs["ds3_l1_32_32_B40"] = _conv_case(m, lib, 1, 1, 32, 32, (3, 3, 3), (1, 1, 1), False, 3, B=40)
+    print({k: f"{v:.2e}" for k, v in errs.items()})
+    assert max(errs.values()) < TOL_LAYER, errs
+
+
 def test_tcgen05_conv_many_tiles_per_cta():
     """Batches large enough that every persistent CTA walks several tiles (stage/phase wrap-around of all pipelines):
     resident, K-staged resident and streamed-weight forms."""
