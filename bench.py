@@ -401,7 +401,8 @@ def _roofline(rep, peaks, B, workload):
         # DRAM bytes per launch of this kernel shape from the committed `ncu --set full` capture (profiles/), if recorded
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-                t = json.load(f).get(name)
+                tab = json.load(f)
+                t = tab.get(f"{name}@{workload}") or tab.get(name)
             if t and t.get("batch") == B and t.get("workload") == workload:
                 roof["traffic"] = t["dram_bytes_per_launch"]
                 roof["traffic_source"] = t["source"]

@@ -137,6 +137,14 @@ struct ConvParams {
     // channels per sample of the statistics array when this launch produces only a slice of the output channels (a 64 -> 64 conv
     // run as two 64 -> 32 halves: `dst`, `bias` and `stats` point at the slice, the per-sample stride stays the full width); 0: Cout
     int stats_C = 0;
+    // Optional GroupNorm + SiLU + additive conditioning applied to the INPUT on its way into the GEMM (Z-stacked tcgen05 form only,
+    // single source): src[0] is then the raw output of the previous convolution (phi halo rows written, zero rows zero) and
+    // gn_stats its per-sample (sum, sumsq); the arithmetic is gn_apply_kernel's (act = SiLU), rounded to fp16 like its store.
+    const double* gn_stats = nullptr;    // [B][Cin][2]
+    const float* gn_gamma = nullptr; const float* gn_beta = nullptr;
+    int gn_groups = 0;
+    double gn_count = 0.0;               // voxels per sample (elements per channel)
+    const float* gn_addvec = nullptr; int gn_addvec_stride = 0;    // [B][stride] conditioning vector at this block's offset, or nullptr
     int B;
 };
 

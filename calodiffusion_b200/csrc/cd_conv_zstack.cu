@@ -35,10 +35,22 @@ constexpr int kCB = 32;              // output channels (one block)
 constexpr int kN = 3 * kCB;          // GEMM N
 constexpr int kSlots = 5;            // 5 x 96 = 480 of the 512 TMEM columns
 constexpr int kMaxStages = 8;
-constexpr int kGroups = 3;           // epilogue groups: output planes j, j+1, j+2 in flight
+// epilogue groups (output planes in flight): three; two in the fused-GroupNorm form, whose eight transform warps take their place
+#ifndef ZS_G_FUSED
+#define ZS_G_FUSED 2
+#endif
+#ifndef ZS_G_PLAIN
+#define ZS_G_PLAIN 3
+#endif
+__host__ __device__ constexpr int zs_groups(bool fuse) { return fuse ? ZS_G_FUSED : ZS_G_PLAIN; }
 constexpr int kIssuers = 2;          // MMA-issuing warps, alternating plane-strips (one warp issues an MMA every ~80 clk, the pipe takes one every 56)
 constexpr int kFirstEpi = 1 + kIssuers;
-constexpr int kZsThreads = 32 * (kFirstEpi + 4 * kGroups);
+#ifndef ZS_XF_WARPS
+#define ZS_XF_WARPS 8
+#endif
+constexpr int kXfWarps = ZS_XF_WARPS;          // transform warps of the fused-GroupNorm form
+__host__ __device__ constexpr int zs_first_xf(bool fuse) { return kFirstEpi + 4 * zs_groups(fuse); }
+__host__ __device__ constexpr int zs_threads(bool fuse) { return 32 * (zs_first_xf(fuse) + (fuse ? kXfWarps : 0)); }
 
 struct ZsParams {
     Geom g;
@@ -59,6 +71,9 @@ struct ZsParams {
     int w_bytes;
     uint32_t idesc;
     int write_halo;
+    // fused GroupNorm + SiLU + conditioning on the input (ConvParams::gn_*)
+    const double* gn_stats; const float* gn_gamma; const float* gn_beta; int gn_cpg; double gn_n; const float* gn_addvec; int gn_addvec_stride;
+    int B;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -125,8 +140,15 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// SiLU through one MUFU, as gn_apply_kernel: x*sigmoid(x) = 0.5*x*(1 + tanh(x/2))
+__device__ __forceinline__ float zs_silu_half(float h) {      // h = x/2
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
+}
+
 struct ZsCtl {
-    uint64_t a_full[kMaxStages], a_empty[kMaxStages];
+    uint64_t a_full[kMaxStages], a_empty[kMaxStages], a_ready[kMaxStages];
     uint64_t t_full[kSlots], t_empty[kSlots];
     uint64_t w_res;
     uint32_t tmem_base;
@@ -136,8 +158,10 @@ constexpr int kZsCtlBytes = 512;
 constexpr int kZsBiasBytes = 128;
 static_assert(sizeof(ZsCtl) <= kZsCtlBytes, "ctl block too small");
 
-template <int CPG, int NQ>   // channels per GroupNorm group of the statistics; K16 steps per shift (C_in / 16)
-__global__ void __launch_bounds__(kZsThreads, 1) conv_zs_kernel(const ZsParams p) {
+// CPG: channels per GroupNorm group of the output statistics; NQ: K16 steps per shift (C_in / 16); FUSE: GroupNorm + SiLU +
+// conditioning applied to the staged input windows by four more warps before the MMAs read them
+template <int CPG, int NQ, bool FUSE>
+__global__ void __launch_bounds__(zs_threads(FUSE), 1) conv_zs_kernel(const ZsParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     ZsCtl* ctl = reinterpret_cast<ZsCtl*>(smem);
     float* sbias = reinterpret_cast<float*>(smem + kZsCtlBytes);
@@ -147,9 +171,12 @@ __global__ void __launch_bounds__(kZsThreads, 1) conv_zs_kernel(const ZsParams p
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
     const Geom& g = p.g;
+    constexpr int kGroups = zs_groups(FUSE), kFirstXf = zs_first_xf(FUSE);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kMaxStages; ++s) { mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), 1); }
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(smem_u32(&ctl->a_full[s]), 1); mbar_init(smem_u32(&ctl->a_empty[s]), 1); mbar_init(smem_u32(&ctl->a_ready[s]), kXfWarps);
+        }
         for (int s = 0; s < kSlots; ++s) { mbar_init(smem_u32(&ctl->t_full[s]), 1); mbar_init(smem_u32(&ctl->t_empty[s]), 12); }
         mbar_init(smem_u32(&ctl->w_res), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -216,7 +243,7 @@ __global__ void __launch_bounds__(kZsThreads, 1) conv_zs_kernel(const ZsParams p
             uint32_t aph = 0, slot = 0, tph = 0;
             for (int k = 0; k < K; ++k) {
                 if ((k & 1) == iw) {
-                    mbar_wait(smem_u32(&ctl->a_full[st]), aph);
+                    mbar_wait(smem_u32(FUSE ? &ctl->a_ready[st] : &ctl->a_full[st]), aph);
                     mbar_wait(smem_u32(&ctl->t_empty[slot]), tph ^ 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t a_lo0 = (abuf_s + st * p.a_stage_bytes) >> 4;
@@ -232,6 +259,89 @@ __global__ void __launch_bounds__(kZsThreads, 1) conv_zs_kernel(const ZsParams p
                 }
                 st = (st + 1 == p.nstages) ? 0 : st + 1; aph ^= (uint32_t)(st == 0);
                 slot = (slot + 1 == kSlots) ? 0u : slot + 1u; tph ^= (uint32_t)(slot == 0u);
+            }
+        }
+    } else if (FUSE && warp >= kFirstXf) {
+        // ===================== transform: GroupNorm + SiLU + conditioning on the staged windows, in place =====================
+        // A thread keeps one 8-channel chunk (its scale / shift / conditioning live in registers, re-derived when the sample
+        // changes) and walks that chunk's rows of the window.  Rows outside the plane, rows of the zero column (rr = R) and whole
+        // zero planes (z = Z, planes outside the batch) are written as zeros - what gn_apply_kernel leaves there.  (The only
+        // out-of-plane row an interior output reads is row -1, a zero-column row.)
+        if (K > 0) {
+            constexpr int NCH = 2 * NQ, RSTEP = (32 * kXfWarps) / NCH;
+            const int tid = (warp - kFirstXf) * 32 + lane;
+            const int ch = tid / RSTEP, r0 = tid % RSTEP;      // a warp's lanes take consecutive rows of ONE chunk: 512 contiguous bytes, no bank conflicts
+            uint32_t zmask = 0;                       // bit n: window row r0 + RSTEP*n is always zero
+            int npieces = 0;
+            for (int w = r0; w < p.wrows; w += RSTEP, ++npieces) {
+                const int prow = 128 * c - (g.Rp + 1) + w;
+                const bool zero = prow < 0 || prow >= g.plane || (prow % g.Rp) == g.R;
+                zmask |= (uint32_t)zero << npieces;
+            }
+            float sc[8], sh[8], ad[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sc[j] = 0.f; sh[j] = 0.f; ad[j] = 0.f; }
+            const int Zp1 = g.Z + 1, C = 8 * NCH;
+            int q = p0 - 1;
+            int b = q >= 0 ? q / Zp1 : -1, z = q - b * Zp1, cur_b = -2;
+            int st = 0;
+            uint32_t ph = 0;
+            for (int k = 0; k < K; ++k, ++q, ++z) {
+                if (z >= Zp1) { z -= Zp1; ++b; }
+                const bool plane_ok = b >= 0 && b < p.B && z < g.Z;
+                if (plane_ok && b != cur_b) {
+                    cur_b = b;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int cc = 8 * ch + j, g0 = (cc / p.gn_cpg) * p.gn_cpg;
+                        double s = 0.0, qq = 0.0;
+                        for (int i = 0; i < p.gn_cpg; ++i) {
+                            const double* d = p.gn_stats + ((long long)b * C + g0 + i) * 2;
+                            s += d[0]; qq += d[1];
+                        }
+                        const double n = p.gn_n;
+                        const float mean = (float)(s / n);
+                        float var = (float)(qq / n - (s / n) * (s / n));
+                        if (var < 0.f) var = 0.f;
+                        // (halved: SiLU's x/2 is taken here - scaling by a power of two commutes with the rounding of the FMA)
+                        const float scj = __ldg(p.gn_gamma + cc) * rsqrtf(var + 1e-5f);
+                        sc[j] = 0.5f * scj;
+                        sh[j] = 0.5f * (__ldg(p.gn_beta + cc) - mean * scj);
+                        ad[j] = p.gn_addvec ? __ldg(p.gn_addvec + (long long)b * p.gn_addvec_stride + cc) : 0.f;
+                    }
+                }
+                mbar_wait_relaxed(smem_u32(&ctl->a_full[st]), ph);
+                unsigned char* base = abuf + (size_t)st * p.a_stage_bytes + (size_t)ch * chunk_bytes + (size_t)r0 * 16;
+                // three pieces per batch: their loads, MUFU chains and stores overlap
+                for (int n0 = 0; n0 < npieces; n0 += 3) {
+                    uint4 raw[3];
+                    bool live[3];
+#pragma unroll
+                    for (int u = 0; u < 3; ++u) {
+                        const int n = n0 + u;
+                        live[u] = n < npieces && plane_ok && !((zmask >> n) & 1u);
+                        raw[u] = make_uint4(0u, 0u, 0u, 0u);
+                        if (live[u]) raw[u] = *reinterpret_cast<const uint4*>(base + (size_t)n * RSTEP * 16);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 3; ++u) {
+                        if (live[u]) {
+                            float f[8];
+                            unpack8(*reinterpret_cast<const Half8*>(&raw[u]), f);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[j] = zs_silu_half(fmaf(f[j], sc[j], sh[j])) + ad[j];
+                            const Half8 o = pack8(f);
+                            raw[u] = *reinterpret_cast<const uint4*>(&o);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 3; ++u)
+                        if (n0 + u < npieces) *reinterpret_cast<uint4*>(base + (size_t)(n0 + u) * RSTEP * 16) = raw[u];
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the UMMA operand reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(&ctl->a_ready[st]));
+                st = (st + 1 == p.nstages) ? 0 : st + 1; ph ^= (uint32_t)(st == 0);
             }
         }
     } else {
@@ -276,10 +386,15 @@ __global__ void __launch_bounds__(kZsThreads, 1) conv_zs_kernel(const ZsParams p
         const long long ostep = (long long)kGroups * g.plane * 8;
         for (int jj = group; jj < J + 4 && K > 0; jj += kGroups, z += kGroups, optr += ostep) {
             while (z >= Zp1) { z -= Zp1; ++b; }
-            const int kmax = jj < K ? jj : K - 1;
-            {
-                const uint32_t lap = (uint32_t)kmax / (uint32_t)kSlots;
-                mbar_wait_relaxed(smem_u32(&ctl->t_full[(uint32_t)kmax - lap * kSlots]), lap & 1u);
+            // every plane-strip this iteration reads (or only releases) must be complete: consecutive strips come from different
+            // issuing warps, and a commit only covers the MMAs of the warp that made it
+#pragma unroll
+            for (int d = 2; d >= 0; --d) {
+                const int k = jj - d;
+                if (k >= 0 && k < K) {
+                    const uint32_t lap = (uint32_t)k / (uint32_t)kSlots;
+                    mbar_wait_relaxed(smem_u32(&ctl->t_full[(uint32_t)k - lap * kSlots]), lap & 1u);
+                }
             }
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const bool real = jj >= 2 && jj < J + 2;
@@ -370,6 +485,8 @@ void zstack_pack_weights(const float* w, int Cin, int Cout, __half* out) {
 // Row efficiency of the strip decomposition: rows of a plane / rows the MMAs cover.
 static double zstack_efficiency(const Geom& g) { const int S = (g.plane + 127) / 128; return (double)g.plane / (128.0 * S); }
 
+bool zstack_geom_efficient(const Geom& g) { return zstack_efficiency(g) >= 0.85; }
+
 // force = 1: take this form whatever its row efficiency (tests).  Returns 0 when launched.
 int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, cudaStream_t st) {
     const int taps = cp.kz * cp.kp * cp.kr;
@@ -379,6 +496,8 @@ int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, 
     if (cp.gin.Z != cp.gout.Z || cp.gin.P != cp.gout.P || cp.gin.R != cp.gout.R) return 1;
     for (int s = 0; s < cp.nsrc; ++s) if (cp.src[s].C % 8 != 0) return 1;
     if (cp.addsrc || cp.pn_stats) return 1;
+    const bool fuse = cp.gn_stats != nullptr;
+    if (fuse && (cp.nsrc != 1 || cp.Cin_total != 32 || !cp.gn_gamma || !cp.gn_beta || cp.gn_groups <= 0 || cp.Cin_total % cp.gn_groups)) return 1;
     if (cp.write_halo && cp.gout.P < 2) return 1;
     const Geom& g = cp.gout;
     // the row windows reach Rp + 1 rows past either end of a strip and one plane past either end of the batch: inside the guard
@@ -406,6 +525,10 @@ int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, 
     p.w = packed_w; p.bias = cp.bias; p.dst = cp.dst; p.stats = cp.stats;
     p.stats_C = cp.stats_C > 0 ? cp.stats_C : cp.Cout;
     p.write_halo = cp.write_halo;
+    p.gn_stats = cp.gn_stats; p.gn_gamma = cp.gn_gamma; p.gn_beta = cp.gn_beta; p.gn_addvec = cp.gn_addvec; p.gn_addvec_stride = cp.gn_addvec_stride;
+    p.gn_cpg = fuse ? cp.Cin_total / cp.gn_groups : 1;
+    p.gn_n = cp.gn_count * p.gn_cpg;
+    p.B = cp.B;
     int cpg = 4;
     if (cp.stats) { cpg = cp.stats_cpg; if (cpg != 4 && cpg != 8) return 1; }
     p.ppc = (p.NP + ctas_per_strip - 1) / ctas_per_strip;
@@ -422,18 +545,21 @@ int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, 
     p.idesc = (1u << 4) | ((uint32_t)(kN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);  // f16 x f16 -> f32, K-major A and B, M = 128
     const int grid = p.S * ctas_used;
     cudaError_t e = cudaSuccess;
-    auto go = [&](auto kern, bool& configured) {
+    auto go = [&](auto kern, bool& configured, bool fused) {
         if (!configured) { e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem); configured = e == cudaSuccess; }
-        if (e == cudaSuccess) kern<<<grid, kZsThreads, smem_total, st>>>(p);
+        if (e == cudaSuccess) kern<<<grid, zs_threads(fused), smem_total, st>>>(p);
     };
-    static bool cfg[6] = {false, false, false, false, false, false};
+    static bool cfg[8] = {false, false, false, false, false, false, false, false};
     const int nq = p.nchunks / 2;
-    if (cpg == 4 && nq == 1) go(conv_zs_kernel<4, 1>, cfg[0]);
-    else if (cpg == 4 && nq == 2) go(conv_zs_kernel<4, 2>, cfg[1]);
-    else if (cpg == 4 && nq == 4) go(conv_zs_kernel<4, 4>, cfg[2]);
-    else if (cpg == 8 && nq == 1) go(conv_zs_kernel<8, 1>, cfg[3]);
-    else if (cpg == 8 && nq == 2) go(conv_zs_kernel<8, 2>, cfg[4]);
-    else if (cpg == 8 && nq == 4) go(conv_zs_kernel<8, 4>, cfg[5]);
+    if (fuse && cpg == 4 && nq == 2) go(conv_zs_kernel<4, 2, true>, cfg[6], true);
+    else if (fuse && cpg == 8 && nq == 2) go(conv_zs_kernel<8, 2, true>, cfg[7], true);
+    else if (fuse) return 1;
+    else if (cpg == 4 && nq == 1) go(conv_zs_kernel<4, 1, false>, cfg[0], false);
+    else if (cpg == 4 && nq == 2) go(conv_zs_kernel<4, 2, false>, cfg[1], false);
+    else if (cpg == 4 && nq == 4) go(conv_zs_kernel<4, 4, false>, cfg[2], false);
+    else if (cpg == 8 && nq == 1) go(conv_zs_kernel<8, 1, false>, cfg[3], false);
+    else if (cpg == 8 && nq == 2) go(conv_zs_kernel<8, 2, false>, cfg[4], false);
+    else if (cpg == 8 && nq == 4) go(conv_zs_kernel<8, 4, false>, cfg[5], false);
     else return 1;
     return e == cudaSuccess ? 0 : 1;
 }

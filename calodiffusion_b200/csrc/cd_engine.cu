@@ -303,6 +303,16 @@ static float* upload_vec(cd_unet* h, const std::string& name, int n) {
 // -------------------------------------------------------------------------------------------------
 namespace cd {
 
+// A GroupNorm + SiLU (+ conditioning) whose only consumer is the next convolution: the Z-stacked tcgen05 conv applies it to its
+// staged input windows (cd_conv_zstack.cu), otherwise the op launches gn_apply first.  raw = the normalised tensor's source,
+// the conv's own source buffer is then where gn_apply would put its result.
+struct FusedGn {
+    int raw = -1;
+    float* gamma = nullptr; float* beta = nullptr;
+    int groups = 0; long long stats_off = -1; int addvec_off = -1;
+};
+
+
 struct Builder {
     cd_unet* h;
     bool ok = true;
@@ -319,9 +329,10 @@ struct Builder {
 
     // conv: srcs are buffer indices at level_in; dst buffer at level_out
     void conv(const ConvW& cw, int level_in, int level_out, std::vector<int> srcs, int dst, int stride, int pz, int cp, int pr,
-              int write_halo, long long stats_off /* -1: none */) {
+              int write_halo, long long stats_off /* -1: none */, FusedGn fg = FusedGn()) {
         cd_unet* hh = h;
         ConvW w = cw;
+        static const int zs_force = getenv("CD_ZS_FORCE") ? 1 : 0;     // tests: Z-stacked form whatever the row efficiency / batch
         if (hh->train) {
             TapeOp t;
             t.kind = 0; t.wname = t_wname; t.bname = t_bname; t.Cin_real = t_cin_real ? t_cin_real : w.Cin; t.Cin_pad = w.Cin; t.Cout = w.Cout;
@@ -336,7 +347,8 @@ struct Builder {
             double mo = (double)go.Z * go.P * go.R, mi = (double)gi.Z * gi.P * gi.R;
             int taps = w.kz * w.kp * w.kr;
             char nm[96];
-            snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : ""), w.Cin, w.Cout,
+            // ("gn": this step also applies the GroupNorm + SiLU + conditioning of its input, fused or as a pass of its own)
+            snprintf(nm, sizeof(nm), "conv_k%d%s_c%d_%d_L%d%s", taps, w.transposed ? "T" : (stride > 1 ? "s2" : (fg.raw >= 0 ? "gn" : "")), w.Cin, w.Cout,
                      level_out, (w.wmma && stride == 1 && !w.transposed) ? "_mma" : (w.wgat ? "_gather" : "_simt"));
             // FLOP = 2*MAC as executed: every output voxel x all taps for a (strided) conv; every INPUT voxel x all
             // taps for a transposed conv (an output voxel of a stride-2 transposed conv receives 1/8 of the taps); bytes = fp16 in + out
@@ -378,8 +390,25 @@ struct Builder {
                     // (the first half is overwritten by whichever full-width form runs below)
                 }
             }
+            if (fg.raw >= 0) {
+                const Geom& g = p.gout;
+                const double cnt = (double)g.Z * g.P * g.R;
+                const double* gst = (const double*)(hh->scratch + (size_t)fg.stats_off * r.B);
+                const float* av = fg.addvec_off >= 0 ? hh->addvec + fg.addvec_off : nullptr;
+                if (hh->conv_backend == 0 && w.wz) {
+                    ConvParams pf = p;
+                    pf.src[0].base = hh->bufs[fg.raw].ptr; pf.src[0].C = hh->bufs[fg.raw].C;
+                    pf.gn_stats = gst; pf.gn_gamma = fg.gamma; pf.gn_beta = fg.beta; pf.gn_groups = fg.groups; pf.gn_count = cnt;
+                    pf.gn_addvec = av; pf.gn_addvec_stride = hh->addvec_stride;
+                    if (launch_conv_zstack(pf, w.wz, zs_force, r.st) == 0) return;
+                }
+                // not taken (small batch, other backend): the stand-alone GroupNorm pass, then the convolution on its result
+                launch_gn_apply(g, hh->bufs[fg.raw].ptr, gst, fg.gamma, fg.beta, fg.groups, cnt, av, hh->addvec_stride, nullptr, nullptr, 0,
+                                hh->bufs[srcs[0]].ptr, w.Cin, 1, nullptr, r.B, r.st);
+                hh->launches += 1;
+            }
             if (hh->conv_backend == 0 && w.wz && stride == 1 && !w.transposed) {
-                if (launch_conv_zstack(p, w.wz, 0, r.st) == 0) return;
+                if (launch_conv_zstack(p, w.wz, zs_force, r.st) == 0) return;
             }
             if (hh->conv_backend == 0 && w.wmma && stride == 1 && !w.transposed) {
                 if (launch_conv_mma(p, w.wmma, r.st) == 0) return;
@@ -521,15 +550,29 @@ struct Builder {
                 h->weights.erase("__split_a"); h->weights.erase("__split_b");
             }
         }
+        // block1's GroupNorm + SiLU + conditioning has one consumer, block2's conv: where that conv can run Z-stacked (sampling
+        // handles, C = 32, a plane that fills its strips) the normalisation is applied on the conv's staged input instead of by a
+        // pass of its own; block1's conv then writes its phi halo rows itself
+        static const bool zs_fuse_off = getenv("CD_NO_GN_FUSE") != nullptr, zs_forced = getenv("CD_ZS_FORCE") != nullptr;
+        const bool fuse = !h->train && !split && !zs_fuse_off && c2.wz && Cout == 32 && (zs_forced || zstack_geom_efficient(h->geom[level]));
         tag(pre + "block1.proj.conv.weight", pre + "block1.proj.conv.bias", Cin);
         if (split) conv_split(c1, ca, cb2, level, srcs, t1, (long long)s1);
         else
-        conv(c1, level, level, srcs, t1, 1, 1, 1, 1, 0, (long long)s1);
+        conv(c1, level, level, srcs, t1, 1, 1, 1, 1, fuse ? 1 : 0, (long long)s1);
         int hbuf = acquire(h, level, Cout);
-        gn(pre + "block1.norm.weight", pre + "block1.norm.bias", level, t1, hbuf, Cout, groups, (long long)s1, 1, addvec_off, -1);
-        int t2 = h->train ? acquire(h, level, Cout) : t1;     // training keeps block1's pre-norm tensor
+        FusedGn fg;
+        if (fuse) {
+            fg.raw = t1; fg.groups = groups; fg.stats_off = (long long)s1; fg.addvec_off = addvec_off;
+            fg.gamma = upload_vec(h, pre + "block1.norm.weight", Cout);
+            fg.beta = upload_vec(h, pre + "block1.norm.bias", Cout);
+            if (!fg.gamma || !fg.beta) { ok = false; return -1; }
+        } else {
+            gn(pre + "block1.norm.weight", pre + "block1.norm.bias", level, t1, hbuf, Cout, groups, (long long)s1, 1, addvec_off, -1);
+        }
+        // (fused: block2's conv reads t1, so its output needs a buffer of its own - hbuf, which then also holds the block's result)
+        int t2 = h->train ? acquire(h, level, Cout) : (fuse ? acquire(h, level, Cout) : t1);     // training keeps block1's pre-norm tensor
         tag(pre + "block2.proj.conv.weight", pre + "block2.proj.conv.bias", Cout);
-        conv(c2, level, level, {hbuf}, t2, 1, 1, 1, 1, 0, (long long)s2);
+        conv(c2, level, level, {hbuf}, t2, 1, 1, 1, 1, 0, (long long)s2, fg);
         int res = srcs[0];
         int rbuf = -1;
         if (has_res) {

@@ -126,6 +126,7 @@ bool zstack_conv_supported(int Cin, int Cout, int taps);
 size_t zstack_packed_elems(int Cin, int Cout, int taps);
 void zstack_pack_weights(const float* w, int Cin, int Cout, __half* out);
 int launch_conv_zstack(const ConvParams& p, const __half* packed_w, int force, cudaStream_t st);
+bool zstack_geom_efficient(const Geom& g);     // the level's plane fills its 128-row strips well enough for the Z-stacked form
 
 
 // ---- training step (cd_backward.cu) ---------------------------------------------------------------
