@@ -19,7 +19,9 @@
 //   * D: TMEM accumulator slots of 128 lanes x N fp32 columns, ring-buffered so the epilogue of one 128-row
 //     sub-tile overlaps the MMAs of the next.  Sub-tiles advance by 126 rows (rows 0 and 127 of a sub-tile lack
 //     their m-1 / m+1 neighbour).
-//   * Epilogue (2 groups of 4 warps): tcgen05.ld of D_0/D_1/D_2, R-recombination by two rotate-shuffles per channel:
+//   * Sub-tiles are dealt round-robin to G classes (3 for the narrow 3x3x3 forms, else 2): class c = MMA-issuing warp 1 + c, the
+//     epilogue group of 4 warps c (one warp per TMEM lane quarter, all channels of the block) and the accumulator slots it owns.
+//   * Epilogue: tcgen05.ld of D_0/D_1/D_2, R-recombination by two rotate-shuffles per channel:
 //     lane 31 / lane 0 first publish their D_0 / D_2 rows in shared memory and, after one 128-thread named barrier,
 //     replace them by the neighbouring warp-quarter's values, so the rotation delivers the right row to every lane
 //     without per-element selects or boundary fix-ups; then bias, fp16 rounding, coalesced PLCP stores of the interior
@@ -251,9 +253,10 @@ constexpr int kXchBytes = kXchFloats * 4 + 1024;  // 16 KB exchange + 128 floats
 static_assert(sizeof(SmemCtl) <= kCtlBytes, "ctl block too small");
 
 // A sub-tile's epilogue is one long dependent instruction stream per warp (TMEM loads, exchange, 2 shuffles + 5 flops per
-// output element, stores); with 4 warps per sub-tile it took ~4300 clk against ~1000 clk of MMAs.  The channels of a block
-// are therefore split over two sets of 4 warps ("halves") whenever CB is a multiple of 32: both sets read the same TMEM
-// lane quarters (a warp may only touch lanes 32*(warp%4)..+31) at different columns.
+// output element, stores): ~4300 clk against ~1000 clk of MMAs with one group of 4 warps.  Round 1 split the channels of a block
+// over two sets of 4 warps ("halves", CD_EPI_SPLIT=1: both sets read the same TMEM lane quarters at different columns); round 2
+// measured the kernel bound by the epilogue's instruction COUNT, and the split doubles the per-row work (row decode, masks, barrier
+// waits): three unsplit groups are faster (DS2 32->32 L0: 0.442 vs 0.468 ms) and are the default.
 template <int CB, bool K3> __host__ __device__ constexpr int kHalves() { return (CD_EPI_SPLIT && CB % 32 == 0) ? 2 : 1; }
 
 template <int CB, bool K3, int CPG>   // CPG: channels per GroupNorm group for the statistics (divides CB)

@@ -19,7 +19,7 @@ x = torch.randn([B] + cfg["SHAPE_PAD"][1:], device="cuda")
 sig = torch.full((B,), 1.5, device="cuda")
 names = {0: "baseline", 1: "epilogue off", 3: "epilogue off + A loaded once", 2: "A loaded once", 4: "no exchange/shuffles", 8: "no stores",
          16: "no statistics", 28: "no shuffles/stores/stats", 32: "no TMEM loads", 60: "TMEM-wait + barrier only"}
-names.update({65: "epilogue off, ONE issuer", 64: "one issuer", 129: "epilogue off, no MMAs", 131: "epilogue off, no MMAs, A once", 128: "no MMAs"})
+names.update({129: "epilogue off, no MMAs", 131: "epilogue off, no MMAs, A once", 128: "no MMAs"})
 modes = [int(a) for a in sys.argv[3].split(",")] if len(sys.argv) > 3 else (0, 1, 3, 2, 4, 8, 16, 28, 32, 60)
 for mode in modes:
     os.environ["CD_DBG_MODE"] = str(mode)
