@@ -485,7 +485,12 @@ void zstack_pack_weights(const float* w, int Cin, int Cout, __half* out) {
 // Row efficiency of the strip decomposition: rows of a plane / rows the MMAs cover.
 static double zstack_efficiency(const Geom& g) { const int S = (g.plane + 127) / 128; return (double)g.plane / (128.0 * S); }
 
-bool zstack_geom_efficient(const Geom& g) { return zstack_efficiency(g) >= 0.85; }
+// Break-even against the R-stacked kernel is near 0.78 (section 4 of DESIGN.md); CD_ZS_MIN_EFF overrides (diagnostics).
+static double zstack_min_efficiency() {
+    static const double v = [] { const char* e = getenv("CD_ZS_MIN_EFF"); return e ? atof(e) : 0.85; }();
+    return v;
+}
+bool zstack_geom_efficient(const Geom& g) { return zstack_efficiency(g) >= zstack_min_efficiency(); }
 
 // force = 1: take this form whatever its row efficiency (tests).  Returns 0 when launched.
 int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, cudaStream_t st) {
@@ -516,7 +521,7 @@ int launch_conv_zstack(const ConvParams& cp, const __half* packed_w, int force, 
     if (p.S > num_sms) return 1;
     const int ctas_per_strip = num_sms / p.S;
     // worth it only where most MMA rows are real rows and every CTA walks enough planes to amortise its two extra plane-strips
-    if (!force && (zstack_efficiency(g) < 0.85 || p.NP < 16 * ctas_per_strip || (long long)p.S * ctas_per_strip * 10 < 9LL * num_sms)) return 1;
+    if (!force && (zstack_efficiency(g) < zstack_min_efficiency() || p.NP < 16 * ctas_per_strip || (long long)p.S * ctas_per_strip * 10 < 9LL * num_sms)) return 1;
     if ((long long)cp.B * g.rows_per_sample + 4096 >= (1LL << 31)) return 1;
     p.src[0] = cp.src[0].base; p.src_chunks[0] = cp.src[0].C / 8;
     p.src[1] = cp.nsrc > 1 ? cp.src[1].base : nullptr; p.src_chunks[1] = cp.nsrc > 1 ? cp.src[1].C / 8 : 0;

@@ -214,7 +214,7 @@ void* cd_train_buffer(cd_unet* h, int which /* 0 P, 1 G, 2 M, 3 V, 4 x0 of the l
 int cd_test_conv(cd_unet* h, int level_in, int level_out, int Cin, int Cout, const int* ksize,
                  const int* stride, int transposed, const float* w_host, const float* bias_host,
                  const float* x_dev /* (B,Cin,Z,P,R) fp32 */, float* y_dev /* (B,Cout,Zo,Po,Ro) fp32 */,
-                 int B, int backend /* 0 R-stacked tcgen05, 1 SIMT, 2 gather tcgen05 */, void* stream);
+                 int B, int backend /* 0 R-stacked tcgen05, 1 SIMT, 2 gather tcgen05, 3 Z-stacked tcgen05 */, void* stream);
 int cd_level_shape(const cd_unet* h, int level, int* zpr /* [3] */);
 
 /* cd_conv_noalloc: no counterpart in the reference - added for callers that cannot
